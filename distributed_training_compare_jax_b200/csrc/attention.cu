@@ -1,0 +1,545 @@
+// Causal flash attention forward / backward on tcgen05 tensor cores (op sites K3/K6, reference:
+// model/CausalSelfAttention.py:34-42 — dense softmax(q k^T * hd^-0.5 + causal mask) v; the (1,1,T,T)
+// additive mask of model/GPTModel.py:50-51 is never materialised, the causal predicate is applied
+// to the diagonal tile only and tiles above the diagonal are skipped).
+//
+// Layout: q, k, v are column slices of one [M = B*T, ld] bf16 buffer (head h occupies columns
+// [h*HD, (h+1)*HD) of each slice); o / do / dq / dk / dv use the same convention.
+//
+// Forward  (CTA = one (batch, head, 128-query block), 128 threads, thread r owns query row r):
+//   S  = Q K_j^T      tcgen05.mma 128x128xHD   -> TMEM cols [0,128)
+//   online softmax: tcgen05.ld of the thread's row, exp2, P (bf16) -> 128B-swizzled smem (K-major A operand)
+//   PV = P V_j        tcgen05.mma 128xHDx128 (V consumed MN-major straight from its TMA tile) -> TMEM cols [128,128+HD)
+//   O  = O*alpha + PV in registers; K/V tiles double-buffered by TMA.
+// Backward (CTA = one (batch, head, 128-key block j); loops over query blocks i >= j; thread r owns key row r):
+//   St  = K_j Q_i^T ; dPt = V_j dO_i^T                         (TMEM cols [0,128), [128,256))
+//   Pt  = exp2(St*c - lse2_i) ; dSt = Pt o (dPt - delta_i)     -> two swizzled smem tiles
+//   dV += Pt dO_i ; dK += dSt Q_i     (accumulate in TMEM across i)
+//   dQ_i = dS K_j                     (the dSt tile re-read as an MN-major A operand) -> fp32 red.add to dq_accum
+#include "common.cuh"
+#include "tma_host.h"
+
+namespace dtc {
+
+constexpr int ATT_BLK = 128;
+constexpr float LOG2E = 1.4426950408889634f;
+
+template <int HD>
+struct AttnCfg {
+  static constexpr int ROW_BYTES = HD * 2;                       // 64 or 128
+  static constexpr uint32_t SWZ = (HD == 64) ? SWZ_128B : SWZ_64B;
+  static constexpr int SWZ_BITS = (HD == 64) ? 3 : 2;
+  static constexpr int TILE_BYTES = ATT_BLK * ROW_BYTES;         // one [128 x HD] tile
+  static constexpr uint32_t SBO = 8 * ROW_BYTES;                 // 8-row group pitch (both majors)
+  static constexpr int P_BYTES = ATT_BLK * ATT_BLK * 2;          // [128 x 128] bf16, two 64-col blocks
+};
+
+// P / dS tile: [128 rows x 128 cols] bf16 stored as two [128 x 64] K-major 128B-swizzled blocks.
+DTC_DEVICE uint32_t p_tile_offset(int row, int col8 /* 16-byte chunk index 0..15 */) {
+  const uint32_t blk = col8 >> 3;
+  return blk * (ATT_BLK * 128) + swizzle_offset<3>(row * 128 + (col8 & 7) * 16);
+}
+
+template <int HD>
+__global__ void __launch_bounds__(128)
+flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
+                      const __grid_constant__ CUtensorMap tm_v, bf16* __restrict__ out, long long ldo,
+                      float* __restrict__ lse2_out, int T, int H, float scale_log2) {
+  using C = AttnCfg<HD>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* sQ = smem;
+  uint8_t* sK = sQ + C::TILE_BYTES;      // 2 stages
+  uint8_t* sV = sK + 2 * C::TILE_BYTES;  // 2 stages
+  uint8_t* sP = sV + 2 * C::TILE_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + C::P_BYTES);
+  uint64_t* bar_q = bars;
+  uint64_t* bar_kv = bars + 1;  // [2]
+  uint64_t* bar_s = bars + 3;
+  uint64_t* bar_o = bars + 4;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 5);
+
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int qblk = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  const int row0 = b * T + qblk * ATT_BLK;  // first global row of the query tile
+  const int nkv = qblk + 1;                 // causal: key blocks 0..qblk
+
+  if (tid == 0) {
+    tma_prefetch_desc(&tm_q);
+    tma_prefetch_desc(&tm_k);
+    tma_prefetch_desc(&tm_v);
+    mbar_init(bar_q, 1);
+    mbar_init(&bar_kv[0], 1);
+    mbar_init(&bar_kv[1], 1);
+    mbar_init(bar_s, 1);
+    mbar_init(bar_o, 1);
+    fence_barrier_init();
+  }
+  if (warp == 0) {
+    tmem_alloc(tmem_ptr_smem, 256);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+  const uint32_t tmem_s = tmem_base, tmem_pv = tmem_base + 128;
+  const uint32_t lane_sel = (uint32_t)(warp * 32) << 16;
+
+  if (tid == 0) {
+    mbar_expect_tx(bar_q, C::TILE_BYTES);
+    tma_load_2d(sQ, &tm_q, bar_q, h * HD, row0);
+    mbar_expect_tx(&bar_kv[0], 2 * C::TILE_BYTES);
+    tma_load_2d(sK, &tm_k, &bar_kv[0], h * HD, b * T);
+    tma_load_2d(sV, &tm_v, &bar_kv[0], h * HD, b * T);
+  }
+
+  constexpr uint32_t idesc_s = make_idesc_bf16(128, 128, 0, 0);
+  constexpr uint32_t idesc_pv = make_idesc_bf16(128, HD, 0, 1);
+
+  float o_acc[HD];
+#pragma unroll
+  for (int j = 0; j < HD; ++j) o_acc[j] = 0.f;
+  float m_run = -INFINITY, l_run = 0.f;
+
+  for (int j = 0; j < nkv; ++j) {
+    const int st = j & 1;
+    if (j == 0) mbar_wait(bar_q, 0);
+    mbar_wait(&bar_kv[st], (j >> 1) & 1);
+    tc_fence_after();
+    if (tid == 0) {
+      const uint32_t aq = smem_u32(sQ), ak = smem_u32(sK + st * C::TILE_BYTES);
+#pragma unroll
+      for (int k = 0; k < HD / 16; ++k)
+        umma_bf16(tmem_s, make_smem_desc(aq + k * 32, 16, C::SBO, C::SWZ), make_smem_desc(ak + k * 32, 16, C::SBO, C::SWZ),
+                  idesc_s, k > 0);
+      umma_commit(bar_s);
+      if (j + 1 < nkv) {  // prefetch next K/V tile (its buffer was released when PV of block j-1 completed)
+        const int ns = st ^ 1;
+        mbar_expect_tx(&bar_kv[ns], 2 * C::TILE_BYTES);
+        tma_load_2d(sK + ns * C::TILE_BYTES, &tm_k, &bar_kv[ns], h * HD, b * T + (j + 1) * ATT_BLK);
+        tma_load_2d(sV + ns * C::TILE_BYTES, &tm_v, &bar_kv[ns], h * HD, b * T + (j + 1) * ATT_BLK);
+      }
+    }
+    mbar_wait(bar_s, j & 1);
+    tc_fence_after();
+
+    // ---- online softmax on this thread's row (two sweeps over TMEM: max, then exp + P write) ----
+    const bool diag = (j == qblk);
+    float mx = -INFINITY;
+#pragma unroll 1
+    for (int c = 0; c < 4; ++c) {
+      uint32_t r[32];
+      tmem_ld_32x32b_x32(tmem_s + lane_sel + c * 32, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        const float s = __uint_as_float(r[i]);
+        if (!diag || (c * 32 + i) <= tid) mx = fmaxf(mx, s);
+      }
+    }
+    const float m_new = fmaxf(m_run, mx * scale_log2);  // row always has >= 1 unmasked column
+    const float alpha = exp2f(m_run - m_new);
+    float l_blk = 0.f;
+#pragma unroll 1
+    for (int c = 0; c < 4; ++c) {
+      uint32_t r[32];
+      tmem_ld_32x32b_x32(tmem_s + lane_sel + c * 32, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        float p[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int col = c * 32 + g * 8 + i;
+          const float s = __uint_as_float(r[g * 8 + i]);
+          p[i] = (!diag || col <= tid) ? exp2f(s * scale_log2 - m_new) : 0.f;
+          l_blk += p[i];
+        }
+        *reinterpret_cast<uint4*>(sP + p_tile_offset(tid, c * 4 + g)) =
+            make_uint4(pack_bf16x2(p[0], p[1]), pack_bf16x2(p[2], p[3]), pack_bf16x2(p[4], p[5]), pack_bf16x2(p[6], p[7]));
+      }
+    }
+    l_run = l_run * alpha + l_blk;
+    m_run = m_new;
+    fence_proxy_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    if (tid == 0) {
+      tc_fence_after();
+      const uint32_t ap = smem_u32(sP), av = smem_u32(sV + st * C::TILE_BYTES);
+#pragma unroll
+      for (int k = 0; k < ATT_BLK / 16; ++k)
+        umma_bf16(tmem_pv, make_smem_desc(ap + (k >> 2) * (ATT_BLK * 128) + (k & 3) * 32, 16, 1024, SWZ_128B),
+                  make_smem_desc(av + k * 16 * C::ROW_BYTES, 16, C::SBO, C::SWZ), idesc_pv, k > 0);
+      umma_commit(bar_o);
+    }
+    mbar_wait(bar_o, j & 1);
+    tc_fence_after();
+#pragma unroll
+    for (int c = 0; c < HD / 32; ++c) {
+      uint32_t r[32];
+      tmem_ld_32x32b_x32(tmem_pv + lane_sel + c * 32, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 32; ++i) o_acc[c * 32 + i] = o_acc[c * 32 + i] * alpha + __uint_as_float(r[i]);
+    }
+    tc_fence_before();
+    __syncthreads();  // all TMEM reads / sP writes of this block retired before the next block's MMAs
+  }
+
+  const float inv_l = 1.f / l_run;
+  bf16* orow = out + (long long)(row0 + tid) * ldo + h * HD;
+#pragma unroll
+  for (int c = 0; c < HD / 8; ++c) {
+    *reinterpret_cast<uint4*>(orow + c * 8) =
+        make_uint4(pack_bf16x2(o_acc[c * 8] * inv_l, o_acc[c * 8 + 1] * inv_l),
+                   pack_bf16x2(o_acc[c * 8 + 2] * inv_l, o_acc[c * 8 + 3] * inv_l),
+                   pack_bf16x2(o_acc[c * 8 + 4] * inv_l, o_acc[c * 8 + 5] * inv_l),
+                   pack_bf16x2(o_acc[c * 8 + 6] * inv_l, o_acc[c * 8 + 7] * inv_l));
+  }
+  lse2_out[((long long)b * H + h) * T + qblk * ATT_BLK + tid] = m_run + log2f(l_run);
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 256);
+  }
+}
+
+// delta[b,h,t] = sum_d dO[b,t,h,d] * O[b,t,h,d]   (one thread per 8 columns, HD/8 threads per (row, head))
+template <int HD>
+__global__ void attn_bwd_prep_kernel(const bf16* __restrict__ o, long long ldo, const bf16* __restrict__ d_o,
+                                     long long lddo, float* __restrict__ delta, int M, int T, int H) {
+  constexpr int TPR = HD / 8;
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long item = idx / TPR;
+  const int part = (int)(idx % TPR);
+  const bool ok = item < (long long)M * H;
+  float acc = 0.f;
+  int m = 0, h = 0;
+  if (ok) {
+    m = (int)(item / H);
+    h = (int)(item % H);
+    const uint4 a = *reinterpret_cast<const uint4*>(o + (long long)m * ldo + h * HD + part * 8);
+    const uint4 g = *reinterpret_cast<const uint4*>(d_o + (long long)m * lddo + h * HD + part * 8);
+    const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, gw[4] = {g.x, g.y, g.z, g.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 fa = unpack_bf16x2(aw[j]), fg = unpack_bf16x2(gw[j]);
+      acc += fa.x * fg.x + fa.y * fg.y;
+    }
+  }
+#pragma unroll
+  for (int off = TPR / 2; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+  if (ok && part == 0) {
+    const int b = m / T, t = m % T;
+    delta[((long long)b * H + h) * T + t] = acc;
+  }
+}
+
+template <int HD>
+__global__ void __launch_bounds__(128)
+flash_attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
+                      const __grid_constant__ CUtensorMap tm_v, const __grid_constant__ CUtensorMap tm_do,
+                      const float* __restrict__ lse2, const float* __restrict__ delta, float* __restrict__ dq_accum,
+                      long long lddq, bf16* __restrict__ dk, bf16* __restrict__ dv, long long lddkv, int T, int H,
+                      float scale, float scale_log2) {
+  using C = AttnCfg<HD>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* sK = smem;
+  uint8_t* sV = sK + C::TILE_BYTES;
+  uint8_t* sQ = sV + C::TILE_BYTES;       // 2 stages
+  uint8_t* sDO = sQ + 2 * C::TILE_BYTES;  // 2 stages
+  uint8_t* sPt = sDO + 2 * C::TILE_BYTES;
+  uint8_t* sDSt = sPt + C::P_BYTES;
+  float* s_lse = reinterpret_cast<float*>(sDSt + C::P_BYTES);  // [2][128]
+  float* s_delta = s_lse + 2 * ATT_BLK;                        // [2][128]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_delta + 2 * ATT_BLK);
+  uint64_t* bar_kv = bars;
+  uint64_t* bar_qdo = bars + 1;  // [2]
+  uint64_t* bar_s = bars + 3;
+  uint64_t* bar_d = bars + 4;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 5);
+
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int jblk = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  const int nblk = T / ATT_BLK;
+  const int kv_row0 = b * T + jblk * ATT_BLK;
+  const long long stat_base = ((long long)b * H + h) * T;
+
+  if (tid == 0) {
+    tma_prefetch_desc(&tm_q);
+    tma_prefetch_desc(&tm_k);
+    tma_prefetch_desc(&tm_v);
+    tma_prefetch_desc(&tm_do);
+    mbar_init(bar_kv, 1);
+    mbar_init(&bar_qdo[0], 1);
+    mbar_init(&bar_qdo[1], 1);
+    mbar_init(bar_s, 1);
+    mbar_init(bar_d, 1);
+    fence_barrier_init();
+  }
+  if (warp == 0) {
+    tmem_alloc(tmem_ptr_smem, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+  const uint32_t tm_st = tmem_base, tm_dpt = tmem_base + 128, tm_dk = tmem_base + 256, tm_dv = tmem_base + 256 + HD,
+                 tm_dq = tmem_base + 256 + 2 * HD;
+  const uint32_t lane_sel = (uint32_t)(warp * 32) << 16;
+
+  if (tid == 0) {
+    mbar_expect_tx(bar_kv, 2 * C::TILE_BYTES);
+    tma_load_2d(sK, &tm_k, bar_kv, h * HD, kv_row0);
+    tma_load_2d(sV, &tm_v, bar_kv, h * HD, kv_row0);
+    mbar_expect_tx(&bar_qdo[0], 2 * C::TILE_BYTES);
+    tma_load_2d(sQ, &tm_q, &bar_qdo[0], h * HD, b * T + jblk * ATT_BLK);
+    tma_load_2d(sDO, &tm_do, &bar_qdo[0], h * HD, b * T + jblk * ATT_BLK);
+  }
+
+  constexpr uint32_t idesc_kk = make_idesc_bf16(128, 128, 0, 0);  // St, dPt : A K-major, B K-major
+  constexpr uint32_t idesc_kn = make_idesc_bf16(128, HD, 0, 1);   // dV, dK  : A K-major (Pt/dSt), B MN-major
+  constexpr uint32_t idesc_nn = make_idesc_bf16(128, HD, 1, 1);   // dQ      : A MN-major (dSt as dS), B MN-major (K)
+
+  int it = 0;
+  for (int i = jblk; i < nblk; ++i, ++it) {
+    const int st = it & 1;
+    // stage the per-row statistics of query block i
+    s_lse[st * ATT_BLK + tid] = lse2[stat_base + i * ATT_BLK + tid];
+    s_delta[st * ATT_BLK + tid] = delta[stat_base + i * ATT_BLK + tid];
+    if (it == 0) mbar_wait(bar_kv, 0);
+    mbar_wait(&bar_qdo[st], (it >> 1) & 1);
+    tc_fence_after();
+    __syncthreads();
+    if (tid == 0) {
+      const uint32_t ak = smem_u32(sK), av = smem_u32(sV), aq = smem_u32(sQ + st * C::TILE_BYTES),
+                     ado = smem_u32(sDO + st * C::TILE_BYTES);
+#pragma unroll
+      for (int k = 0; k < HD / 16; ++k)
+        umma_bf16(tm_st, make_smem_desc(ak + k * 32, 16, C::SBO, C::SWZ), make_smem_desc(aq + k * 32, 16, C::SBO, C::SWZ),
+                  idesc_kk, k > 0);
+#pragma unroll
+      for (int k = 0; k < HD / 16; ++k)
+        umma_bf16(tm_dpt, make_smem_desc(av + k * 32, 16, C::SBO, C::SWZ), make_smem_desc(ado + k * 32, 16, C::SBO, C::SWZ),
+                  idesc_kk, k > 0);
+      umma_commit(bar_s);
+      if (i + 1 < nblk) {  // prefetch Q / dO of the next query block
+        const int ns = st ^ 1;
+        mbar_expect_tx(&bar_qdo[ns], 2 * C::TILE_BYTES);
+        tma_load_2d(sQ + ns * C::TILE_BYTES, &tm_q, &bar_qdo[ns], h * HD, b * T + (i + 1) * ATT_BLK);
+        tma_load_2d(sDO + ns * C::TILE_BYTES, &tm_do, &bar_qdo[ns], h * HD, b * T + (i + 1) * ATT_BLK);
+      }
+    }
+    mbar_wait(bar_s, it & 1);
+    tc_fence_after();
+
+    const bool diag = (i == jblk);
+    const float* lse_i = s_lse + st * ATT_BLK;
+    const float* del_i = s_delta + st * ATT_BLK;
+#pragma unroll 1
+    for (int c = 0; c < 4; ++c) {
+      uint32_t rs[32], rp[32];
+      tmem_ld_32x32b_x32(tm_st + lane_sel + c * 32, rs);
+      tmem_ld_32x32b_x32(tm_dpt + lane_sel + c * 32, rp);
+      tmem_ld_wait();
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        float p[8], ds[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const int q = c * 32 + g * 8 + e;  // query column inside the block; this thread's key row is `tid`
+          const float s = __uint_as_float(rs[g * 8 + e]);
+          const float pv = (!diag || q >= tid) ? exp2f(s * scale_log2 - lse_i[q]) : 0.f;
+          p[e] = pv;
+          ds[e] = pv * (__uint_as_float(rp[g * 8 + e]) - del_i[q]);
+        }
+        const uint32_t off = p_tile_offset(tid, c * 4 + g);
+        *reinterpret_cast<uint4*>(sPt + off) =
+            make_uint4(pack_bf16x2(p[0], p[1]), pack_bf16x2(p[2], p[3]), pack_bf16x2(p[4], p[5]), pack_bf16x2(p[6], p[7]));
+        *reinterpret_cast<uint4*>(sDSt + off) = make_uint4(pack_bf16x2(ds[0], ds[1]), pack_bf16x2(ds[2], ds[3]),
+                                                           pack_bf16x2(ds[4], ds[5]), pack_bf16x2(ds[6], ds[7]));
+      }
+    }
+    fence_proxy_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    if (tid == 0) {
+      tc_fence_after();
+      const uint32_t apt = smem_u32(sPt), adst = smem_u32(sDSt), aq = smem_u32(sQ + st * C::TILE_BYTES),
+                     ado = smem_u32(sDO + st * C::TILE_BYTES), ak = smem_u32(sK);
+      const uint32_t acc = it > 0;
+#pragma unroll
+      for (int k = 0; k < ATT_BLK / 16; ++k) {
+        const uint32_t a_off = (k >> 2) * (ATT_BLK * 128) + (k & 3) * 32;  // K-major walk over the 128 q columns
+        // dV += Pt[kv, q] * dO[q, :]      (B = dO tile consumed MN-major: rows are the reduction index)
+        umma_bf16(tm_dv, make_smem_desc(apt + a_off, 16, 1024, SWZ_128B),
+                  make_smem_desc(ado + k * 16 * C::ROW_BYTES, 16, C::SBO, C::SWZ), idesc_kn, acc | (k > 0));
+      }
+#pragma unroll
+      for (int k = 0; k < ATT_BLK / 16; ++k) {
+        const uint32_t a_off = (k >> 2) * (ATT_BLK * 128) + (k & 3) * 32;
+        // dK += dSt[kv, q] * Q[q, :]
+        umma_bf16(tm_dk, make_smem_desc(adst + a_off, 16, 1024, SWZ_128B),
+                  make_smem_desc(aq + k * 16 * C::ROW_BYTES, 16, C::SBO, C::SWZ), idesc_kn, acc | (k > 0));
+      }
+#pragma unroll
+      for (int k = 0; k < ATT_BLK / 16; ++k) {
+        // dQ = dS[q, kv] * K[kv, :] : the dSt tile read as an MN-major A operand (q contiguous): 64-wide q blocks
+        // are 128*128 B apart (LBO), 8-kv-row groups 1024 B apart (SBO); one K step = 16 kv rows = 2048 B.
+        umma_bf16(tm_dq, make_smem_desc(adst + k * 2048, ATT_BLK * 128, 1024, SWZ_128B),
+                  make_smem_desc(ak + k * 16 * C::ROW_BYTES, 16, C::SBO, C::SWZ), idesc_nn, k > 0);
+      }
+      umma_commit(bar_d);
+    }
+    mbar_wait(bar_d, it & 1);
+    tc_fence_after();
+    {
+      float* dq_row = dq_accum + (long long)(b * T + i * ATT_BLK + tid) * lddq + h * HD;
+#pragma unroll
+      for (int c = 0; c < HD / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(tm_dq + lane_sel + c * 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int e = 0; e < 32; e += 4)
+          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dq_row + c * 32 + e),
+                       "f"(__uint_as_float(r[e]) * scale), "f"(__uint_as_float(r[e + 1]) * scale),
+                       "f"(__uint_as_float(r[e + 2]) * scale), "f"(__uint_as_float(r[e + 3]) * scale)
+                       : "memory");
+      }
+    }
+    tc_fence_before();
+    __syncthreads();
+  }
+
+  // write dK (scaled) and dV for this key block
+  bf16* dk_row = dk + (long long)(kv_row0 + tid) * lddkv + h * HD;
+  bf16* dv_row = dv + (long long)(kv_row0 + tid) * lddkv + h * HD;
+#pragma unroll
+  for (int c = 0; c < HD / 32; ++c) {
+    uint32_t rk[32], rv[32];
+    tmem_ld_32x32b_x32(tm_dk + lane_sel + c * 32, rk);
+    tmem_ld_32x32b_x32(tm_dv + lane_sel + c * 32, rv);
+    tmem_ld_wait();
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      const int e = g * 8;
+      *reinterpret_cast<uint4*>(dk_row + c * 32 + e) = make_uint4(
+          pack_bf16x2(__uint_as_float(rk[e]) * scale, __uint_as_float(rk[e + 1]) * scale),
+          pack_bf16x2(__uint_as_float(rk[e + 2]) * scale, __uint_as_float(rk[e + 3]) * scale),
+          pack_bf16x2(__uint_as_float(rk[e + 4]) * scale, __uint_as_float(rk[e + 5]) * scale),
+          pack_bf16x2(__uint_as_float(rk[e + 6]) * scale, __uint_as_float(rk[e + 7]) * scale));
+      *reinterpret_cast<uint4*>(dv_row + c * 32 + e) =
+          make_uint4(pack_bf16x2(__uint_as_float(rv[e]), __uint_as_float(rv[e + 1])),
+                     pack_bf16x2(__uint_as_float(rv[e + 2]), __uint_as_float(rv[e + 3])),
+                     pack_bf16x2(__uint_as_float(rv[e + 4]), __uint_as_float(rv[e + 5])),
+                     pack_bf16x2(__uint_as_float(rv[e + 6]), __uint_as_float(rv[e + 7])));
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+template <int HD>
+static int attn_tmap(CUtensorMap* m, const void* p, long long rows, int H, long long ld) {
+  return make_tmap_2d_bf16(m, p, rows, (uint64_t)H * HD, ld, ATT_BLK, HD,
+                           HD == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B);
+}
+
+template <int HD>
+static int launch_fwd(const void* q, const void* k, const void* v, long long ld, void* out, long long ldo, float* lse2,
+                      int B, int H, int T, cudaStream_t stream) {
+  using C = AttnCfg<HD>;
+  CUtensorMap tq, tk, tv;
+  int rc;
+  const long long M = (long long)B * T;
+  if ((rc = attn_tmap<HD>(&tq, q, M, H, ld))) return rc;
+  if ((rc = attn_tmap<HD>(&tk, k, M, H, ld))) return rc;
+  if ((rc = attn_tmap<HD>(&tv, v, M, H, ld))) return rc;
+  const int smem = 5 * C::TILE_BYTES + C::P_BYTES + 1024 + 128;
+  auto kern = flash_attn_fwd_kernel<HD>;
+  static bool configured = false;
+  if (!configured) {
+    DTC_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured = true;
+  }
+  const float scale = 1.f / sqrtf((float)HD);
+  dim3 grid(T / ATT_BLK, H, B);
+  kern<<<grid, 128, smem, stream>>>(tq, tk, tv, reinterpret_cast<bf16*>(out), ldo, lse2, T, H, scale * LOG2E);
+  DTC_CHECK_LAUNCH();
+  return 0;
+}
+
+template <int HD>
+static int launch_bwd(const void* q, const void* k, const void* v, long long ld, const void* o, long long ldo,
+                      const void* d_o, long long lddo, const float* lse2, float* delta, float* dq_accum, long long lddq,
+                      void* dk, void* dv, long long lddkv, int B, int H, int T, cudaStream_t stream) {
+  using C = AttnCfg<HD>;
+  CUtensorMap tq, tk, tv, tdo;
+  int rc;
+  const long long M = (long long)B * T;
+  if ((rc = attn_tmap<HD>(&tq, q, M, H, ld))) return rc;
+  if ((rc = attn_tmap<HD>(&tk, k, M, H, ld))) return rc;
+  if ((rc = attn_tmap<HD>(&tv, v, M, H, ld))) return rc;
+  if ((rc = attn_tmap<HD>(&tdo, d_o, M, H, lddo))) return rc;
+  {
+    const long long threads = M * H * (HD / 8);
+    attn_bwd_prep_kernel<HD><<<(int)((threads + 255) / 256), 256, 0, stream>>>(
+        reinterpret_cast<const bf16*>(o), ldo, reinterpret_cast<const bf16*>(d_o), lddo, delta, (int)M, T, H);
+    DTC_CHECK_LAUNCH();
+  }
+  const int smem = 6 * C::TILE_BYTES + 2 * C::P_BYTES + 4 * ATT_BLK * 4 + 1024 + 128;
+  auto kern = flash_attn_bwd_kernel<HD>;
+  static bool configured = false;
+  if (!configured) {
+    DTC_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured = true;
+  }
+  const float scale = 1.f / sqrtf((float)HD);
+  dim3 grid(T / ATT_BLK, H, B);
+  kern<<<grid, 128, smem, stream>>>(tq, tk, tv, tdo, lse2, delta, dq_accum, lddq, reinterpret_cast<bf16*>(dk),
+                                    reinterpret_cast<bf16*>(dv), lddkv, T, H, scale, scale * LOG2E);
+  DTC_CHECK_LAUNCH();
+  return 0;
+}
+
+}  // namespace dtc
+
+using namespace dtc;
+
+// q/k/v: bf16 pointers to the first column of each slice inside a [B*T, ld] buffer; out [B*T, ldo] bf16;
+// lse2 [B,H,T] fp32 (log2-domain log-sum-exp, consumed by the backward).  T % 128 == 0, head_dim 32 or 64.
+extern "C" int dtc_flash_attn_fwd(const void* q, const void* k, const void* v, long long ld, void* out, long long ldo,
+                                  float* lse2, int B, int H, int T, int head_dim, cudaStream_t stream) {
+  DTC_CHECK_ARG(B > 0 && H > 0 && T > 0 && T % ATT_BLK == 0, "flash_attn_fwd: T=%d must be a multiple of %d", T, ATT_BLK);
+  DTC_CHECK_ARG(head_dim == 32 || head_dim == 64, "flash_attn_fwd: head_dim %d not supported (32, 64)", head_dim);
+  DTC_CHECK_ARG(ld % 8 == 0 && ldo % 8 == 0, "flash_attn_fwd: leading dimensions must be multiples of 8");
+  DTC_CHECK_ARG((((uintptr_t)q | (uintptr_t)k | (uintptr_t)v | (uintptr_t)out) & 15) == 0, "flash_attn_fwd: alignment");
+  if (head_dim == 32) return launch_fwd<32>(q, k, v, ld, out, ldo, lse2, B, H, T, stream);
+  return launch_fwd<64>(q, k, v, ld, out, ldo, lse2, B, H, T, stream);
+}
+
+// dq_accum [B*T, lddq] fp32 must be ZERO on entry (partial dQ tiles are reduce-added);
+// dk/dv [B*T, lddkv] bf16 are overwritten; delta [B,H,T] fp32 is scratch written by the prep kernel.
+extern "C" int dtc_flash_attn_bwd(const void* q, const void* k, const void* v, long long ld, const void* o, long long ldo,
+                                  const void* d_o, long long lddo, const float* lse2, float* delta, float* dq_accum,
+                                  long long lddq, void* dk, void* dv, long long lddkv, int B, int H, int T, int head_dim,
+                                  cudaStream_t stream) {
+  DTC_CHECK_ARG(B > 0 && H > 0 && T > 0 && T % ATT_BLK == 0, "flash_attn_bwd: T=%d must be a multiple of %d", T, ATT_BLK);
+  DTC_CHECK_ARG(head_dim == 32 || head_dim == 64, "flash_attn_bwd: head_dim %d not supported (32, 64)", head_dim);
+  DTC_CHECK_ARG(ld % 8 == 0 && ldo % 8 == 0 && lddo % 8 == 0 && lddq % 4 == 0 && lddkv % 8 == 0,
+                "flash_attn_bwd: leading dimension alignment");
+  if (head_dim == 32)
+    return launch_bwd<32>(q, k, v, ld, o, ldo, d_o, lddo, lse2, delta, dq_accum, lddq, dk, dv, lddkv, B, H, T, stream);
+  return launch_bwd<64>(q, k, v, ld, o, ldo, d_o, lddo, lse2, delta, dq_accum, lddq, dk, dv, lddkv, B, H, T, stream);
+}

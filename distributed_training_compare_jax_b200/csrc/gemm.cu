@@ -1,0 +1,331 @@
+// tcgen05 / TMEM / TMA GEMM for sm_100a with fused epilogues.
+//
+//   D[M,N] = A[M,K] * B[N,K]^T      bf16 operands, fp32 accumulation in tensor memory
+//
+// Either operand may be stored K-major (reduction dim contiguous) or MN-major (row dim contiguous),
+// which covers all three GEMMs of a Linear layer without materialising a transpose:
+//   forward   Y  = X  W          A = X  (K-major)   B = W  [K,N] (MN-major)
+//   dgrad     dX = dY W^T        A = dY (K-major)   B = W  [K,N] read as [N_out=K, red=N] (K-major)
+//   wgrad     dW = X^T dY        A = X  [M,K] read as [K, red=M] (MN-major)   B = dY (MN-major)
+// Covers the op sites K5/K7/K8/K9/K10/K11/K16 of SURVEY.md §2.5 (reference: model/CausalSelfAttention.py:18-20,46,
+// model/MLP.py:13-24, model/GPTModel.py:72 and their autodiff transposes).
+//
+// Structure (one 128 x BN output tile per CTA, 192 threads):
+//   warp 0      TMA producer  : cp.async.bulk.tensor -> 128B-swizzled smem ring, mbarrier complete_tx
+//   warp 1      MMA issuer    : one elected lane issues tcgen05.mma (UMMA 128 x BN x 16), tcgen05.commit frees stages
+//   warps 2..5  epilogue      : tcgen05.ld (one accumulator row per thread) -> bias / GELU / residual /
+//                               GELU-backward / fp32 reduce-add (split-K) -> 16-byte global stores
+#include <stdarg.h>
+#include <stdio.h>
+
+#include "common.cuh"
+#include "tma_host.h"
+
+namespace dtc {
+
+constexpr int BM = 128;
+constexpr int BK = 64;  // 64 bf16 = 128 bytes = one swizzle row
+constexpr int MAX_STAGES = 8;
+constexpr int GEMM_THREADS = 192;
+
+enum GemmEpiMode : int {
+  EPI_STORE_BF16 = 0,     // out_bf16 = alpha*acc + bias
+  EPI_BIAS_GELU = 1,      // out_bf16 = acc + bias ; out2_bf16 = gelu_tanh(acc + bias)
+  EPI_BIAS_RESIDUAL = 2,  // out_bf16 = acc + bias + aux
+  EPI_DGELU = 3,          // out_bf16 = acc * gelu_tanh'(aux)
+  EPI_ATOMIC_F32 = 4,     // out_f32 += alpha*acc      (split-K / gradient accumulation)
+  EPI_STORE_F32 = 5,      // out_f32 = alpha*acc + bias
+};
+
+struct GemmEpi {
+  int mode;
+  float alpha;
+  const bf16* bias;  // [N] bf16 (compute copy of the parameter) or null
+  const bf16* aux;
+  long long ld_aux;
+  void* out;
+  long long ldo;
+  bf16* out2;
+  long long ldo2;
+};
+
+template <int BN>
+struct GemmSmem {
+  static constexpr int A_BYTES = BM * BK * 2;
+  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int bytes(int stages) { return stages * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/; }
+};
+
+DTC_DEVICE void red_add_v4_f32(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+template <bool A_MN, bool B_MN, int BN>
+__global__ void __launch_bounds__(GEMM_THREADS)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, int M, int N,
+                    int K, int m_blocks, int kb_per_split, int num_stages, GemmEpi epi) {
+  using S = GemmSmem<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  // 128B swizzle atoms need a 1024-byte aligned base
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + num_stages * S::STAGE_BYTES);
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = bars + MAX_STAGES;
+  uint64_t* tmem_full_bar = bars + 2 * MAX_STAGES;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 2 * MAX_STAGES + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int m_blk = blockIdx.x % m_blocks;  // m fastest: CTAs that share a B tile are adjacent
+  const int n_blk = blockIdx.x / m_blocks;
+  const int total_kb = (K + BK - 1) / BK;
+  const int kb_begin = blockIdx.y * kb_per_split;
+  const int kb_end = min(total_kb, kb_begin + kb_per_split);
+  const int nkb = kb_end - kb_begin;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tma_a);
+    tma_prefetch_desc(&tma_b);
+    for (int s = 0; s < num_stages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(tmem_full_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_ptr_smem, BN);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp == 0) {
+    // ------------------------------ TMA producer ------------------------------
+    if (elect_one()) {
+      for (int i = 0; i < nkb; ++i) {
+        const int s = i % num_stages;
+        const uint32_t ph = (i / num_stages) & 1;
+        mbar_wait(&empty_bar[s], ph ^ 1);
+        uint8_t* sa = smem + s * S::STAGE_BYTES;
+        uint8_t* sb = sa + S::A_BYTES;
+        mbar_expect_tx(&full_bar[s], S::STAGE_BYTES);
+        const int k0 = (kb_begin + i) * BK;
+        if (A_MN) {
+          // global [K, M] (M contiguous): one 64(m) x 64(k) box per 64 rows of the tile
+#pragma unroll
+          for (int j = 0; j < BM / 64; ++j) tma_load_2d(sa + j * (BK * 128), &tma_a, &full_bar[s], m_blk * BM + j * 64, k0);
+        } else {
+          tma_load_2d(sa, &tma_a, &full_bar[s], k0, m_blk * BM);
+        }
+        if (B_MN) {
+#pragma unroll
+          for (int j = 0; j < BN / 64; ++j) tma_load_2d(sb + j * (BK * 128), &tma_b, &full_bar[s], n_blk * BN + j * 64, k0);
+        } else {
+          tma_load_2d(sb, &tma_b, &full_bar[s], k0, n_blk * BN);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------ MMA issuer ------------------------------
+    constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+    // K-major, 128B swizzle: 8-row groups 1024 B apart (SBO); LBO unused (encoded 1).  One UMMA_K=16 step = 32 B.
+    // MN-major, 128B swizzle: 64-element column groups BK*128 B apart (LBO), 8-k groups 1024 B apart (SBO);
+    // one UMMA_K=16 step = 16 rows of 128 B.
+    constexpr uint32_t A_LBO = A_MN ? BK * 128 : 16, A_STEP = A_MN ? 2048 : 32;
+    constexpr uint32_t B_LBO = B_MN ? BK * 128 : 16, B_STEP = B_MN ? 2048 : 32;
+    for (int i = 0; i < nkb; ++i) {
+      const int s = i % num_stages;
+      const uint32_t ph = (i / num_stages) & 1;
+      mbar_wait(&full_bar[s], ph);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t sa = smem_u32(smem + s * S::STAGE_BYTES);
+        const uint32_t sb = sa + S::A_BYTES;
+#pragma unroll
+        for (int k = 0; k < BK / 16; ++k) {
+          const uint64_t da = make_smem_desc(sa + k * A_STEP, A_LBO, 1024, SWZ_128B);
+          const uint64_t db = make_smem_desc(sb + k * B_STEP, B_LBO, 1024, SWZ_128B);
+          umma_bf16(tmem_base, da, db, idesc, (i > 0 || k > 0) ? 1u : 0u);
+        }
+        umma_commit(&empty_bar[s]);                   // frees this smem stage once the MMAs have read it
+        if (i == nkb - 1) umma_commit(tmem_full_bar);  // accumulator complete
+      }
+      __syncwarp();
+    }
+  } else {
+    // ------------------------------ epilogue ------------------------------
+    const int q = warp & 3;  // TMEM lane quadrant this warp may read
+    const int row = q * 32 + lane;
+    const long long gm = (long long)m_blk * BM + row;
+    const bool row_ok = gm < M;
+    if (nkb > 0) {
+      mbar_wait(tmem_full_bar, 0);
+      tc_fence_after();
+    }
+    const int mode = epi.mode;
+    const float alpha = epi.alpha;
+#pragma unroll 1
+    for (int c = 0; c < BN / 32; ++c) {
+      uint32_t r[32];
+      if (nkb > 0) {
+        tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(q * 32) << 16) + c * 32, r);
+        tmem_ld_wait();
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) r[j] = 0;
+      }
+      const int n0 = n_blk * BN + c * 32;
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        const int n = n0 + g * 8;
+        if (!row_ok || n >= N) continue;  // N % 8 == 0, so an 8-group is all in or all out
+        float v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]) * alpha;
+        if (epi.bias != nullptr && mode != EPI_ATOMIC_F32 && mode != EPI_DGELU) {
+          const uint4 bb = *reinterpret_cast<const uint4*>(epi.bias + n);
+          const uint32_t bw[4] = {bb.x, bb.y, bb.z, bb.w};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float2 f = unpack_bf16x2(bw[j]);
+            v[2 * j] += f.x;
+            v[2 * j + 1] += f.y;
+          }
+        }
+        if (mode == EPI_ATOMIC_F32) {
+          float* o = reinterpret_cast<float*>(epi.out) + gm * epi.ldo + n;
+          red_add_v4_f32(o, v[0], v[1], v[2], v[3]);
+          red_add_v4_f32(o + 4, v[4], v[5], v[6], v[7]);
+          continue;
+        }
+        if (mode == EPI_STORE_F32) {
+          float* o = reinterpret_cast<float*>(epi.out) + gm * epi.ldo + n;
+          *reinterpret_cast<float4*>(o) = make_float4(v[0], v[1], v[2], v[3]);
+          *reinterpret_cast<float4*>(o + 4) = make_float4(v[4], v[5], v[6], v[7]);
+          continue;
+        }
+        if (mode == EPI_BIAS_RESIDUAL || mode == EPI_DGELU) {
+          const uint4 a = *reinterpret_cast<const uint4*>(epi.aux + gm * epi.ld_aux + n);
+          const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float2 f = unpack_bf16x2(aw[j]);
+            if (mode == EPI_BIAS_RESIDUAL) {
+              v[2 * j] += f.x;
+              v[2 * j + 1] += f.y;
+            } else {
+              v[2 * j] *= gelu_tanh_grad(f.x);
+              v[2 * j + 1] *= gelu_tanh_grad(f.y);
+            }
+          }
+        }
+        bf16* o = reinterpret_cast<bf16*>(epi.out) + gm * epi.ldo + n;
+        *reinterpret_cast<uint4*>(o) = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]),
+                                                  pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+        if (mode == EPI_BIAS_GELU) {
+          bf16* o2 = epi.out2 + gm * epi.ldo2 + n;
+          *reinterpret_cast<uint4*>(o2) =
+              make_uint4(pack_bf16x2(gelu_tanh(v[0]), gelu_tanh(v[1])), pack_bf16x2(gelu_tanh(v[2]), gelu_tanh(v[3])),
+                         pack_bf16x2(gelu_tanh(v[4]), gelu_tanh(v[5])), pack_bf16x2(gelu_tanh(v[6]), gelu_tanh(v[7])));
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, BN);
+  }
+}
+
+template <bool A_MN, bool B_MN, int BN>
+static int launch_gemm(const void* A, long long lda, const void* B, long long ldb, int M, int N, int K, int splits,
+                       int stages, const GemmEpi& epi, cudaStream_t stream) {
+  using S = GemmSmem<BN>;
+  CUtensorMap ta, tb;
+  int rc;
+  if (A_MN) rc = make_tmap_2d_bf16(&ta, A, K, M, lda, BK, 64, CU_TENSOR_MAP_SWIZZLE_128B);
+  else rc = make_tmap_2d_bf16(&ta, A, M, K, lda, BM, BK, CU_TENSOR_MAP_SWIZZLE_128B);
+  if (rc) return rc;
+  if (B_MN) rc = make_tmap_2d_bf16(&tb, B, K, N, ldb, BK, 64, CU_TENSOR_MAP_SWIZZLE_128B);
+  else rc = make_tmap_2d_bf16(&tb, B, N, K, ldb, BN, BK, CU_TENSOR_MAP_SWIZZLE_128B);
+  if (rc) return rc;
+
+  const int total_kb = (K + BK - 1) / BK;
+  if (splits < 1) splits = 1;
+  if (splits > total_kb) splits = total_kb > 0 ? total_kb : 1;
+  const int kb_per_split = (total_kb + splits - 1) / splits;
+  splits = kb_per_split > 0 ? (total_kb + kb_per_split - 1) / kb_per_split : 1;
+  if (splits < 1) splits = 1;
+  if (stages < 2) stages = 2;
+  if (stages > MAX_STAGES) stages = MAX_STAGES;
+  while (S::bytes(stages) > 227 * 1024) --stages;
+  const int smem_bytes = S::bytes(stages);
+  auto kern = gemm_tcgen05_kernel<A_MN, B_MN, BN>;
+  static int configured_smem = 0;  // per instantiation
+  if (smem_bytes > configured_smem) {
+    DTC_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    configured_smem = 227 * 1024;
+  }
+  const int m_blocks = (M + BM - 1) / BM, n_blocks = (N + BN - 1) / BN;
+  dim3 grid(m_blocks * n_blocks, splits, 1);
+  kern<<<grid, GEMM_THREADS, smem_bytes, stream>>>(ta, tb, M, N, K, m_blocks, kb_per_split, stages, epi);
+  DTC_CHECK_LAUNCH();
+  return 0;
+}
+
+}  // namespace dtc
+
+using namespace dtc;
+
+// C ABI -----------------------------------------------------------------------------------------
+// A: a_mn_major == 0 -> [M, K] row-major (lda elements between rows); == 1 -> [K, M] row-major.
+// B: b_mn_major == 0 -> [N, K] row-major;                             == 1 -> [K, N] row-major.
+// Requirements: all leading dimensions and base pointers 16-byte aligned; N % 8 == 0.
+// block_n: 64 / 128 / 256 (0 = choose); splits > 1 requires epi_mode == EPI_ATOMIC_F32.
+extern "C" int dtc_gemm_bf16(const void* A, long long lda, int a_mn_major, const void* B, long long ldb, int b_mn_major,
+                             int M, int N, int K, int epi_mode, float alpha, const void* bias, const void* aux,
+                             long long ld_aux, void* out, long long ldo, void* out2, long long ldo2, int splits,
+                             int stages, int block_n, cudaStream_t stream) {
+  DTC_CHECK_ARG(M > 0 && N > 0 && K > 0, "gemm: empty problem M=%d N=%d K=%d", M, N, K);
+  DTC_CHECK_ARG(N % 8 == 0, "gemm: N=%d must be a multiple of 8", N);
+  DTC_CHECK_ARG(lda % 8 == 0 && ldb % 8 == 0, "gemm: lda=%lld ldb=%lld must be multiples of 8 elements", lda, ldb);
+  DTC_CHECK_ARG(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0 && ((uintptr_t)out & 15) == 0,
+                "gemm: operand pointers must be 16-byte aligned");
+  DTC_CHECK_ARG(epi_mode >= 0 && epi_mode <= 5, "gemm: bad epilogue mode %d", epi_mode);
+  DTC_CHECK_ARG(splits <= 1 || epi_mode == EPI_ATOMIC_F32, "gemm: split-K needs the fp32 reduce-add epilogue");
+  DTC_CHECK_ARG(!(epi_mode == EPI_BIAS_RESIDUAL || epi_mode == EPI_DGELU) || aux != nullptr, "gemm: aux missing");
+  DTC_CHECK_ARG(epi_mode != EPI_BIAS_GELU || out2 != nullptr, "gemm: out2 missing");
+  DTC_CHECK_ARG(ldo % 8 == 0 && (aux == nullptr || ld_aux % 8 == 0) && (out2 == nullptr || ldo2 % 8 == 0),
+                "gemm: output/aux leading dimensions must be multiples of 8");
+  GemmEpi epi;
+  epi.mode = epi_mode;
+  epi.alpha = alpha;
+  epi.bias = reinterpret_cast<const bf16*>(bias);
+  epi.aux = reinterpret_cast<const bf16*>(aux);
+  epi.ld_aux = ld_aux;
+  epi.out = out;
+  epi.ldo = ldo;
+  epi.out2 = reinterpret_cast<bf16*>(out2);
+  epi.ldo2 = ldo2;
+  if (block_n == 0) block_n = (N <= 64) ? 64 : 128;
+  if (stages == 0) stages = (block_n == 256) ? 4 : (block_n == 128 ? 3 : 4);
+#define DTC_GEMM_DISPATCH(AMN, BMN)                                                                          \
+  switch (block_n) {                                                                                         \
+    case 64: return launch_gemm<AMN, BMN, 64>(A, lda, B, ldb, M, N, K, splits, stages, epi, stream);         \
+    case 128: return launch_gemm<AMN, BMN, 128>(A, lda, B, ldb, M, N, K, splits, stages, epi, stream);       \
+    case 256: return launch_gemm<AMN, BMN, 256>(A, lda, B, ldb, M, N, K, splits, stages, epi, stream);       \
+    default: dtc_set_error("gemm: block_n must be 64, 128 or 256 (got %d)", block_n); return -1;             \
+  }
+  if (!a_mn_major && !b_mn_major) { DTC_GEMM_DISPATCH(false, false) }
+  if (!a_mn_major && b_mn_major) { DTC_GEMM_DISPATCH(false, true) }
+  if (a_mn_major && !b_mn_major) { DTC_GEMM_DISPATCH(true, false) }
+  DTC_GEMM_DISPATCH(true, true)
+#undef DTC_GEMM_DISPATCH
+}

@@ -1,0 +1,85 @@
+// Library-wide runtime helpers: error string, version, device probe, small utility kernels.
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "common.cuh"
+
+static thread_local char g_err[1024] = "";
+
+void dtc_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+extern "C" const char* dtc_last_error() { return g_err; }
+extern "C" int dtc_version() { return 100; }
+
+// Returns the compute capability major*10+minor of the current device (e.g. 100 for B200), or <0.
+extern "C" int dtc_device_arch() {
+  int dev = 0, major = 0, minor = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return -1;
+  if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess) return -1;
+  if (cudaDeviceGetAttribute(&minor, cudaDevAttrComputeCapabilityMinor, dev) != cudaSuccess) return -1;
+  return major * 10 + minor;
+}
+
+namespace dtc {
+
+__global__ void cast_f32_to_bf16_kernel(const float* __restrict__ in, bf16* __restrict__ out, long long n) {
+  long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 8;
+  const long long stride = (long long)gridDim.x * blockDim.x * 8;
+  for (; i + 8 <= n; i += stride) {
+    const float4 a = *reinterpret_cast<const float4*>(in + i);
+    const float4 b = *reinterpret_cast<const float4*>(in + i + 4);
+    *reinterpret_cast<uint4*>(out + i) =
+        make_uint4(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w), pack_bf16x2(b.x, b.y), pack_bf16x2(b.z, b.w));
+  }
+  // tail (n % 8) handled by the thread whose chunk is partial
+  if (i < n && i + 8 > n) {
+    for (long long j = i; j < n; ++j) out[j] = __float2bfloat16(in[j]);
+  }
+}
+
+// dst_bf16[m, dst_col0 + c] = bf16(src_f32[m, c])   (attention-backward dQ accumulator -> dqkv slice)
+__global__ void cast_f32_to_bf16_2d_kernel(const float* __restrict__ in, long long ld_in, bf16* __restrict__ out,
+                                           long long ld_out, int rows, int cols) {
+  const int cpr = cols / 8;
+  long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long total = (long long)rows * cpr;
+  for (; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+    const int r = (int)(idx / cpr), c = (int)(idx % cpr) * 8;
+    const float4 a = *reinterpret_cast<const float4*>(in + r * ld_in + c);
+    const float4 b = *reinterpret_cast<const float4*>(in + r * ld_in + c + 4);
+    *reinterpret_cast<uint4*>(out + r * ld_out + c) =
+        make_uint4(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w), pack_bf16x2(b.x, b.y), pack_bf16x2(b.z, b.w));
+  }
+}
+
+}  // namespace dtc
+
+extern "C" int dtc_cast_f32_to_bf16(const float* in, void* out, long long n, cudaStream_t stream) {
+  DTC_CHECK_ARG(n >= 0, "cast: negative size");
+  if (n == 0) return 0;
+  DTC_CHECK_ARG(((uintptr_t)in & 15) == 0 && ((uintptr_t)out & 15) == 0, "cast: pointers must be 16-byte aligned");
+  long long chunks = (n + 7) / 8;
+  int blocks = (int)((chunks + 255) / 256);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  dtc::cast_f32_to_bf16_kernel<<<blocks, 256, 0, stream>>>(in, reinterpret_cast<bf16*>(out), n);
+  DTC_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int dtc_cast_f32_to_bf16_2d(const float* in, long long ld_in, void* out, long long ld_out, int rows, int cols,
+                                       cudaStream_t stream) {
+  DTC_CHECK_ARG(cols % 8 == 0 && ld_in % 4 == 0 && ld_out % 8 == 0, "cast2d: cols/ld alignment");
+  long long total = (long long)rows * (cols / 8);
+  if (total == 0) return 0;
+  int blocks = (int)((total + 255) / 256);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  dtc::cast_f32_to_bf16_2d_kernel<<<blocks, 256, 0, stream>>>(in, ld_in, reinterpret_cast<bf16*>(out), ld_out, rows, cols);
+  DTC_CHECK_LAUNCH();
+  return 0;
+}

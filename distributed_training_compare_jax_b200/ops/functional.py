@@ -1,0 +1,161 @@
+"""Python front end of the native sm_100a ops (thin, allocation-explicit wrappers around ``native.call``).
+
+Every function takes torch CUDA tensors (bf16 activations / compute weights, fp32 statistics and gradients),
+optionally writes into caller-provided outputs (the step engine passes preallocated buffers so a CUDA graph
+replay never allocates) and enqueues exactly the kernels named in ``include/dtc_b200.h``.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import native
+
+EPI = {"store": 0, "bias_gelu": 1, "bias_residual": 2, "dgelu": 3, "atomic_f32": 4, "store_f32": 5}
+BF16 = torch.bfloat16
+F32 = torch.float32
+
+
+def _check_rowmajor(t: torch.Tensor, name: str) -> None:
+    if t.dim() != 2 or t.stride(1) != 1:
+        raise ValueError(f"{name}: expected a 2-D tensor with unit inner stride, got shape {tuple(t.shape)} "
+                         f"stride {t.stride()}")
+
+
+def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = False, epi: str = "store",
+         alpha: float = 1.0, bias: torch.Tensor | None = None, aux: torch.Tensor | None = None,
+         out: torch.Tensor | None = None, out2: torch.Tensor | None = None, splits: int = 0, stages: int = 0,
+         block_n: int = 0) -> torch.Tensor:
+    """D[M,N] = A·Bᵀ on the tcgen05 GEMM.  ``a`` is [M,K] (or [K,M] when ``a_mn``), ``b`` is [N,K]
+    (or [K,N] when ``b_mn``).  See ``dtc_gemm_bf16`` for the epilogues."""
+    _check_rowmajor(a, "a")
+    _check_rowmajor(b, "b")
+    K, M = (a.shape[0], a.shape[1]) if a_mn else (a.shape[1], a.shape[0])
+    Kb, N = (b.shape[0], b.shape[1]) if b_mn else (b.shape[1], b.shape[0])
+    if K != Kb:
+        raise ValueError(f"gemm: reduction dims differ ({K} vs {Kb})")
+    mode = EPI[epi]
+    if out is None:
+        if mode == 4:
+            raise ValueError("gemm: the fp32 reduce-add epilogue needs a caller-provided accumulator")
+        out = torch.empty((M, N), device=a.device, dtype=F32 if mode == 5 else BF16)
+    _check_rowmajor(out, "out")
+    if mode == 1 and out2 is None:
+        out2 = torch.empty((M, N), device=a.device, dtype=BF16)
+    native.call("dtc_gemm_bf16", a, a.stride(0), int(a_mn), b, b.stride(0), int(b_mn), M, N, K, mode, float(alpha),
+                bias, aux, aux.stride(0) if aux is not None else 0, out, out.stride(0), out2,
+                out2.stride(0) if out2 is not None else 0, splits, stages, block_n)
+    return out if mode != 1 else (out, out2)
+
+
+def layernorm_fwd(x, gamma, beta, eps: float = 1e-6, out=None, mean=None, rstd=None):
+    M, D = x.shape
+    out = torch.empty_like(x) if out is None else out
+    mean = torch.empty(M, device=x.device, dtype=F32) if mean is None else mean
+    rstd = torch.empty(M, device=x.device, dtype=F32) if rstd is None else rstd
+    native.call("dtc_layernorm_fwd", x, gamma, beta, out, mean, rstd, M, D, float(eps))
+    return out, mean, rstd
+
+
+def layernorm_bwd(dy, x, mean, rstd, gamma, dgamma, dbeta, dres=None, out=None):
+    M, D = x.shape
+    out = torch.empty_like(x) if out is None else out
+    native.call("dtc_layernorm_bwd", dy, x, mean, rstd, gamma, dres, out, dgamma, dbeta, M, D)
+    return out
+
+
+def embed_fwd(ids, wte, wpe, T: int, dropout_p: float, seed: int, step_ptr, stream_id: int = 0, row_offset: int = 0,
+              out=None):
+    M = ids.numel()
+    V, D = wte.shape
+    out = torch.empty((M, D), device=wte.device, dtype=BF16) if out is None else out
+    native.call("dtc_embed_fwd", ids, wte, wpe, out, M, T, D, V, float(dropout_p), int(seed), step_ptr, int(stream_id),
+                int(row_offset))
+    return out
+
+
+def embed_bwd(ids, dh, dwte, dwpe, T: int, dropout_p: float, seed: int, step_ptr, stream_id: int = 0,
+              row_offset: int = 0):
+    M = ids.numel()
+    V, D = dwte.shape
+    native.call("dtc_embed_bwd", ids, dh, dwte, dwpe, M, T, D, V, float(dropout_p), int(seed), step_ptr, int(stream_id),
+                int(row_offset))
+
+
+def ce_fwd_bwd(logits, labels, V: int, gscale: float, loss_rows=None):
+    """In place: ``logits`` [M, ld] (bf16) become dlogits; returns the per-row losses (fp32 [M])."""
+    M = logits.shape[0]
+    loss_rows = torch.empty(M, device=logits.device, dtype=F32) if loss_rows is None else loss_rows
+    native.call("dtc_ce_fwd_bwd", logits, logits.stride(0), labels, loss_rows, M, V, float(gscale))
+    return loss_rows
+
+
+def ce_stats(logits, labels, V_local: int, vocab_start: int, stats):
+    native.call("dtc_ce_stats", logits, logits.stride(0), labels, stats, logits.shape[0], V_local, vocab_start)
+    return stats
+
+
+def ce_combine(stats, n_shards: int, M: int, lse, loss_rows):
+    native.call("dtc_ce_combine", stats, n_shards, M, lse, loss_rows)
+
+
+def ce_grad(logits, labels, lse, V_local: int, vocab_start: int, gscale: float):
+    native.call("dtc_ce_grad", logits, logits.stride(0), labels, lse, logits.shape[0], V_local, vocab_start,
+                float(gscale))
+
+
+def reduce_sum(x, scale: float, out, accumulate: bool = False):
+    native.call("dtc_reduce_sum", x, x.numel(), float(scale), out, int(accumulate))
+    return out
+
+
+def flash_attn_fwd(qkv: torch.Tensor, B: int, H: int, T: int, hd: int, out=None, lse2=None):
+    """``qkv`` [B*T, 3*H*hd] bf16 with q | k | v column slices.  Returns (out [B*T, H*hd], lse2 [B,H,T])."""
+    M = B * T
+    Dl = H * hd
+    out = torch.empty((M, Dl), device=qkv.device, dtype=BF16) if out is None else out
+    lse2 = torch.empty((B, H, T), device=qkv.device, dtype=F32) if lse2 is None else lse2
+    q, k, v = qkv[:, :Dl], qkv[:, Dl:2 * Dl], qkv[:, 2 * Dl:]
+    native.call("dtc_flash_attn_fwd", q, k, v, qkv.stride(0), out, out.stride(0), lse2, B, H, T, hd)
+    return out, lse2
+
+
+def flash_attn_bwd(qkv, o, d_o, lse2, B: int, H: int, T: int, hd: int, dqkv=None, dq_accum=None, delta=None):
+    """Returns dqkv [B*T, 3*H*hd] bf16.  ``dq_accum`` (fp32 [B*T, H*hd]) is zeroed here unless provided zeroed."""
+    M, Dl = B * T, H * hd
+    dqkv = torch.empty((M, 3 * Dl), device=qkv.device, dtype=BF16) if dqkv is None else dqkv
+    if dq_accum is None:
+        dq_accum = torch.zeros((M, Dl), device=qkv.device, dtype=F32)
+    else:
+        dq_accum.zero_()
+    delta = torch.empty((B, H, T), device=qkv.device, dtype=F32) if delta is None else delta
+    q, k, v = qkv[:, :Dl], qkv[:, Dl:2 * Dl], qkv[:, 2 * Dl:]
+    dk, dv = dqkv[:, Dl:2 * Dl], dqkv[:, 2 * Dl:]
+    native.call("dtc_flash_attn_bwd", q, k, v, qkv.stride(0), o, o.stride(0), d_o, d_o.stride(0), lse2, delta, dq_accum,
+                dq_accum.stride(0), dk, dv, dqkv.stride(0), B, H, T, hd)
+    native.call("dtc_cast_f32_to_bf16_2d", dq_accum, dq_accum.stride(0), dqkv, dqkv.stride(0), M, Dl)
+    return dqkv
+
+
+def colsum(x, out):
+    native.call("dtc_colsum", x, x.stride(0), x.shape[0], x.shape[1], out)
+    return out
+
+
+def cast_bf16(src_f32, dst_bf16):
+    native.call("dtc_cast_f32_to_bf16", src_f32, dst_bf16, src_f32.numel())
+    return dst_bf16
+
+
+def sumsq_partials(g, partials):
+    native.call("dtc_sumsq_partials", g, g.numel(), partials)
+    return partials
+
+
+def clip_finalize(partials, n_partials: int, grad_scale: float, max_norm: float, scalars, step):
+    native.call("dtc_clip_finalize", partials, n_partials, float(grad_scale), float(max_norm), scalars, step)
+
+
+def adamw(p, m, v, g, p_bf16, scalars, step_ptr, lr, b1, b2, eps, wd, grad_scale: float = 1.0, zero_grad: bool = True,
+          n: int | None = None):
+    native.call("dtc_adamw", p, m, v, g, p_bf16, p.numel() if n is None else n, scalars, step_ptr, float(lr), float(b1),
+                float(b2), float(eps), float(wd), float(grad_scale), int(zero_grad))

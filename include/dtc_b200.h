@@ -1,0 +1,91 @@
+/* C ABI of libdtc_b200.so — the hand-written sm_100a (B200) kernel library of this framework.
+ *
+ * Conventions
+ *  - every function returns 0 on success, a positive cudaError_t on a CUDA failure, a negative value on an
+ *    argument error; dtc_last_error() returns a human-readable message for the calling thread.
+ *  - all pointers are device pointers unless stated otherwise; "bf16" buffers are passed as void*.
+ *  - kernels are enqueued on `stream` and never synchronise, allocate or free device memory, so every
+ *    call can be captured into a CUDA graph.
+ *  - citations "ref: path:line" point at the reference implementation (KT19/distributed-training-compare-jax)
+ *    whose behaviour the op reproduces; SURVEY.md §2.5 ids (K*, X*) name the op site.
+ */
+#ifndef DTC_B200_H_
+#define DTC_B200_H_
+
+#include <cuda_runtime.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- runtime --------------------------------------------------------------------------------------- */
+const char* dtc_last_error(void);
+int dtc_version(void);
+int dtc_device_arch(void); /* compute capability major*10+minor of the current device, <0 on error */
+int dtc_cast_f32_to_bf16(const float* in, void* out, long long n, cudaStream_t stream);
+int dtc_cast_f32_to_bf16_2d(const float* in, long long ld_in, void* out, long long ld_out, int rows, int cols,
+                            cudaStream_t stream);
+
+/* ---- tcgen05 GEMM (K5 K7 K8 K9 K10 K11 K16; ref: model/CausalSelfAttention.py:18-20,46, model/MLP.py:13-24,
+ *      model/GPTModel.py:72) --------------------------------------------------------------------------
+ * D[M,N] = A[M,K] * B[N,K]^T, bf16 operands, fp32 accumulation in tensor memory.
+ *   a_mn_major == 0: A is [M,K] row-major (lda);  == 1: A is [K,M] row-major.
+ *   b_mn_major == 0: B is [N,K] row-major (ldb);  == 1: B is [K,N] row-major.
+ * epi_mode: 0 out_bf16 = alpha*acc + bias          1 out = acc+bias, out2 = gelu_tanh(out)
+ *           2 out_bf16 = acc + bias + aux          3 out_bf16 = acc * gelu_tanh'(aux)
+ *           4 out_f32 += alpha*acc (split-K ok)    5 out_f32 = alpha*acc + bias
+ * bias: bf16 [N] or NULL.  splits/stages/block_n: 0 = library default.  N % 8 == 0, ld* % 8 == 0. */
+int dtc_gemm_bf16(const void* A, long long lda, int a_mn_major, const void* B, long long ldb, int b_mn_major, int M,
+                  int N, int K, int epi_mode, float alpha, const void* bias, const void* aux, long long ld_aux,
+                  void* out, long long ldo, void* out2, long long ldo2, int splits, int stages, int block_n,
+                  cudaStream_t stream);
+
+/* ---- causal flash attention (K3 K6; ref: model/CausalSelfAttention.py:34-42, model/GPTModel.py:50-51) ---- */
+int dtc_flash_attn_fwd(const void* q, const void* k, const void* v, long long ld, void* out, long long ldo,
+                       float* lse2, int B, int H, int T, int head_dim, cudaStream_t stream);
+/* dq_accum (fp32) must be zero on entry; delta [B,H,T] fp32 is scratch. */
+int dtc_flash_attn_bwd(const void* q, const void* k, const void* v, long long ld, const void* o, long long ldo,
+                       const void* d_o, long long lddo, const float* lse2, float* delta, float* dq_accum,
+                       long long lddq, void* dk, void* dv, long long lddkv, int B, int H, int T, int head_dim,
+                       cudaStream_t stream);
+
+/* ---- LayerNorm (K4; ref: model/TransformerBlock.py:16,22, model/GPTModel.py:71) -------------------- */
+int dtc_layernorm_fwd(const void* x, const void* gamma, const void* beta, void* y, float* mean, float* rstd, int M,
+                      int D, float eps, cudaStream_t stream);
+/* dx = (dres ? dres : 0) + LN'(dy); dgamma/dbeta fp32 [D] are accumulated into. */
+int dtc_layernorm_bwd(const void* dy, const void* x, const float* mean, const float* rstd, const void* gamma,
+                      const void* dres, void* dx, float* dgamma, float* dbeta, int M, int D, cudaStream_t stream);
+
+/* ---- embedding + positional + dropout (K1 K2; ref: model/GPTModel.py:30-38) ------------------------ */
+int dtc_embed_fwd(const int* ids, const void* wte, const void* wpe, void* out, int M, int T, int D, int V,
+                  float dropout_p, unsigned long long seed, const int* step_ptr, unsigned int stream_id,
+                  long long row_offset, cudaStream_t stream);
+int dtc_embed_bwd(const int* ids, const void* dh, float* dwte, float* dwpe, int M, int T, int D, int V,
+                  float dropout_p, unsigned long long seed, const int* step_ptr, unsigned int stream_id,
+                  long long row_offset, cudaStream_t stream);
+
+/* ---- softmax cross-entropy (K12 X7; ref: train/create_train_step.py:32-34,148) --------------------- */
+int dtc_ce_fwd_bwd(void* logits, long long ld, const int* labels, float* loss_rows, int M, int V, float gscale,
+                   cudaStream_t stream);
+int dtc_ce_stats(const void* logits, long long ld, const int* labels, float* stats, int M, int V_local,
+                 int vocab_start, cudaStream_t stream);
+int dtc_ce_combine(const float* stats, int n_shards, int M, float* lse, float* loss_rows, cudaStream_t stream);
+int dtc_ce_grad(void* logits, long long ld, const int* labels, const float* lse, int M, int V_local, int vocab_start,
+                float gscale, cudaStream_t stream);
+int dtc_reduce_sum(const float* in, int n, float scale, float* out, int accumulate, cudaStream_t stream);
+
+/* ---- optimizer (K13 K14; ref: train/create_optimizer.py:9-12) -------------------------------------- */
+int dtc_sumsq_num_partials(long long n);
+int dtc_sumsq_partials(const float* g, long long n, float* partials, cudaStream_t stream);
+/* scalars[0] = ||g||*grad_scale, scalars[1] = clip factor; *step += 1 when step != NULL */
+int dtc_clip_finalize(const float* partials, int n_partials, float grad_scale, float max_norm, float* scalars,
+                      int* step, cudaStream_t stream);
+int dtc_adamw(float* p, float* m, float* v, float* g, void* p_bf16, long long n, const float* scalars,
+              const int* step_ptr, float lr, float b1, float b2, float eps, float wd, float grad_scale, int zero_grad,
+              cudaStream_t stream);
+int dtc_colsum(const void* x, long long ld, int M, int N, float* out, cudaStream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DTC_B200_H_ */
