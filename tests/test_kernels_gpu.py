@@ -131,13 +131,15 @@ def test_layernorm_fwd_bwd(M, D):
 def test_embed_fwd_bwd_dropout_mask_consistency():
     B, T, D, V, p = 4, 128, 512, 1000, 0.1
     ids = torch.randint(0, V, (B * T,), device="cuda", dtype=torch.int32)
-    wte, wpe = randn(V, D), randn(T, D)
+    # strictly positive tables: wte[x] + wpe[t] is never exactly 0, so `h != 0` identifies the kept elements
+    wte = (1 + torch.rand(V, D, device="cuda")).to(BF16)
+    wpe = (1 + torch.rand(T, D, device="cuda")).to(BF16)
     step = torch.tensor([3], device="cuda", dtype=torch.int32)
     h0 = Fn.embed_fwd(ids, wte, wpe, T, 0.0, 7, step)
     want = wte.float()[ids.long()] + wpe.float().repeat(B, 1)
     assert rel_err(h0, want) < 1e-2
     h = Fn.embed_fwd(ids, wte, wpe, T, p, 7, step)
-    keep = (h != 0) | (want == 0)
+    keep = h != 0
     frac = 1.0 - keep.float().mean().item()
     assert abs(frac - p) < 0.01
     assert rel_err(h, torch.where(keep, want / (1 - p), torch.zeros_like(want))) < 1e-2
@@ -170,7 +172,7 @@ def test_cross_entropy_fused(M, V, ld):
 
 
 def test_cross_entropy_vocab_parallel_matches_fused():
-    M, V, n = 48, 1000, 4
+    M, V, n = 48, 1024, 4
     Vl = V // n
     full = randn(M, V, scale=3.0)
     labels = torch.randint(0, V, (M,), device="cuda", dtype=torch.int32)
