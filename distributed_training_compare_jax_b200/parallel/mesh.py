@@ -1,0 +1,146 @@
+"""Explicit device-mesh runtime (components C8/§2.4/§5.9; reference: the implicit 1-D ``Mesh(("data",))`` of
+train/train.py:29 and the ``pmap`` axis "pipe" of train/create_train_step.py:70).
+
+One process per GPU.  A :class:`DeviceMesh` factors the world into (pp, dp, tp) axes — tensor-parallel ranks
+are adjacent (fastest varying) so that TP traffic stays inside one NVSwitch domain even on multi-node jobs —
+and owns one ``torch.distributed`` process group per axis: NCCL on GPUs (bootstrap, PP send/recv, baseline
+collectives), gloo on CPU (plumbing tests).  The fused compute+collective kernels attach symmetric-memory
+arenas to these groups (``parallel/symm.py``).
+
+Axis names: the reference calls its only axis ``"data"`` even for TP (quirk Q11); ``axis("data")`` therefore
+resolves to the single non-trivial axis of a 1-D mesh, and ``"model"`` / ``"pipe"`` name the TP / PP axes.
+"""
+from __future__ import annotations
+
+import datetime
+import os
+from dataclasses import dataclass, field
+
+import torch
+import torch.distributed as dist
+
+
+@dataclass
+class Axis:
+    name: str
+    size: int = 1
+    rank: int = 0
+    group: object | None = None
+    ranks: list[int] = field(default_factory=lambda: [0])
+
+    def all_reduce(self, t: torch.Tensor, op=None) -> torch.Tensor:
+        if self.size > 1:
+            dist.all_reduce(t, op=op or dist.ReduceOp.SUM, group=self.group)
+        return t
+
+    def all_gather_into(self, out: torch.Tensor, t: torch.Tensor) -> torch.Tensor:
+        if self.size > 1:
+            dist.all_gather_into_tensor(out, t, group=self.group)
+        else:
+            out.copy_(t.reshape(out.shape))
+        return out
+
+    def broadcast(self, t: torch.Tensor, src_index: int) -> torch.Tensor:
+        if self.size > 1:
+            dist.broadcast(t, src=self.ranks[src_index], group=self.group)
+        return t
+
+
+@dataclass
+class DeviceMesh:
+    world_size: int
+    rank: int
+    device: torch.device
+    dp: Axis
+    tp: Axis
+    pp: Axis
+    backend: str = "none"
+
+    def axis(self, name: str) -> Axis:
+        if name in ("model", "tp"):
+            return self.tp
+        if name in ("pipe", "pp"):
+            return self.pp
+        if name == "dp":
+            return self.dp
+        if name == "data":  # reference naming: the single axis of a 1-D mesh
+            for a in (self.tp, self.pp):
+                if a.size > 1 and self.dp.size == 1:
+                    return a
+            return self.dp
+        raise KeyError(name)
+
+    @property
+    def is_main(self) -> bool:
+        return self.rank == 0
+
+    def barrier(self) -> None:
+        if self.world_size > 1:
+            dist.barrier()
+
+    def max_over_ranks(self, value: float) -> float:
+        if self.world_size == 1:
+            return value
+        t = torch.tensor([value], dtype=torch.float64, device=self.device if self.backend == "nccl" else "cpu")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+
+def init_distributed(device_type: str | None = None, timeout_s: int = 600) -> tuple[int, int, torch.device, str]:
+    """Initialise torch.distributed from the torchrun / spawn environment.  Returns (rank, world, device, backend)."""
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", str(rank)))
+    use_cuda = torch.cuda.is_available() if device_type is None else device_type == "cuda"
+    if use_cuda:
+        torch.cuda.set_device(local_rank % torch.cuda.device_count())
+        device = torch.device("cuda", torch.cuda.current_device())
+    else:
+        device = torch.device("cpu")
+    backend = "none"
+    if world > 1:
+        backend = "nccl" if use_cuda else "gloo"
+        if not dist.is_initialized():
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            os.environ.setdefault("MASTER_PORT", "29512")
+            kw = {"device_id": device} if use_cuda else {}
+            dist.init_process_group(backend, rank=rank, world_size=world,
+                                    timeout=datetime.timedelta(seconds=timeout_s), **kw)
+    return rank, world, device, backend
+
+
+def build_mesh(dp: int, tp: int, pp: int, device_type: str | None = None) -> DeviceMesh:
+    """Create the (pp, dp, tp) mesh; rank = (pp_idx * dp + dp_idx) * tp + tp_idx."""
+    rank, world, device, backend = init_distributed(device_type)
+    if dp * tp * pp != world:
+        raise ValueError(f"mesh {pp}x{dp}x{tp} (pp x dp x tp) does not match world size {world}")
+    tp_idx, dp_idx, pp_idx = rank % tp, (rank // tp) % dp, rank // (tp * dp)
+
+    def make(name: str, size: int, my_index: int, groups: list[list[int]]) -> Axis:
+        mine, my_ranks = None, [rank]
+        for ranks in groups:  # every rank must create every group (collective call)
+            g = dist.new_group(ranks) if (world > 1 and size > 1) else None
+            if rank in ranks:
+                mine, my_ranks = g, ranks
+        return Axis(name, size, my_index, mine, my_ranks)
+
+    tp_groups = [[(p * dp + d) * tp + t for t in range(tp)] for p in range(pp) for d in range(dp)]
+    dp_groups = [[(p * dp + d) * tp + t for d in range(dp)] for p in range(pp) for t in range(tp)]
+    pp_groups = [[(p * dp + d) * tp + t for p in range(pp)] for d in range(dp) for t in range(tp)]
+    return DeviceMesh(world, rank, device, make("dp", dp, dp_idx, dp_groups), make("tp", tp, tp_idx, tp_groups),
+                      make("pp", pp, pp_idx, pp_groups), backend)
+
+
+def single_device_mesh(device: torch.device | str | None = None) -> DeviceMesh:
+    if device is None:
+        device = torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available() else torch.device("cpu")
+    return DeviceMesh(1, 0, torch.device(device), Axis("dp"), Axis("tp"), Axis("pp"))
+
+
+def shutdown() -> None:
+    if dist.is_available() and dist.is_initialized():
+        try:
+            dist.barrier()
+        except Exception:
+            pass
+        dist.destroy_process_group()

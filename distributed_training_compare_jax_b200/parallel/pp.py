@@ -1,0 +1,124 @@
+"""Pipeline parallelism: schedules + point-to-point executor (components C11-PP / R12; reference:
+train/create_train_step.py:55-195 — a GPipe clock loop of ``M + S − 1`` ticks with ``ppermute`` of
+(h, y, valid) every tick, and train/train.py:107-233 for the stage layout).
+
+What is kept: one stage per rank, contiguous layers per stage, GPipe (all forwards, then all backwards) as the
+default schedule, the loss of the last stage made visible on every stage (reference ``psum``, X12).
+What is dropped on purpose: labels and validity flags do not travel with the activations
+(every stage gets the batch from its own loader; validity is static in the schedule) and nothing is sent on
+bubble ticks.  Added: the 1F1B schedule (at most S − stage microbatches in flight).
+
+Transfers stay on NCCL send/recv (``torch.distributed`` P2P; gloo on CPU).  A send produced by one action
+and the receive needed by the next are issued as ONE batched P2P group, which is what makes the
+bidirectional steady state of 1F1B deadlock-free.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+import torch
+import torch.distributed as dist
+
+
+@dataclass(frozen=True)
+class Action:
+    kind: str  # "F" or "B"
+    mb: int
+
+
+def stage_layers(n_layers: int, n_stages: int, reference_truncate: bool = False) -> list[range]:
+    """Contiguous layer ranges per stage.  ``reference_truncate`` reproduces the reference's
+    ``layers_per_stage = n_layers // n_stages`` (train/train.py:118), which silently drops the remainder
+    (12 layers on 8 stages → an 8-layer model, quirk Q2); the default spreads all layers (e.g. 2,2,2,2,1,1,1,1)."""
+    if reference_truncate:
+        per = n_layers // n_stages
+        return [range(s * per, (s + 1) * per) for s in range(n_stages)]
+    base, extra = divmod(n_layers, n_stages)
+    out, start = [], 0
+    for s in range(n_stages):
+        n = base + (1 if s < extra else 0)
+        out.append(range(start, start + n))
+        start += n
+    return out
+
+
+def build_schedule(kind: str, n_stages: int, stage: int, n_micro: int) -> list[Action]:
+    """Per-stage action list.  gpipe: F0..F(M-1), B(M-1)..B0 (backward in reverse microbatch order, as the
+    autodiff of the reference's forward scan does).  1f1b: S-1-stage warm-up forwards, then alternate."""
+    if kind == "gpipe":
+        return [Action("F", m) for m in range(n_micro)] + [Action("B", m) for m in reversed(range(n_micro))]
+    if kind == "1f1b":
+        warm = min(n_stages - 1 - stage, n_micro)
+        acts = [Action("F", m) for m in range(warm)]
+        f, b = warm, 0
+        while b < n_micro:
+            if f < n_micro:
+                acts.append(Action("F", f))
+                f += 1
+            acts.append(Action("B", b))
+            b += 1
+        return acts
+    raise ValueError(f"unknown pipeline schedule `{kind}`")
+
+
+def bubble_fraction(n_stages: int, n_micro: int) -> float:
+    """(S−1)/(M+S−1): idle share of a GPipe / 1F1B pipeline with equal stage times."""
+    return (n_stages - 1) / (n_micro + n_stages - 1)
+
+
+def max_in_flight(actions: list[Action]) -> int:
+    live = peak = 0
+    for a in actions:
+        live += 1 if a.kind == "F" else -1
+        peak = max(peak, live)
+    return peak
+
+
+class P2PBackend:
+    """torch.distributed point-to-point over the PP axis (NCCL on GPU, gloo on CPU)."""
+
+    def __init__(self, axis):
+        self.axis = axis
+
+    def exchange(self, sends: list[tuple[torch.Tensor, int]], recvs: list[tuple[torch.Tensor, int]]) -> None:
+        """sends / recvs: (tensor, stage index of the peer).  All issued as one batched group, then waited."""
+        ops = [dist.P2POp(dist.isend, t, self.axis.ranks[peer], group=self.axis.group) for t, peer in sends]
+        ops += [dist.P2POp(dist.irecv, t, self.axis.ranks[peer], group=self.axis.group) for t, peer in recvs]
+        if ops:
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()
+
+
+class PipelineExecutor:
+    """Walks a stage's action list, moving activations (forward) and activation gradients (backward)."""
+
+    def __init__(self, engine, axis, schedule: str, p2p=None):
+        self.engine, self.axis = engine, axis
+        self.stage, self.n_stages = axis.rank, axis.size
+        self.actions = build_schedule(schedule, self.n_stages, self.stage, engine.n_micro)
+        self.p2p = p2p or P2PBackend(axis)
+        self.trace: list[tuple[str, int]] = []  # (event, mb) — used by the schedule tests
+
+    def run(self) -> None:
+        eng, first, last = self.engine, self.stage == 0, self.stage == self.n_stages - 1
+        pending_sends: list[tuple[torch.Tensor, int]] = []
+        for a in self.actions:
+            recvs: list[tuple[torch.Tensor, int]] = []
+            if a.kind == "F" and not first:
+                recvs.append((eng.input_buffer(a.mb), self.stage - 1))
+            if a.kind == "B" and not last:
+                recvs.append((eng.grad_input_buffer(a.mb), self.stage + 1))
+            if pending_sends or recvs:
+                self.p2p.exchange(pending_sends, recvs)
+                pending_sends = []
+            self.trace.append((a.kind, a.mb))
+            if a.kind == "F":
+                out = eng.forward(a.mb)
+                if not last:
+                    pending_sends.append((out, self.stage + 1))
+            else:
+                gin = eng.backward(a.mb)
+                if not first:
+                    pending_sends.append((gin.contiguous(), self.stage - 1))
+        if pending_sends:
+            self.p2p.exchange(pending_sends, [])

@@ -1,0 +1,241 @@
+"""Stage engines: run forward / backward of the locally owned slice of the model for one microbatch.
+
+Two interchangeable implementations behind the same interface (``set_batch`` / ``forward`` / ``backward``):
+
+* :class:`NativeStageEngine` — the product path on B200: explicit (autograd-free) forward and backward over
+  preallocated workspaces, every op a hand-written sm_100a kernel from ``libdtc_b200.so``; nothing is
+  allocated after construction, so a whole training step can be captured into one CUDA graph.
+* :class:`TorchStageEngine` — fp32 PyTorch autograd over the same parameter store (oracle T0, CPU / gloo
+  plumbing path, and the "library kernels only" stand-in baseline when run on CUDA).
+
+The strategies compose them: DP = one stage + gradient reduction, TP = collectives inside the stage,
+PP = one stage per rank driven by a schedule (``parallel/pp.py``).  Replaces the reference's jitted
+``value_and_grad(loss_fn)`` (train/create_train_step.py:28-50) and the per-tick body of the pmapped pipeline
+step (train/create_train_step.py:90-168).
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from ..config.schema import ModelConfig
+from ..models.GPTModel import GPTModel
+from ..models.param_tree import LocalShape, ParamStore
+from ..ops import functional as Fn
+from ..parallel.mesh import DeviceMesh
+
+BF16, F32, I32 = torch.bfloat16, torch.float32, torch.int32
+
+
+class Workspace:
+    """Activations saved for the backward pass + scratch, for one microbatch of ``B x T`` tokens."""
+
+    def __init__(self, cfg: ModelConfig, local: LocalShape, B: int, T: int, device, tp_size: int, stream_id: int = 0):
+        self.B, self.T, self.M = B, T, B * T
+        self.stream_id, self.row_offset = stream_id, 0
+        M, D, L = self.M, cfg.d_model, local.L
+        Dl, Fl, Hl, Vl = local.d_local, local.ff_local, local.heads_local, local.vocab_local
+
+        def e(*shape, dtype=BF16):
+            return torch.empty(shape, device=device, dtype=dtype)
+
+        self.ids = torch.zeros(M, device=device, dtype=I32)
+        self.labels = torch.zeros(M, device=device, dtype=I32)
+        self.h = [e(M, D) for _ in range(L + 1)]
+        self.ln1, self.ln2 = e(L, M, D), e(L, M, D)
+        self.mean1, self.rstd1 = e(L, M, dtype=F32), e(L, M, dtype=F32)
+        self.mean2, self.rstd2 = e(L, M, dtype=F32), e(L, M, dtype=F32)
+        self.qkv, self.attn = e(L, M, 3 * Dl), e(L, M, Dl)
+        self.lse2 = e(L, B, Hl, T, dtype=F32)
+        self.hmid = e(L, M, D)
+        self.f1, self.g = e(L, M, Fl), e(L, M, Fl)
+        # backward scratch (shared by all layers)
+        self.dh_a, self.dh_b, self.dh_mid, self.dln = e(M, D), e(M, D), e(M, D), e(M, D)
+        self.dqkv, self.dattn, self.df1 = e(M, 3 * Dl), e(M, Dl), e(M, Fl)
+        self.dq_accum, self.delta = e(M, Dl, dtype=F32), e(B, Hl, T, dtype=F32)
+        self.dh0 = None  # buffer holding dL/dh[0] after backward (set by the engine)
+        if local.has_head:
+            self.lnf, self.meanf, self.rstdf = e(M, D), e(M, dtype=F32), e(M, dtype=F32)
+            self.logits = e(M, Vl)
+            self.loss_rows, self.lse = e(M, dtype=F32), e(M, dtype=F32)
+            if tp_size > 1:
+                self.ce_stats_local, self.ce_stats_all = e(M, 3, dtype=F32), e(tp_size, M, 3, dtype=F32)
+
+
+class StageEngineBase:
+    backend = "base"
+
+    def __init__(self, cfg: ModelConfig, local: LocalShape, mesh: DeviceMesh, store: ParamStore, micro_batch: int,
+                 seq_len: int, n_micro: int, global_tokens: int, seed: int):
+        self.cfg, self.local, self.mesh, self.store = cfg, local, mesh, store
+        self.micro_batch, self.seq_len, self.n_micro = micro_batch, seq_len, n_micro
+        self.global_tokens = global_tokens  # tokens the mean loss is taken over (all DP ranks, all microbatches)
+        self.seed = seed
+        self.model = GPTModel(cfg, local, mesh)
+        self.device = store.device
+        self.loss_sum = torch.zeros(1, device=self.device, dtype=F32)  # sum over local rows / global_tokens
+
+    # hooks used by the data-parallel engine to overlap gradient reduction with the backward pass
+    def on_layer_grads_ready(self, l: int) -> None:
+        pass
+
+    def on_head_grads_ready(self) -> None:
+        pass
+
+    def begin_step(self) -> None:
+        self.loss_sum.zero_()
+
+
+class NativeStageEngine(StageEngineBase):
+    backend = "native"
+
+    def __init__(self, *a, wgrad_splits: int = 0, **kw):
+        super().__init__(*a, **kw)
+        if self.device.type != "cuda":
+            raise RuntimeError("the native engine needs a CUDA device (sm_100a)")
+        if self.seq_len % 128:
+            raise ValueError("native flash attention needs seq_len % 128 == 0")
+        self.c, self.g = self.store.c, self.store.g
+        M = self.micro_batch * self.seq_len
+        # split-K factor for the wgrad GEMMs (reduction over tokens): aim for >= 4 k-blocks of 64 per split
+        self.wgrad_splits = wgrad_splits or max(1, min(8, M // 512))
+        dp = self.mesh.dp
+        self.ws = []
+        for i in range(self.n_micro):
+            w = Workspace(self.cfg, self.local, self.micro_batch, self.seq_len, self.device, self.mesh.tp.size,
+                          stream_id=0)
+            # global row index of local row 0: distinct dropout masks per DP rank / microbatch, identical across TP
+            w.row_offset = (dp.rank * self.n_micro + i) * M
+            self.ws.append(w)
+        self.tp_hooks = None  # set by parallel/tp.py when the fused GEMM+collective kernels are enabled
+
+    # ---- building block shared by attention-out and fc2 (row-parallel Linear + bias + residual) ----
+    def row_parallel_out(self, x, w, bias, residual, out) -> None:
+        tp = self.mesh.tp
+        if self.tp_hooks is not None:
+            self.tp_hooks.row_parallel_out(self, x, w, bias, residual, out)
+            return
+        if tp.size == 1 or tp.rank == 0:
+            Fn.gemm(x, w, b_mn=True, bias=bias, epi="bias_residual", aux=residual, out=out)
+        else:
+            Fn.gemm(x, w, b_mn=True, out=out)
+        tp.all_reduce(out)
+
+    def set_batch(self, mb: int, x: torch.Tensor | None, y: torch.Tensor | None) -> None:
+        """x, y: int32 [micro_batch, T] (device or pinned host); copied into the static workspace buffers."""
+        ws = self.ws[mb]
+        if x is not None and self.local.has_embed:
+            ws.ids.copy_(x.reshape(-1), non_blocking=True)
+        if y is not None and self.local.has_head:
+            ws.labels.copy_(y.reshape(-1), non_blocking=True)
+
+    def input_buffer(self, mb: int) -> torch.Tensor:
+        return self.ws[mb].h[0]
+
+    def forward(self, mb: int) -> torch.Tensor | None:
+        """Runs embed (first stage) + local layers (+ head, loss and head backward on the last stage).
+        Returns the activation buffer to send downstream, or None on the last stage."""
+        ws = self.ws[mb]
+        if self.local.has_embed:
+            self.model.native_embed_forward(self, ws)
+        self.model.native_stage_forward(self, ws)
+        if not self.local.has_head:
+            return ws.h[self.local.L]
+        ws.dh_top = self.model.native_head_forward_backward(self, ws, 1.0 / self.global_tokens)
+        Fn.reduce_sum(ws.loss_rows, 1.0 / self.global_tokens, self.loss_sum, accumulate=True)
+        return None
+
+    def grad_input_buffer(self, mb: int) -> torch.Tensor:
+        """Where an upstream gradient (dL/dh[L]) must be placed on a non-last stage."""
+        return self.ws[mb].dh_b
+
+    def backward(self, mb: int) -> torch.Tensor | None:
+        ws = self.ws[mb]
+        top = ws.dh_top if self.local.has_head else ws.dh_b
+        dh0 = self.model.native_stage_backward(self, ws, top)
+        if self.local.has_embed:
+            self.model.native_embed_backward(self, ws, dh0)
+            return None
+        return dh0
+
+
+class TorchStageEngine(StageEngineBase):
+    """fp32 autograd engine over the same ParamStore (CPU oracle / gloo path / cuBLAS stand-in baseline)."""
+    backend = "torch"
+
+    def __init__(self, *a, **kw):
+        super().__init__(*a, **kw)
+        self.params = {}
+        for name in self.store.names():
+            p = self.store.p[name]
+            p.requires_grad_(True)
+            p.grad = self.store.g[name]
+            self.params[name] = p
+        self._x = [None] * self.n_micro
+        self._y = [None] * self.n_micro
+        self._in = [None] * self.n_micro
+        self._out = [None] * self.n_micro
+        self._loss = [None] * self.n_micro
+        self._gin = [None] * self.n_micro
+        self._step_count = 0
+
+    def set_batch(self, mb, x, y) -> None:
+        if x is not None:
+            self._x[mb] = torch.as_tensor(np.asarray(x) if not torch.is_tensor(x) else x).to(self.device).long()
+        if y is not None:
+            self._y[mb] = torch.as_tensor(np.asarray(y) if not torch.is_tensor(y) else y).to(self.device).long()
+
+    def begin_step(self) -> None:
+        super().begin_step()
+        self._step_count += 1
+
+    def input_buffer(self, mb):
+        if self._in[mb] is None:
+            self._in[mb] = torch.zeros(self.micro_batch, self.seq_len, self.cfg.d_model, device=self.device)
+        return self._in[mb]
+
+    def forward(self, mb):
+        m, p = self.model, self.params
+        T = self.seq_len
+        if self.local.has_embed:
+            gen = torch.Generator(device=self.device)
+            gen.manual_seed(self.seed * 7919 + (self._step_count * 64 + self.mesh.dp.rank) * 64 + mb)
+            h, mask = m.embed_forward(p, self._x[mb], gen)
+        else:
+            h = self.input_buffer(mb).detach().requires_grad_(True)
+            self._in[mb] = h
+            mask = torch.where(torch.tril(torch.ones(T, T, device=self.device)) == 1, 0.0, -1e9)[None, None]
+        h = m.stage_forward(p, h, mask)
+        if not self.local.has_head:
+            self._out[mb] = h
+            return h.detach()
+        logits = m.head_forward(p, h)
+        rows = m.loss_rows(p, logits, self._y[mb])
+        self._loss[mb] = rows.sum() / self.global_tokens
+        self.loss_sum += self._loss[mb].detach()
+        return None
+
+    def grad_input_buffer(self, mb):
+        if self._gin[mb] is None:
+            self._gin[mb] = torch.zeros(self.micro_batch, self.seq_len, self.cfg.d_model, device=self.device)
+        return self._gin[mb]
+
+    def backward(self, mb):
+        if self.local.has_head:
+            self._loss[mb].backward()
+        else:
+            self._out[mb].backward(self.grad_input_buffer(mb))
+        self._loss[mb], self._out[mb] = None, None
+        if self.local.has_embed:
+            return None
+        g = self._in[mb].grad
+        return g
+
+
+def make_engine(backend: str, *args, **kw) -> StageEngineBase:
+    if backend == "native":
+        return NativeStageEngine(*args, **kw)
+    if backend == "torch":
+        kw.pop("wgrad_splits", None)
+        return TorchStageEngine(*args, **kw)
+    raise ValueError(f"unknown backend {backend}")
