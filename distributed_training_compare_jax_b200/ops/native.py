@@ -103,6 +103,12 @@ def launches() -> int:
     return _LAUNCHES
 
 
+def add_launches(n: int) -> None:
+    """Account for kernels launched by a CUDA-graph replay (counted once while the graph was captured)."""
+    global _LAUNCHES
+    _LAUNCHES += n
+
+
 def sumsq_num_partials(n: int) -> int:
     return int(load().dtc_sumsq_num_partials(n))
 

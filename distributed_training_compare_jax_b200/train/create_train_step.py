@@ -19,6 +19,7 @@ from typing import Any
 
 import torch
 
+from ..ops import native
 from ..parallel.pp import PipelineExecutor
 
 
@@ -78,6 +79,7 @@ class _GraphedBody:
     def __init__(self, body, enabled: bool, eager_iters: int = 2):
         self.body, self.enabled, self.eager_left = body, enabled, eager_iters
         self.graph = None
+        self.launches_per_replay = 0
 
     def __call__(self) -> None:
         if not self.enabled:
@@ -85,6 +87,7 @@ class _GraphedBody:
             return
         if self.graph is not None:
             self.graph.replay()
+            native.add_launches(self.launches_per_replay)
             return
         if self.eager_left > 0:
             self.eager_left -= 1
@@ -92,10 +95,14 @@ class _GraphedBody:
             return
         torch.cuda.synchronize()
         g = torch.cuda.CUDAGraph()
+        before = native.launches()
         with torch.cuda.graph(g):
             self.body()
+        self.launches_per_replay = native.launches() - before  # captured, not executed
+        native.add_launches(-self.launches_per_replay)
         self.graph = g
         g.replay()
+        native.add_launches(self.launches_per_replay)
 
 
 def create_train_step(parallel: str = "dp", cuda_graph: bool = True) -> Any:
