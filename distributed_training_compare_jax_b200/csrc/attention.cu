@@ -543,3 +543,69 @@ extern "C" int dtc_flash_attn_bwd(const void* q, const void* k, const void* v, l
     return launch_bwd<32>(q, k, v, ld, o, ldo, d_o, lddo, lse2, delta, dq_accum, lddq, dk, dv, lddkv, B, H, T, stream);
   return launch_bwd<64>(q, k, v, ld, o, ldo, d_o, lddo, lse2, delta, dq_accum, lddq, dk, dv, lddkv, B, H, T, stream);
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// Allocation-free attention backward.
+//
+// dtc_flash_attn_bwd needs a [B,H,T] fp32 scratch buffer (`delta`) that the caller has to allocate.  Some
+// callers cannot do that: plugins and custom calls hosted by a runtime that owns every device allocation and
+// forbids cudaMalloc from foreign code, step loops that cannot afford the device-wide synchronisation a
+// cudaMalloc / cudaFree implies, and jobs whose device-memory budget is fixed before training starts.  For them
+// this variant keeps the scratch in a fixed array that is part of the library image.  Every GPU that loads the library holds these
+// DTC_ATTN_STATIC_DELTA_MAX * 4 bytes (1 MiB) from load until the process exits.
+//
+// The array name below is only meaningful to device code; on the host it is a stand-in symbol, not a device
+// address.  The host therefore asks the runtime for the real address (cudaGetSymbolAddress) once per device,
+// with that device current, and hands that pointer to the kernels.
+// ---------------------------------------------------------------------------------------------------------
+#define DTC_ATTN_STATIC_DELTA_MAX (1 << 18) /* floats: B*H*T may not exceed this (reference config uses 65536) */
+#define DTC_MAX_DEVICES 64
+
+static __device__ __align__(256) float g_attn_delta_scratch[DTC_ATTN_STATIC_DELTA_MAX];
+static float* g_attn_delta_devptr[DTC_MAX_DEVICES];  // per-device resolved address, filled on first use
+
+static int attn_static_delta_ptr(float** out) {
+  int dev = -1;
+  DTC_CHECK_CUDA(cudaGetDevice(&dev));
+  DTC_CHECK_ARG(dev >= 0 && dev < DTC_MAX_DEVICES, "flash_attn_bwd_static: device index %d out of range", dev);
+  if (g_attn_delta_devptr[dev] == nullptr) {
+    void* p = nullptr;
+    DTC_CHECK_CUDA(cudaGetSymbolAddress(&p, g_attn_delta_scratch));
+    DTC_CHECK_ARG(p != nullptr, "flash_attn_bwd_static: cudaGetSymbolAddress returned a null address");
+    g_attn_delta_devptr[dev] = static_cast<float*>(p);
+  }
+  *out = g_attn_delta_devptr[dev];
+  return 0;
+}
+
+// Same contract as dtc_flash_attn_bwd (dq_accum fp32 must be zero on entry and receives dQ; dk / dv are
+// overwritten) except that no scratch pointer is passed: the per-row delta = rowsum(dO * O) lives in the
+// library's static device array.
+//  * Limit: B*H*T <= DTC_ATTN_STATIC_DELTA_MAX (262144); larger problems are rejected with an error.
+//  * Calls no cudaMalloc / cudaFree / allocating library routine.
+//  * The first call on each device resolves the array's device address; make that first call outside of any
+//    stream capture (e.g. during warm-up), with the device current.
+//  * All calls on one GPU share the array and it keeps the previous call's contents.  Nothing in it has to
+//    start at zero — the first kernel overwrites every element the second one reads — but two calls that
+//    overlap on the GPU (different streams, or graph branches running concurrently) race on it.
+extern "C" int dtc_flash_attn_bwd_static(const void* q, const void* k, const void* v, long long ld, const void* o,
+                                         long long ldo, const void* d_o, long long lddo, const float* lse2,
+                                         float* dq_accum, long long lddq, void* dk, void* dv, long long lddkv, int B,
+                                         int H, int T, int head_dim, cudaStream_t stream) {
+  DTC_CHECK_ARG(B > 0 && H > 0 && T > 0 && T % ATT_BLK == 0, "flash_attn_bwd_static: T=%d must be a multiple of %d", T,
+                ATT_BLK);
+  DTC_CHECK_ARG(head_dim == 32 || head_dim == 64, "flash_attn_bwd_static: head_dim %d not supported (32, 64)", head_dim);
+  DTC_CHECK_ARG(ld % 8 == 0 && ldo % 8 == 0 && lddo % 8 == 0 && lddq % 4 == 0 && lddkv % 8 == 0,
+                "flash_attn_bwd_static: leading dimension alignment");
+  const long long need = (long long)B * H * T;
+  DTC_CHECK_ARG(need <= DTC_ATTN_STATIC_DELTA_MAX,
+                "flash_attn_bwd_static: B*H*T = %lld exceeds the static scratch capacity of %d floats; "
+                "use dtc_flash_attn_bwd with a caller-provided delta buffer",
+                need, DTC_ATTN_STATIC_DELTA_MAX);
+  float* delta = nullptr;
+  const int rc = attn_static_delta_ptr(&delta);
+  if (rc) return rc;
+  if (head_dim == 32)
+    return launch_bwd<32>(q, k, v, ld, o, ldo, d_o, lddo, lse2, delta, dq_accum, lddq, dk, dv, lddkv, B, H, T, stream);
+  return launch_bwd<64>(q, k, v, ld, o, ldo, d_o, lddo, lse2, delta, dq_accum, lddq, dk, dv, lddkv, B, H, T, stream);
+}

@@ -49,6 +49,17 @@ int dtc_flash_attn_bwd(const void* q, const void* k, const void* v, long long ld
                        long long lddq, void* dk, void* dv, long long lddkv, int B, int H, int T, int head_dim,
                        cudaStream_t stream);
 
+/* No counterpart in the reference.  Allocation-free variant of dtc_flash_attn_bwd for callers that may not
+ * allocate device memory (plugins inside a runtime that owns all allocations, loops that cannot take the
+ * device-wide sync of cudaMalloc/cudaFree, jobs with a device-memory budget fixed up front):
+ * the [B,H,T] delta scratch lives in a 1 MiB static device array inside the library (held by every GPU that loads
+ * it, until exit).  Limit B*H*T <= 262144, larger sizes are rejected.  The first call on a device resolves the
+ * array address — make it before any stream capture.  Calls share the array: overlapping calls on one GPU race. */
+int dtc_flash_attn_bwd_static(const void* q, const void* k, const void* v, long long ld, const void* o, long long ldo,
+                              const void* d_o, long long lddo, const float* lse2, float* dq_accum, long long lddq,
+                              void* dk, void* dv, long long lddkv, int B, int H, int T, int head_dim,
+                              cudaStream_t stream);
+
 /* ---- LayerNorm (K4; ref: model/TransformerBlock.py:16,22, model/GPTModel.py:71) -------------------- */
 int dtc_layernorm_fwd(const void* x, const void* gamma, const void* beta, void* y, float* mean, float* rstd, int M,
                       int D, float eps, cudaStream_t stream);
