@@ -167,7 +167,6 @@ def run(args) -> dict | None:
         "gpu_launches": int(gpu_launches),  # rank 0, both timed regions (2K steps)
         "clocks": clocks.summary(), "loss_first": first_loss, "loss_last": last,
     }
-    shutdown()
     return result if mesh.is_main else None
 
 
@@ -194,12 +193,19 @@ def main() -> int:
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                "--master-addr", "127.0.0.1", "--master-port", "29541", os.path.abspath(__file__), *sys.argv[1:]]
         return subprocess.call(cmd)
+    if os.environ.get("DTC_HANG_DUMP"):  # debugging aid: dump every thread's stack if the run stalls
+        import faulthandler
+        faulthandler.dump_traceback_later(int(os.environ["DTC_HANG_DUMP"]), exit=True)
     os.environ.setdefault("RANK", "0")
     os.environ.setdefault("WORLD_SIZE", "1")
     os.environ.setdefault("LOCAL_RANK", "0")
-    res = run(args)
+    res = run(args)  # engine, CUDA graph and communicator users are released when run() returns
     if res is not None:
-        print(json.dumps(res))
+        print(json.dumps(res), flush=True)
+    import gc
+    gc.collect()
+    from distributed_training_compare_jax_b200.parallel.mesh import shutdown
+    shutdown(hard_exit_after_s=20)
     return 0
 
 

@@ -27,6 +27,7 @@ class Axis:
     rank: int = 0
     group: object | None = None
     ranks: list[int] = field(default_factory=lambda: [0])
+    group2: object | None = None  # second communicator over the same ranks (PP: upstream gradient traffic)
 
     def all_reduce(self, t: torch.Tensor, op=None) -> torch.Tensor:
         if self.size > 1:
@@ -86,7 +87,7 @@ class DeviceMesh:
         return float(t.item())
 
 
-def init_distributed(device_type: str | None = None, timeout_s: int = 600) -> tuple[int, int, torch.device, str]:
+def init_distributed(device_type: str | None = None, timeout_s: int | None = None) -> tuple[int, int, torch.device, str]:
     """Initialise torch.distributed from the torchrun / spawn environment.  Returns (rank, world, device, backend)."""
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -98,6 +99,8 @@ def init_distributed(device_type: str | None = None, timeout_s: int = 600) -> tu
     else:
         device = torch.device("cpu")
     backend = "none"
+    if timeout_s is None:
+        timeout_s = int(os.environ.get("DTC_DIST_TIMEOUT", "600"))
     if world > 1:
         backend = "nccl" if use_cuda else "gloo"
         if not dist.is_initialized():
@@ -116,19 +119,20 @@ def build_mesh(dp: int, tp: int, pp: int, device_type: str | None = None) -> Dev
         raise ValueError(f"mesh {pp}x{dp}x{tp} (pp x dp x tp) does not match world size {world}")
     tp_idx, dp_idx, pp_idx = rank % tp, (rank // tp) % dp, rank // (tp * dp)
 
-    def make(name: str, size: int, my_index: int, groups: list[list[int]]) -> Axis:
-        mine, my_ranks = None, [rank]
+    def make(name: str, size: int, my_index: int, groups: list[list[int]], second: bool = False) -> Axis:
+        mine, mine2, my_ranks = None, None, [rank]
         for ranks in groups:  # every rank must create every group (collective call)
             g = dist.new_group(ranks) if (world > 1 and size > 1) else None
+            g2 = dist.new_group(ranks) if (second and world > 1 and size > 1) else None
             if rank in ranks:
-                mine, my_ranks = g, ranks
-        return Axis(name, size, my_index, mine, my_ranks)
+                mine, mine2, my_ranks = g, g2, ranks
+        return Axis(name, size, my_index, mine, my_ranks, mine2)
 
     tp_groups = [[(p * dp + d) * tp + t for t in range(tp)] for p in range(pp) for d in range(dp)]
     dp_groups = [[(p * dp + d) * tp + t for d in range(dp)] for p in range(pp) for t in range(tp)]
     pp_groups = [[(p * dp + d) * tp + t for p in range(pp)] for d in range(dp) for t in range(tp)]
     return DeviceMesh(world, rank, device, make("dp", dp, dp_idx, dp_groups), make("tp", tp, tp_idx, tp_groups),
-                      make("pp", pp, pp_idx, pp_groups), backend)
+                      make("pp", pp, pp_idx, pp_groups, second=True), backend)
 
 
 def single_device_mesh(device: torch.device | str | None = None) -> DeviceMesh:
@@ -137,10 +141,31 @@ def single_device_mesh(device: torch.device | str | None = None) -> DeviceMesh:
     return DeviceMesh(1, 0, torch.device(device), Axis("dp"), Axis("tp"), Axis("pp"))
 
 
-def shutdown() -> None:
-    if dist.is_available() and dist.is_initialized():
+def shutdown(hard_exit_after_s: float | None = None) -> None:
+    """Tear the process groups down.  CUDA graphs that captured NCCL work must be released first (drop the
+    train-step / engine objects before calling this); with ``hard_exit_after_s`` a teardown that does not finish
+    in time ends the process with ``os._exit(0)`` instead of hanging the job."""
+    if not (dist.is_available() and dist.is_initialized()):
+        return
+
+    def _destroy():
         try:
+            if torch.cuda.is_available():
+                torch.cuda.synchronize()
             dist.barrier()
         except Exception:
             pass
         dist.destroy_process_group()
+
+    if hard_exit_after_s is None:
+        _destroy()
+        return
+    import sys
+    import threading
+    t = threading.Thread(target=_destroy, daemon=True)
+    t.start()
+    t.join(hard_exit_after_s)
+    if t.is_alive():
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)

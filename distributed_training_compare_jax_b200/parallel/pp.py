@@ -8,9 +8,13 @@ What is dropped on purpose: labels and validity flags do n
 (every stage gets the batch from its own loader; validity is static in the schedule) and nothing is sent on
 bubble ticks.  Added: the 1F1B schedule (at most S − stage microbatches in flight).
 
-Transfers stay on NCCL send/recv (``torch.distributed`` P2P; gloo on CPU).  A send produced by one action
-and the receive needed by the next are issued as ONE batched P2P group, which is what makes the
-bidirectional steady state of 1F1B deadlock-free.
+Transfers stay on NCCL send/recv (``torch.distributed`` P2P; gloo on CPU).  Activations (downstream) and
+activation gradients (upstream) travel on TWO separate communicators, each with its own NCCL stream: a send is
+issued right after the action that produced it and is not waited for, a receive is issued right before the
+action that needs it.  Because the two directions never queue behind each other, the bidirectional steady
+state of 1F1B cannot form a wait cycle, and no batching of unrelated sends and receives is needed (measured on
+B200: a batched group holding a send and a receive whose peer issues them as two separate groups never
+completes under NCCL 2.28 — ``tools/p2p_probe.py``).
 """
 from __future__ import annotations
 
@@ -75,18 +79,36 @@ def max_in_flight(actions: list[Action]) -> int:
 
 
 class P2PBackend:
-    """torch.distributed point-to-point over the PP axis (NCCL on GPU, gloo on CPU)."""
+    """torch.distributed point-to-point over the PP axis (NCCL on GPU, gloo on CPU): one communicator per
+    direction (``axis.group`` downstream, ``axis.group2`` upstream)."""
 
     def __init__(self, axis):
         self.axis = axis
+        self.inflight: list = []
 
-    def exchange(self, sends: list[tuple[torch.Tensor, int]], recvs: list[tuple[torch.Tensor, int]]) -> None:
-        """sends / recvs: (tensor, stage index of the peer).  All issued as one batched group, then waited."""
-        ops = [dist.P2POp(dist.isend, t, self.axis.ranks[peer], group=self.axis.group) for t, peer in sends]
-        ops += [dist.P2POp(dist.irecv, t, self.axis.ranks[peer], group=self.axis.group) for t, peer in recvs]
-        if ops:
-            for w in dist.batch_isend_irecv(ops):
-                w.wait()
+    def _group(self, peer: int):
+        down = peer > self.axis.rank
+        g2 = getattr(self.axis, "group2", None)
+        return self.axis.group if (down or g2 is None) else g2
+
+    def send(self, t: torch.Tensor, peer: int) -> None:
+        """Asynchronous: the buffer must stay untouched until ``flush`` (end of the step)."""
+        self.inflight.append(dist.isend(t, self.axis.ranks[peer], group=self._group_for_send(peer)))
+
+    def _group_for_send(self, peer: int):
+        # a downstream send (to stage+1) pairs with the peer's receive from stage-1: both use the downstream group
+        return self._group(peer)
+
+    def recv(self, t: torch.Tensor, peer: int) -> None:
+        down = peer < self.axis.rank  # data arriving from the previous stage travels downstream
+        g2 = getattr(self.axis, "group2", None)
+        g = self.axis.group if (down or g2 is None) else g2
+        dist.irecv(t, self.axis.ranks[peer], group=g).wait()
+
+    def flush(self) -> None:
+        for w in self.inflight:
+            w.wait()
+        self.inflight = []
 
 
 class PipelineExecutor:
@@ -101,24 +123,18 @@ class PipelineExecutor:
 
     def run(self) -> None:
         eng, first, last = self.engine, self.stage == 0, self.stage == self.n_stages - 1
-        pending_sends: list[tuple[torch.Tensor, int]] = []
         for a in self.actions:
-            recvs: list[tuple[torch.Tensor, int]] = []
             if a.kind == "F" and not first:
-                recvs.append((eng.input_buffer(a.mb), self.stage - 1))
+                self.p2p.recv(eng.input_buffer(a.mb), self.stage - 1)
             if a.kind == "B" and not last:
-                recvs.append((eng.grad_input_buffer(a.mb), self.stage + 1))
-            if pending_sends or recvs:
-                self.p2p.exchange(pending_sends, recvs)
-                pending_sends = []
+                self.p2p.recv(eng.grad_input_buffer(a.mb), self.stage + 1)
             self.trace.append((a.kind, a.mb))
             if a.kind == "F":
                 out = eng.forward(a.mb)
                 if not last:
-                    pending_sends.append((out, self.stage + 1))
+                    self.p2p.send(out, self.stage + 1)
             else:
                 gin = eng.backward(a.mb)
                 if not first:
-                    pending_sends.append((gin.contiguous(), self.stage - 1))
-        if pending_sends:
-            self.p2p.exchange(pending_sends, [])
+                    self.p2p.send(gin.contiguous(), self.stage - 1)
+        self.p2p.flush()

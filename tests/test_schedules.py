@@ -49,23 +49,30 @@ class _FakeNet:
         self.lock = threading.Condition()
         self.box = {}
 
-    def exchange(self, me, sends, recvs):
+    def send(self, me, t, peer):
         with self.lock:
-            for t, peer in sends:
-                self.box.setdefault((me, peer), []).append(t.clone())
+            self.box.setdefault((me, peer), []).append(t.clone())
             self.lock.notify_all()
-            for t, peer in recvs:
-                ok = self.lock.wait_for(lambda: self.box.get((peer, me)), timeout=5)
-                assert ok, f"stage {me} starved waiting for stage {peer}: deadlock"
-                t.copy_(self.box[(peer, me)].pop(0))
+
+    def recv(self, me, t, peer):
+        with self.lock:
+            ok = self.lock.wait_for(lambda: self.box.get((peer, me)), timeout=5)
+            assert ok, f"stage {me} starved waiting for stage {peer}: deadlock"
+            t.copy_(self.box[(peer, me)].pop(0))
 
 
 class _FakeP2P:
     def __init__(self, net, me):
         self.net, self.me = net, me
 
-    def exchange(self, sends, recvs):
-        self.net.exchange(self.me, sends, recvs)
+    def send(self, t, peer):
+        self.net.send(self.me, t, peer)
+
+    def recv(self, t, peer):
+        self.net.recv(self.me, t, peer)
+
+    def flush(self):
+        pass
 
 
 class _FakeEngine:
