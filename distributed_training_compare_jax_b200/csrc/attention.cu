@@ -60,7 +60,8 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 5);
 
   const int tid = threadIdx.x, warp = tid >> 5;
-  const int qblk = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  // heaviest tiles first: query block i attends i+1 key blocks, so launch the last query blocks first
+  const int qblk = gridDim.x - 1 - blockIdx.x, h = blockIdx.y, b = blockIdx.z;
   const int row0 = b * T + qblk * ATT_BLK;  // first global row of the query tile
   const int nkv = qblk + 1;                 // causal: key blocks 0..qblk
 

@@ -17,6 +17,7 @@
 //                               GELU-backward / fp32 reduce-add (split-K) -> 16-byte global stores
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "tma_host.h"
@@ -280,9 +281,345 @@ static int launch_gemm(const void* A, long long lda, const void* B, long long ld
   return 0;
 }
 
+
+// =========================================================================================================
+// Persistent variant (default): one CTA per SM walks a static round-robin tile list.
+//   * the accumulator is double-buffered in TMEM (2 x BN columns): the MMA warp starts tile i+1 while the
+//     epilogue warps drain tile i;
+//   * bf16 outputs leave through a 128B-swizzled smem staging tile and TMA stores (coalesced, clipped at the
+//     matrix edge by the tensor map); the residual / pre-activation tile needed by the epilogue is TMA-loaded
+//     into a second staging tile by the producer warp while the mainloop runs;
+//   * fp32 outputs (split-K reduce-add, fp32 store) keep the register path.
+// =========================================================================================================
+constexpr int PG_STAGE_MAX = 6;
+
+template <int BN>
+struct PgSmem {
+  static constexpr int A_BYTES = BM * BK * 2;
+  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int HALF_BYTES = BM * 128;                   // 128 rows x 64 bf16
+  static constexpr int TILE_BYTES = (BN / 64) * HALF_BYTES;     // staging tile [128 x BN] bf16
+  static constexpr int bytes(int stages) { return stages * STAGE_BYTES + 2 * TILE_BYTES + 1024 + 256; }
+};
+
+constexpr int PG_THREADS = 64 + 256;  // TMA warp, MMA warp, 8 epilogue warps (two per TMEM lane quadrant)
+DTC_DEVICE void epi_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+
+template <bool A_MN, bool B_MN, int BN>
+__global__ void __launch_bounds__(PG_THREADS)
+gemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                       const __grid_constant__ CUtensorMap tma_out, const __grid_constant__ CUtensorMap tma_out2,
+                       const __grid_constant__ CUtensorMap tma_aux, int M, int N, int K, int m_blocks, int n_blocks,
+                       int splits, int kb_per_split, int num_stages, GemmEpi epi) {
+  using S = PgSmem<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* stage_out = smem + num_stages * S::STAGE_BYTES;  // out tile (bf16)
+  uint8_t* stage_aux = stage_out + S::TILE_BYTES;           // aux tile (input) or out2 tile (GELU output)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(stage_aux + S::TILE_BYTES);
+  uint64_t* full_bar = bars;                       // [PG_STAGE_MAX]
+  uint64_t* empty_bar = bars + PG_STAGE_MAX;       // [PG_STAGE_MAX]
+  uint64_t* tmem_full = bars + 2 * PG_STAGE_MAX;   // [2]
+  uint64_t* tmem_empty = tmem_full + 2;            // [2]
+  uint64_t* aux_full = tmem_empty + 2;
+  uint64_t* aux_empty = aux_full + 1;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(aux_empty + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int total_kb = (K + BK - 1) / BK;
+  const int tiles_mn = m_blocks * n_blocks;
+  const int total_tiles = tiles_mn * splits;
+  const int mode = epi.mode;
+  const bool bf16_out = mode <= EPI_DGELU;
+  const bool use_aux = (mode == EPI_BIAS_RESIDUAL || mode == EPI_DGELU);
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tma_a);
+    tma_prefetch_desc(&tma_b);
+    if (bf16_out) tma_prefetch_desc(&tma_out);
+    for (int s = 0; s < num_stages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&tmem_full[b], 1);
+      mbar_init(&tmem_empty[b], 8);  // one arrival per epilogue warp
+    }
+    mbar_init(aux_full, 1);
+    mbar_init(aux_empty, 8);
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_ptr_smem, 2 * BN);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp == 0) {
+    // ------------------------------ TMA producer ------------------------------
+    if (elect_one()) {
+      uint32_t kit = 0;  // running k-block counter across tiles -> stage / phase
+      int it = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+        const int split = tile / tiles_mn, mn = tile % tiles_mn;
+        const int m_blk = mn % m_blocks, n_blk = mn / m_blocks;
+        const int kb_begin = split * kb_per_split;
+        const int nkb = min(total_kb, kb_begin + kb_per_split) - kb_begin;
+        if (use_aux) {  // stage the residual / pre-activation tile for this output tile
+          mbar_wait(aux_empty, (it & 1) ^ 1);
+          mbar_expect_tx(aux_full, S::TILE_BYTES);
+#pragma unroll
+          for (int hf = 0; hf < BN / 64; ++hf)
+            tma_load_2d(stage_aux + hf * S::HALF_BYTES, &tma_aux, aux_full, n_blk * BN + hf * 64, m_blk * BM);
+        }
+        for (int i = 0; i < nkb; ++i, ++kit) {
+          const int s = kit % num_stages;
+          const uint32_t ph = (kit / num_stages) & 1;
+          mbar_wait(&empty_bar[s], ph ^ 1);
+          uint8_t* sa = smem + s * S::STAGE_BYTES;
+          uint8_t* sb = sa + S::A_BYTES;
+          mbar_expect_tx(&full_bar[s], S::STAGE_BYTES);
+          const int k0 = (kb_begin + i) * BK;
+          if (A_MN) {
+#pragma unroll
+            for (int j = 0; j < BM / 64; ++j) tma_load_2d(sa + j * (BK * 128), &tma_a, &full_bar[s], m_blk * BM + j * 64, k0);
+          } else {
+            tma_load_2d(sa, &tma_a, &full_bar[s], k0, m_blk * BM);
+          }
+          if (B_MN) {
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j) tma_load_2d(sb + j * (BK * 128), &tma_b, &full_bar[s], n_blk * BN + j * 64, k0);
+          } else {
+            tma_load_2d(sb, &tma_b, &full_bar[s], k0, n_blk * BN);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------ MMA issuer ------------------------------
+    constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+    constexpr uint32_t A_LBO = A_MN ? BK * 128 : 16, A_STEP = A_MN ? 2048 : 32;
+    constexpr uint32_t B_LBO = B_MN ? BK * 128 : 16, B_STEP = B_MN ? 2048 : 32;
+    uint32_t kit = 0;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+      const int split = tile / tiles_mn;
+      const int kb_begin = split * kb_per_split;
+      const int nkb = min(total_kb, kb_begin + kb_per_split) - kb_begin;
+      const int buf = it & 1;
+      mbar_wait(&tmem_empty[buf], ((it >> 1) & 1) ^ 1);  // epilogue has drained this accumulator buffer
+      tc_fence_after();
+      const uint32_t tmem_d = tmem_base + buf * BN;
+      for (int i = 0; i < nkb; ++i, ++kit) {
+        const int s = kit % num_stages;
+        const uint32_t ph = (kit / num_stages) & 1;
+        mbar_wait(&full_bar[s], ph);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t sa = smem_u32(smem + s * S::STAGE_BYTES);
+          const uint32_t sb = sa + S::A_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            const uint64_t da = make_smem_desc(sa + k * A_STEP, A_LBO, 1024, SWZ_128B);
+            const uint64_t db = make_smem_desc(sb + k * B_STEP, B_LBO, 1024, SWZ_128B);
+            umma_bf16(tmem_d, da, db, idesc, (i > 0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[s]);
+          if (i == nkb - 1) umma_commit(&tmem_full[buf]);
+        }
+        __syncwarp();
+      }
+    }
+  } else {
+    // ------------------------------ epilogue (warps 2..9, 256 threads) ------------------------------
+    // warp w reads TMEM lane quadrant w % 4; the two warps of a quadrant split the BN columns in halves
+    const int q = warp & 3;
+    const int chalf = (warp - 2) >> 2;
+    const int row = q * 32 + lane;
+    const bool store_leader = (threadIdx.x == 64);  // first epilogue thread issues the TMA stores
+    const float alpha = epi.alpha;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+      const int mn = tile % tiles_mn;
+      const int m_blk = mn % m_blocks, n_blk = mn / m_blocks;
+      const int buf = it & 1;
+      const long long gm = (long long)m_blk * BM + row;
+      const bool row_ok = gm < M;
+      mbar_wait(&tmem_full[buf], (it >> 1) & 1);
+      tc_fence_after();
+      if (use_aux) mbar_wait(aux_full, it & 1);
+      if (bf16_out) {
+        // the previous tile's TMA stores must have finished READING the staging tiles before they are rewritten
+        if (store_leader) tma_store_wait_read();
+        epi_bar_sync();
+      }
+      const uint32_t tmem_d = tmem_base + buf * BN + ((uint32_t)(q * 32) << 16);
+#pragma unroll 1
+      for (int c = chalf * (BN / 64); c < (chalf + 1) * (BN / 64); ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(tmem_d + c * 32, r);
+        tmem_ld_wait();
+        const int n0 = n_blk * BN + c * 32;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          const int n = n0 + g * 8;
+          float v[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]) * alpha;
+          if (epi.bias != nullptr && mode != EPI_ATOMIC_F32 && mode != EPI_DGELU && n < N) {
+            const uint4 bb = *reinterpret_cast<const uint4*>(epi.bias + n);
+            const uint32_t bw[4] = {bb.x, bb.y, bb.z, bb.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const float2 f = unpack_bf16x2(bw[j]);
+              v[2 * j] += f.x;
+              v[2 * j + 1] += f.y;
+            }
+          }
+          if (!bf16_out) {
+            if (!row_ok || n >= N) continue;
+            float* o = reinterpret_cast<float*>(epi.out) + gm * epi.ldo + n;
+            if (mode == EPI_ATOMIC_F32) {
+              red_add_v4_f32(o, v[0], v[1], v[2], v[3]);
+              red_add_v4_f32(o + 4, v[4], v[5], v[6], v[7]);
+            } else {
+              *reinterpret_cast<float4*>(o) = make_float4(v[0], v[1], v[2], v[3]);
+              *reinterpret_cast<float4*>(o + 4) = make_float4(v[4], v[5], v[6], v[7]);
+            }
+            continue;
+          }
+          // staging offset of this 16-byte chunk: 64-column half, 128-byte rows, 128B swizzle (matches the TMA maps)
+          const uint32_t off = (uint32_t)(c >> 1) * S::HALF_BYTES + swizzle_offset<3>(row * 128 + ((c & 1) * 4 + g) * 16);
+          if (use_aux) {
+            const uint4 a = *reinterpret_cast<const uint4*>(stage_aux + off);
+            const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const float2 f = unpack_bf16x2(aw[j]);
+              if (mode == EPI_BIAS_RESIDUAL) {
+                v[2 * j] += f.x;
+                v[2 * j + 1] += f.y;
+              } else {
+                v[2 * j] *= gelu_tanh_grad(f.x);
+                v[2 * j + 1] *= gelu_tanh_grad(f.y);
+              }
+            }
+          }
+          *reinterpret_cast<uint4*>(stage_out + off) = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]),
+                                                                 pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+          if (mode == EPI_BIAS_GELU) {
+            *reinterpret_cast<uint4*>(stage_aux + off) = make_uint4(
+                pack_bf16x2(gelu_tanh(v[0]), gelu_tanh(v[1])), pack_bf16x2(gelu_tanh(v[2]), gelu_tanh(v[3])),
+                pack_bf16x2(gelu_tanh(v[4]), gelu_tanh(v[5])), pack_bf16x2(gelu_tanh(v[6]), gelu_tanh(v[7])));
+          }
+        }
+      }
+      // accumulator buffer (and the aux tile) may be reused by the MMA / producer warps
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive(&tmem_empty[buf]);
+        if (use_aux) mbar_arrive(aux_empty);
+      }
+      if (bf16_out) {
+        fence_proxy_async_smem();
+        epi_bar_sync();
+        if (store_leader) {
+#pragma unroll
+          for (int hf = 0; hf < BN / 64; ++hf) {
+            tma_store_2d(&tma_out, stage_out + hf * S::HALF_BYTES, n_blk * BN + hf * 64, m_blk * BM);
+            if (mode == EPI_BIAS_GELU)
+              tma_store_2d(&tma_out2, stage_aux + hf * S::HALF_BYTES, n_blk * BN + hf * 64, m_blk * BM);
+          }
+          tma_store_commit();
+        }
+      }
+    }
+    if (bf16_out && store_leader) tma_store_wait_all();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 2 * BN);
+  }
+}
+
+static int num_sms() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess ||
+        n <= 0)
+      n = 148;
+  }
+  return n;
+}
+
+template <bool A_MN, bool B_MN, int BN>
+static int launch_gemm_persistent(const void* A, long long lda, const void* B, long long ldb, int M, int N, int K,
+                                  int splits, int stages, const GemmEpi& epi, cudaStream_t stream) {
+  using S = PgSmem<BN>;
+  CUtensorMap ta, tb, tout, tout2, taux;
+  int rc;
+  if (A_MN) rc = make_tmap_2d_bf16(&ta, A, K, M, lda, BK, 64, CU_TENSOR_MAP_SWIZZLE_128B);
+  else rc = make_tmap_2d_bf16(&ta, A, M, K, lda, BM, BK, CU_TENSOR_MAP_SWIZZLE_128B);
+  if (rc) return rc;
+  if (B_MN) rc = make_tmap_2d_bf16(&tb, B, K, N, ldb, BK, 64, CU_TENSOR_MAP_SWIZZLE_128B);
+  else rc = make_tmap_2d_bf16(&tb, B, N, K, ldb, BN, BK, CU_TENSOR_MAP_SWIZZLE_128B);
+  if (rc) return rc;
+  tout = ta;
+  tout2 = ta;
+  taux = ta;  // placeholders: never dereferenced when the mode does not use them
+  if (epi.mode <= EPI_DGELU) {
+    if ((rc = make_tmap_2d_bf16(&tout, epi.out, M, N, epi.ldo, BM, 64, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+    if (epi.mode == EPI_BIAS_GELU &&
+        (rc = make_tmap_2d_bf16(&tout2, epi.out2, M, N, epi.ldo2, BM, 64, CU_TENSOR_MAP_SWIZZLE_128B)))
+      return rc;
+    if ((epi.mode == EPI_BIAS_RESIDUAL || epi.mode == EPI_DGELU) &&
+        (rc = make_tmap_2d_bf16(&taux, epi.aux, M, N, epi.ld_aux, BM, 64, CU_TENSOR_MAP_SWIZZLE_128B)))
+      return rc;
+  }
+  const int total_kb = (K + BK - 1) / BK;
+  if (splits < 1) splits = 1;
+  if (splits > total_kb) splits = total_kb;
+  const int kb_per_split = (total_kb + splits - 1) / splits;
+  splits = (total_kb + kb_per_split - 1) / kb_per_split;
+  if (stages < 2) stages = 2;
+  if (stages > PG_STAGE_MAX) stages = PG_STAGE_MAX;
+  while (S::bytes(stages) > 227 * 1024) --stages;
+  const int smem_bytes = S::bytes(stages);
+  auto kern = gemm_persistent_kernel<A_MN, B_MN, BN>;
+  static bool configured = false;
+  if (!configured) {
+    DTC_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    configured = true;
+  }
+  const int m_blocks = (M + BM - 1) / BM, n_blocks = (N + BN - 1) / BN;
+  const int total_tiles = m_blocks * n_blocks * splits;
+  const int grid = total_tiles < num_sms() ? total_tiles : num_sms();
+  kern<<<grid, PG_THREADS, smem_bytes, stream>>>(ta, tb, tout, tout2, taux, M, N, K, m_blocks, n_blocks, splits,
+                                                   kb_per_split, stages, epi);
+  DTC_CHECK_LAUNCH();
+  return 0;
+}
+
 }  // namespace dtc
 
 using namespace dtc;
+
+static int g_gemm_impl = 0;  // 0 = persistent kernel (default), 1 = one-tile-per-CTA kernel
+// Tuning / A-B switch used by tools/gemm_bench.py.
+extern "C" int dtc_gemm_set_impl(int impl) {
+  g_gemm_impl = impl;
+  return 0;
+}
 
 // C ABI -----------------------------------------------------------------------------------------
 // A: a_mn_major == 0 -> [M, K] row-major (lda elements between rows); == 1 -> [K, M] row-major.
@@ -315,6 +652,19 @@ extern "C" int dtc_gemm_bf16(const void* A, long long lda, int a_mn_major, const
   epi.out2 = reinterpret_cast<bf16*>(out2);
   epi.ldo2 = ldo2;
   if (block_n == 0) block_n = (N <= 64) ? 64 : 128;
+  static const bool env_v1 = getenv("DTC_GEMM_V1") != nullptr;  // A/B switch: one-tile-per-CTA kernel
+  const bool use_v1 = env_v1 || g_gemm_impl == 1;
+  if (!use_v1 && block_n != 256) {
+    if (stages == 0) stages = PG_STAGE_MAX;
+#define DTC_PGEMM_DISPATCH(AMN, BMN)                                                                              \
+  if (block_n == 64) return launch_gemm_persistent<AMN, BMN, 64>(A, lda, B, ldb, M, N, K, splits, stages, epi, stream); \
+  return launch_gemm_persistent<AMN, BMN, 128>(A, lda, B, ldb, M, N, K, splits, stages, epi, stream);
+    if (!a_mn_major && !b_mn_major) { DTC_PGEMM_DISPATCH(false, false) }
+    if (!a_mn_major && b_mn_major) { DTC_PGEMM_DISPATCH(false, true) }
+    if (a_mn_major && !b_mn_major) { DTC_PGEMM_DISPATCH(true, false) }
+    DTC_PGEMM_DISPATCH(true, true)
+#undef DTC_PGEMM_DISPATCH
+  }
   if (stages == 0) stages = (block_n == 256) ? 4 : (block_n == 128 ? 3 : 4);
 #define DTC_GEMM_DISPATCH(AMN, BMN)                                                                          \
   switch (block_n) {                                                                                         \

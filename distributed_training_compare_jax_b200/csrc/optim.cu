@@ -179,8 +179,8 @@ extern "C" int dtc_adamw(float* p, float* m, float* v, float* g, void* p_bf16, l
 // out[n] += sum_m x[m, n]   (x bf16 [M, N] with leading dimension ld, N % 8 == 0)
 extern "C" int dtc_colsum(const void* x, long long ld, int M, int N, float* out, cudaStream_t stream) {
   DTC_CHECK_ARG(M > 0 && N > 0 && N % 8 == 0 && ld % 8 == 0, "colsum: bad shape M=%d N=%d ld=%lld", M, N, ld);
-  int ysplit = (M + 63) / 64;
-  if (ysplit > 32) ysplit = 32;
+  int ysplit = (M + 31) / 32;  // >= 4 rows per thread; enough CTAs to fill 148 SMs even for N = 512
+  if (ysplit > 128) ysplit = 128;
   dim3 grid((N + 255) / 256, ysplit);
   colsum_kernel<<<grid, 256, 0, stream>>>(reinterpret_cast<const bf16*>(x), ld, M, N, out);
   DTC_CHECK_LAUNCH();
