@@ -36,6 +36,10 @@ enum GemmEpiMode : int {
   EPI_DGELU = 3,          // out_bf16 = acc * gelu_tanh'(aux)
   EPI_ATOMIC_F32 = 4,     // out_f32 += alpha*acc      (split-K / gradient accumulation)
   EPI_STORE_F32 = 5,      // out_f32 = alpha*acc + bias
+  // Fused GEMM -> all-reduce over NVSwitch multicast: every rank reduce-adds its partial tile (rank 0 also adds
+  // bias + residual) into ALL ranks' copies of a zeroed symmetric bf16 buffer with multimem.red (`out` is the
+  // multicast address).  Persistent kernel only.
+  EPI_MC_RED_BF16 = 6,
 };
 
 struct GemmEpi {
@@ -58,6 +62,11 @@ struct GemmSmem {
   static constexpr int bytes(int stages) { return stages * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/; }
 };
 
+DTC_DEVICE void mc_red_add_bf16x8(bf16* mc_addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("multimem.red.relaxed.sys.global.add.v4.bf16x2 [%0], {%1, %2, %3, %4};" ::"l"(mc_addr), "r"(a), "r"(b),
+               "r"(c), "r"(d)
+               : "memory");
+}
 DTC_DEVICE void red_add_v4_f32(float* addr, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
@@ -332,8 +341,8 @@ gemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
   const int tiles_mn = m_blocks * n_blocks;
   const int total_tiles = tiles_mn * splits;
   const int mode = epi.mode;
-  const bool bf16_out = mode <= EPI_DGELU;
-  const bool use_aux = (mode == EPI_BIAS_RESIDUAL || mode == EPI_DGELU);
+  const bool bf16_out = mode <= EPI_DGELU;  // outputs that leave through the smem staging tile + TMA store
+  const bool use_aux = (mode == EPI_BIAS_RESIDUAL || mode == EPI_DGELU || (mode == EPI_MC_RED_BF16 && epi.aux != nullptr));
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tma_a);
@@ -481,6 +490,24 @@ gemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
               v[2 * j + 1] += f.y;
             }
           }
+          if (mode == EPI_MC_RED_BF16) {
+            if (use_aux) {  // rank 0 carries the residual tile (TMA-staged like the residual epilogue)
+              const uint32_t aoff =
+                  (uint32_t)(c >> 1) * S::HALF_BYTES + swizzle_offset<3>(row * 128 + ((c & 1) * 4 + g) * 16);
+              const uint4 a = *reinterpret_cast<const uint4*>(stage_aux + aoff);
+              const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const float2 f = unpack_bf16x2(aw[j]);
+                v[2 * j] += f.x;
+                v[2 * j + 1] += f.y;
+              }
+            }
+            if (!row_ok || n >= N) continue;
+            mc_red_add_bf16x8(reinterpret_cast<bf16*>(epi.out) + gm * epi.ldo + n, pack_bf16x2(v[0], v[1]),
+                              pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+            continue;
+          }
           if (!bf16_out) {
             if (!row_ok || n >= N) continue;
             float* o = reinterpret_cast<float*>(epi.out) + gm * epi.ldo + n;
@@ -586,6 +613,9 @@ static int launch_gemm_persistent(const void* A, long long lda, const void* B, l
         (rc = make_tmap_2d_bf16(&taux, epi.aux, M, N, epi.ld_aux, BM, 64, CU_TENSOR_MAP_SWIZZLE_128B)))
       return rc;
   }
+  if (epi.mode == EPI_MC_RED_BF16 && epi.aux != nullptr &&
+      (rc = make_tmap_2d_bf16(&taux, epi.aux, M, N, epi.ld_aux, BM, 64, CU_TENSOR_MAP_SWIZZLE_128B)))
+    return rc;
   const int total_kb = (K + BK - 1) / BK;
   if (splits < 1) splits = 1;
   if (splits > total_kb) splits = total_kb;
@@ -635,7 +665,7 @@ extern "C" int dtc_gemm_bf16(const void* A, long long lda, int a_mn_major, const
   DTC_CHECK_ARG(lda % 8 == 0 && ldb % 8 == 0, "gemm: lda=%lld ldb=%lld must be multiples of 8 elements", lda, ldb);
   DTC_CHECK_ARG(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0 && ((uintptr_t)out & 15) == 0,
                 "gemm: operand pointers must be 16-byte aligned");
-  DTC_CHECK_ARG(epi_mode >= 0 && epi_mode <= 5, "gemm: bad epilogue mode %d", epi_mode);
+  DTC_CHECK_ARG(epi_mode >= 0 && epi_mode <= 6, "gemm: bad epilogue mode %d", epi_mode);
   DTC_CHECK_ARG(splits <= 1 || epi_mode == EPI_ATOMIC_F32, "gemm: split-K needs the fp32 reduce-add epilogue");
   DTC_CHECK_ARG(!(epi_mode == EPI_BIAS_RESIDUAL || epi_mode == EPI_DGELU) || aux != nullptr, "gemm: aux missing");
   DTC_CHECK_ARG(epi_mode != EPI_BIAS_GELU || out2 != nullptr, "gemm: out2 missing");
@@ -653,7 +683,8 @@ extern "C" int dtc_gemm_bf16(const void* A, long long lda, int a_mn_major, const
   epi.ldo2 = ldo2;
   if (block_n == 0) block_n = (N <= 64) ? 64 : 128;
   static const bool env_v1 = getenv("DTC_GEMM_V1") != nullptr;  // A/B switch: one-tile-per-CTA kernel
-  const bool use_v1 = env_v1 || g_gemm_impl == 1;
+  const bool use_v1 = (env_v1 || g_gemm_impl == 1) && epi_mode != EPI_MC_RED_BF16;
+  if (epi_mode == EPI_MC_RED_BF16 && block_n == 256) block_n = 128;
   if (!use_v1 && block_n != 256) {
     if (stages == 0) stages = PG_STAGE_MAX;
 #define DTC_PGEMM_DISPATCH(AMN, BMN)                                                                              \

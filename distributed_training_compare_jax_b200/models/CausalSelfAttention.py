@@ -54,5 +54,4 @@ class CausalSelfAttention:
                           self.config.head_dim, dqkv=ws.dqkv, dq_accum=ws.dq_accum, delta=ws.delta)
         Fn.colsum(ws.dqkv, g["bqkv"][l])
         Fn.gemm(ws.ln1[l], ws.dqkv, a_mn=True, b_mn=True, epi="atomic_f32", out=g["wqkv"][l], splits=eng.wgrad_splits)
-        Fn.gemm(ws.dqkv, c["wqkv"][l], out=ws.dln)
-        self.mesh.tp.all_reduce(ws.dln)
+        eng.tp_reduced_gemm(ws.dqkv, c["wqkv"][l], out=ws.dln)

@@ -109,8 +109,7 @@ class GPTModel:
         # logits now hold dlogits (pad columns are zero)
         Fn.colsum(ws.logits, g["blm"])
         Fn.gemm(ws.lnf, ws.logits, a_mn=True, b_mn=True, epi="atomic_f32", out=g["wlm"], splits=1)
-        Fn.gemm(ws.logits, c["wlm"], out=ws.dln)
-        tp.all_reduce(ws.dln)
+        eng.tp_reduced_gemm(ws.logits, c["wlm"], out=ws.dln)
         Fn.layernorm_bwd(ws.dln, ws.h[L], ws.meanf, ws.rstdf, c["lnf_g"], g["lnf_g"], g["lnf_b"], dres=None, out=ws.dh_a)
         eng.on_head_grads_ready()
         return ws.dh_a

@@ -44,5 +44,4 @@ class MLP:
         Fn.gemm(dh, c["w2"][l], epi="dgelu", aux=ws.f1[l], out=ws.df1)
         Fn.colsum(ws.df1, g["b1"][l])
         Fn.gemm(ws.ln2[l], ws.df1, a_mn=True, b_mn=True, epi="atomic_f32", out=g["w1"][l], splits=eng.wgrad_splits)
-        Fn.gemm(ws.df1, c["w1"][l], out=ws.dln)
-        self.mesh.tp.all_reduce(ws.dln)
+        eng.tp_reduced_gemm(ws.df1, c["w1"][l], out=ws.dln)

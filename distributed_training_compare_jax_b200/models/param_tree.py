@@ -132,7 +132,7 @@ class ParamStore:
     ``self.g[name]``, ``self.c[name]`` (compute copy) are views; ``flat_*`` are the whole buffers."""
 
     def __init__(self, local: LocalShape, device: torch.device | str = "cpu", with_compute_copy: bool = True,
-                 with_optimizer_state: bool = True, flat_alloc=None):
+                 with_optimizer_state: bool = True, flat_alloc=None, symm_group=None):
         self.local = local
         self.device = torch.device(device)
         rep, shard = local.physical_shapes()
@@ -149,10 +149,20 @@ class ParamStore:
         self.shard_numel = off - self.rep_numel
         alloc = flat_alloc or (lambda n, dtype: torch.zeros(n, device=self.device, dtype=dtype))
         self.flat_master = alloc(self.numel, torch.float32)
-        self.flat_grad = alloc(self.numel, torch.float32)
         self.flat_m = alloc(self.numel, torch.float32) if with_optimizer_state else None
         self.flat_v = alloc(self.numel, torch.float32) if with_optimizer_state else None
-        self.flat_compute = alloc(self.numel, torch.bfloat16) if with_compute_copy else None
+        self.symm = None
+        if symm_group is not None:
+            # gradient + bf16 compute copy in symmetric memory: peers (and the NVSwitch multicast address) can reach
+            # them, which is what the fused reduce-scatter / sharded AdamW / all-gather kernels operate on
+            from ..parallel.symm import SymmBuffer
+            self.symm = {"grad": SymmBuffer(self.numel, torch.float32, self.device, symm_group),
+                         "compute": SymmBuffer(self.numel, torch.bfloat16, self.device, symm_group)}
+            self.flat_grad = self.symm["grad"].tensor
+            self.flat_compute = self.symm["compute"].tensor
+        else:
+            self.flat_grad = alloc(self.numel, torch.float32)
+            self.flat_compute = alloc(self.numel, torch.bfloat16) if with_compute_copy else None
         self.p = self._views(self.flat_master)
         self.g = self._views(self.flat_grad)
         self.c = self._views(self.flat_compute) if with_compute_copy else None

@@ -41,6 +41,10 @@ _PROTOS: dict[str, list[Any]] = {
     "dtc_clip_finalize": [P, I, F, F, P, P],
     "dtc_adamw": [P, P, P, P, P, L, P, P, F, F, F, F, F, F, I],
     "dtc_colsum": [P, L, I, I, P],
+    "dtc_symm_barrier": [P, I, I, I],
+    "dtc_dp_reduce_scatter": [P, U64, P, I, I, L, L, P],
+    "dtc_dp_norm_exchange": [P, I, P, P, I, I, I, F, P, P],
+    "dtc_dp_adamw_allgather": [P, P, P, P, U64, P, I, L, L, L, P, P, F, F, F, F, F],
 }
 # launches per call (for the gpu_launches accounting in bench.py)
 _LAUNCH_COUNT = {"dtc_flash_attn_bwd": 2}
@@ -69,6 +73,10 @@ def load(build_if_missing: bool = True) -> C.CDLL:
     lib.dtc_device_arch.restype = I
     lib.dtc_sumsq_num_partials.restype = I
     lib.dtc_sumsq_num_partials.argtypes = [L]
+    lib.dtc_dp_num_partials.restype = I
+    lib.dtc_dp_num_partials.argtypes = [L]
+    lib.dtc_gemm_set_impl.restype = I
+    lib.dtc_gemm_set_impl.argtypes = [I]
     for name, argtypes in _PROTOS.items():
         fn = getattr(lib, name)
         fn.restype = I

@@ -1,15 +1,25 @@
-"""Data-parallel gradient reduction (components R10/R11, collectives X1/X2; reference: the all-reduce GSPMD
-inserts for ``P(None)`` parameters with a ``P("data", None)`` batch — parallel/sharding.py:25-27,
-train/create_train_step.py:34-40).
+"""Data-parallel gradient reduction + optimizer (components R10/R11, collectives X1/X2; reference: the gradient
+all-reduce GSPMD inserts for ``P(None)`` parameters under a ``P("data", None)`` batch — parallel/sharding.py:25-27,
+train/create_train_step.py:34-40 — followed by a replicated clip + AdamW).
 
-``make_grad_reducer`` returns the callable the optimizer invokes to make ``flat_grad`` hold the DP-summed
-gradient.  Baseline: one NCCL all-reduce over the flat gradient buffer.  The bucketed, backward-overlapped
-variant hooks the engine's ``on_*_grads_ready`` callbacks and reduces each bucket (head, layer L-1 … 0, embed)
-on a side stream as soon as its gradients are final.
+Two implementations of "make the optimizer see the DP-summed gradient":
+
+* :class:`BucketedAllReduce` (NCCL baseline): per-layer buckets (head, layer L-1 … 0, embed) all-reduced on a
+  side stream as soon as their gradients are final, overlapping the rest of the backward pass; the optimizer then
+  runs replicated, exactly like the reference.
+* :class:`FusedShardedStep` (product path, ``fused_comm: true``): the flat gradient and the bf16 compute copy live in
+  symmetric memory; one kernel reduce-scatters the gradient through NVSwitch (``multimem.ld_reduce``) while
+  accumulating ‖g‖², one tiny kernel exchanges the partial norms and derives the clip factor, and one kernel
+  runs AdamW on the owned 1/n shard and all-gathers the new bf16 parameters (``multimem.st``).  Mathematically the
+  same update as the replicated optimizer; optimizer-state traffic drops by n.
 """
 from __future__ import annotations
 
 import torch
+import torch.distributed as dist
+
+from ..ops import native
+from .symm import FlagBarrier, SymmBuffer
 
 
 class BucketedAllReduce:
@@ -19,27 +29,29 @@ class BucketedAllReduce:
         self.engine, self.mesh = engine, mesh
         self.store = engine.store
         self.stream = torch.cuda.Stream(device=engine.device)
-        self.done = torch.cuda.Event()
         engine.on_layer_grads_ready = self._layer_ready
         engine.on_head_grads_ready = self._head_ready
         st = self.store
         L = engine.local.L
-        # contiguous element ranges per bucket inside the flat buffer: the stacked (L, ...) tensors are not
-        # contiguous per layer, so a bucket is the list of per-layer slices of every stacked tensor
+
+        def numel(shape):
+            n = 1
+            for s in shape:
+                n *= s
+            return n
+
+        # the stacked (L, ...) tensors are not contiguous per layer: a layer bucket is one slice of each of them
         self.layer_slices = []
         for l in range(L):
             sl = []
             for name, (off, shape) in st.offsets.items():
-                if len(shape) >= 2 and shape[0] == L and name not in ("wte", "wpe", "wlm"):
-                    per = 1
-                    for s in shape[1:]:
-                        per *= s
+                if name not in ("wte", "wpe", "wlm", "blm", "lnf_g", "lnf_b"):
+                    per = numel(shape[1:])
                     sl.append((off + l * per, per))
             self.layer_slices.append(sl)
-        self.head_slices = [(st.offsets[n][0], int(torch.tensor(st.offsets[n][1]).prod())) for n in
-                            ("lnf_g", "lnf_b", "wlm", "blm") if n in st.offsets]
-        self.embed_slices = [(st.offsets[n][0], int(torch.tensor(st.offsets[n][1]).prod())) for n in ("wte", "wpe")
-                             if n in st.offsets]
+        self.head_slices = [(st.offsets[n][0], numel(st.offsets[n][1])) for n in ("lnf_g", "lnf_b", "wlm", "blm")
+                            if n in st.offsets]
+        self.embed_slices = [(st.offsets[n][0], numel(st.offsets[n][1])) for n in ("wte", "wpe") if n in st.offsets]
 
     def _reduce(self, slices) -> None:
         cur = torch.cuda.current_stream()
@@ -58,6 +70,55 @@ class BucketedAllReduce:
         """Called by the optimizer after backward: reduce the embedding bucket, then join the side stream."""
         self._reduce(self.embed_slices)
         torch.cuda.current_stream().wait_stream(self.stream)
+
+
+class FusedShardedStep:
+    """reduce-scatter(+‖g‖²) → norm exchange → sharded AdamW + all-gather, all through symmetric memory."""
+
+    def __init__(self, cfg, engine, mesh):
+        self.cfg, self.engine, self.mesh, self.store = cfg, engine, mesh, engine.store
+        st, dp = self.store, mesh.dp
+        if not getattr(st, "symm", None):
+            raise RuntimeError("FusedShardedStep needs a ParamStore allocated in symmetric memory")
+        self.grad, self.compute = st.symm["grad"], st.symm["compute"]
+        self.norm_slots = SymmBuffer(16, torch.float32, st.device, dp.group)
+        self.barrier = FlagBarrier(st.device, dp.group)
+        n = st.numel
+        per = -(-(n // dp.size) // 64) * 64
+        self.off = min(dp.rank * per, n)
+        self.n = max(0, min(n, self.off + per) - self.off)
+        self.n_partials = int(native.load().dtc_dp_num_partials(max(self.n, 4)))
+        self.partials = torch.zeros(self.n_partials, device=st.device, dtype=torch.float32)
+        self.scalars = torch.zeros(2, device=st.device, dtype=torch.float32)
+        self.max_norm = cfg.grad_clip
+        self.uses_multicast = bool(self.grad.mc_ptr and self.compute.mc_ptr)
+
+    @property
+    def last_norm(self):
+        return self.scalars[0]
+
+    def step(self) -> None:
+        st, dp, c = self.store, self.mesh.dp, self.cfg
+        self.barrier(0)  # every rank's backward has finished writing its gradient
+        native.call("dtc_dp_reduce_scatter", st.flat_grad, self.grad.mc_ptr, self.grad.ptr_array, dp.rank, dp.size,
+                    self.off, self.n, self.partials)
+        native.call("dtc_dp_norm_exchange", self.partials, self.n_partials, self.norm_slots.ptr_array,
+                    self.barrier.ptr_array, dp.rank, dp.size, 1, float(self.max_norm), self.scalars, st.step)
+        native.call("dtc_dp_adamw_allgather", st.flat_master, st.flat_m, st.flat_v, st.flat_grad, self.compute.mc_ptr,
+                    self.compute.ptr_array, dp.size, self.off, self.n, st.numel, self.scalars, st.step, float(c.lr),
+                    float(c.b1), float(c.b2), float(c.eps), float(c.weight_decay))
+        self.barrier(2)  # every rank's compute copy is complete before the next forward reads it
+
+    def sync_full_state(self) -> None:
+        """Checkpointing: master weights / Adam moments are only current on the owning rank — gather them."""
+        st, dp = self.store, self.mesh.dp
+        per = -(-(st.numel // dp.size) // 64) * 64
+        for flat in (st.flat_master, st.flat_m, st.flat_v):
+            for r in range(dp.size):
+                off = min(r * per, st.numel)
+                n = max(0, min(st.numel, off + per) - off)
+                if n:
+                    dist.broadcast(flat[off:off + n], src=dp.ranks[r], group=dp.group)
 
 
 def make_grad_reducer(engine, mesh):

@@ -109,6 +109,11 @@ class NativeStageEngine(StageEngineBase):
             self.ws.append(w)
         self.tp_hooks = None  # set by parallel/tp.py when the fused GEMM+collective kernels are enabled
 
+    def begin_step(self) -> None:
+        super().begin_step()
+        if self.tp_hooks is not None:
+            self.tp_hooks.begin_step()
+
     # ---- building block shared by attention-out and fc2 (row-parallel Linear + bias + residual) ----
     def row_parallel_out(self, x, w, bias, residual, out) -> None:
         tp = self.mesh.tp
@@ -120,6 +125,14 @@ class NativeStageEngine(StageEngineBase):
         else:
             Fn.gemm(x, w, b_mn=True, out=out)
         tp.all_reduce(out)
+
+    def tp_reduced_gemm(self, a, w, out) -> None:
+        """out = sum over TP ranks of a · wᵀ (dX of a column-parallel Linear, collectives X5 / X8)."""
+        if self.tp_hooks is not None:
+            self.tp_hooks.reduced_gemm(self, a, w, out)
+            return
+        Fn.gemm(a, w, out=out)
+        self.mesh.tp.all_reduce(out)
 
     def set_batch(self, mb: int, x: torch.Tensor | None, y: torch.Tensor | None) -> None:
         """x, y: int32 [micro_batch, T] (device or pinned host); copied into the static workspace buffers."""

@@ -42,19 +42,27 @@ def build_state(train_config: TrainConfig, model_config: ModelConfig, opt_config
                 micro_batch: int, n_micro: int, global_tokens: int, local: LocalShape, clip_scope: str = "global",
                 clip_scale: float = 1.0, pp_stage_keys: bool = False) -> TrainState:
     backend = resolve_backend(train_config, mesh.device)
-    store = ParamStore(local, mesh.device, with_compute_copy=(backend == "native"))
+    native_dp = backend == "native" and mesh.dp.size > 1
+    # fused DP path (symmetric-memory reduce-scatter + sharded AdamW + all-gather): pure data parallelism only
+    fused_dp = native_dp and train_config.fused_comm and mesh.tp.size == 1 and mesh.pp.size == 1
+    store = ParamStore(local, mesh.device, with_compute_copy=(backend == "native"),
+                       symm_group=mesh.dp.group if fused_dp else None)
     init_params(store, train_config.seed, pp_stage_keys=pp_stage_keys, stage_index=mesh.pp.rank)
     engine = make_engine(backend, model_config, local, mesh, store, micro_batch, model_config.max_seq_len, n_micro,
                          global_tokens, train_config.seed)
     reducer = None
-    if backend == "native" and mesh.dp.size > 1 and train_config.fused_comm:
+    if native_dp and not fused_dp:
         from ..parallel.dp import make_grad_reducer
-        reducer = make_grad_reducer(engine, mesh)
+        reducer = make_grad_reducer(engine, mesh)   # NCCL: per-layer buckets overlapped with the backward pass
     if backend == "native" and mesh.tp.size > 1 and train_config.fused_comm:
         from ..parallel.tp import attach_fused_tp
         attach_fused_tp(engine, mesh)
-    opt = create_optimizer(opt_config).bind(engine, mesh, clip_scope=clip_scope, clip_scale=clip_scale,
-                                            grad_reducer=reducer)
+    if fused_dp:
+        from ..parallel.dp import FusedShardedStep
+        opt = FusedShardedStep(opt_config, engine, mesh)
+    else:
+        opt = create_optimizer(opt_config).bind(engine, mesh, clip_scope=clip_scope, clip_scale=clip_scale,
+                                                grad_reducer=reducer)
     state = TrainState(engine, opt, mesh)
     if train_config.resume:
         meta = load_checkpoint(train_config.resume, store)
@@ -93,6 +101,8 @@ def _run_loop(train_config: TrainConfig, model_config: ModelConfig, state: Train
                     log.record(s, float(l))
                 pending = []
         if train_config.checkpoint_dir and train_config.checkpoint_every and step % train_config.checkpoint_every == 0:
+            if hasattr(state.optimizer, "sync_full_state"):
+                state.optimizer.sync_full_state()
             save_checkpoint(os.path.join(train_config.checkpoint_dir, f"step_{state.step}.npz"), state.engine.store,
                             mesh, state.step, {"strategy": strategy})
     ms = mesh.max_over_ranks(timer.stop())
@@ -103,6 +113,8 @@ def _run_loop(train_config: TrainConfig, model_config: ModelConfig, state: Train
                "final_loss": log.loss_history[-1] if log.loss_history else None}
     log.finish(metrics)
     if train_config.checkpoint_dir:
+        if hasattr(state.optimizer, "sync_full_state"):
+            state.optimizer.sync_full_state()
         save_checkpoint(os.path.join(train_config.checkpoint_dir, "final.npz"), state.engine.store, mesh, state.step,
                         {"strategy": strategy})
     return metrics
