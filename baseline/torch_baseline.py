@@ -1,0 +1,106 @@
+"""Stand-in "library kernels only" baseline: the same GPT, data shapes and optimizer written in plain
+PyTorch — cuBLAS GEMMs (nn.Linear), SDPA flash attention, F.layer_norm / F.gelu / F.cross_entropy, fused
+torch.optim.AdamW, clip_grad_norm_, NCCL all-reduce through DistributedDataParallel — bf16 autocast with fp32
+master weights.  It shares NO code with the product path (none of this repo's kernels, engine or models) and
+exists only to be measured on the same box, because the reference's own JAX build cannot be installed offline.
+
+    python baseline/torch_baseline.py [--steps 50] [--warmup 5] [--compile-off]
+    torchrun --nproc-per-node N baseline/torch_baseline.py     (data parallel, batch 8 per rank)
+Prints one JSON line with device-timed (CUDA events, max over ranks) tokens/s.
+"""
+import argparse
+import json
+import os
+
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+import torch.nn.functional as F
+
+
+class Block(nn.Module):
+    def __init__(self, d, h, f):
+        super().__init__()
+        self.h = h
+        self.ln1, self.ln2 = nn.LayerNorm(d, eps=1e-6), nn.LayerNorm(d, eps=1e-6)
+        self.qkv, self.out = nn.Linear(d, 3 * d), nn.Linear(d, d)
+        self.fc1, self.fc2 = nn.Linear(d, f), nn.Linear(f, d)
+
+    def forward(self, x):
+        B, T, D = x.shape
+        q, k, v = self.qkv(self.ln1(x)).view(B, T, 3, self.h, D // self.h).permute(2, 0, 3, 1, 4)
+        a = F.scaled_dot_product_attention(q, k, v, is_causal=True).transpose(1, 2).reshape(B, T, D)
+        x = x + self.out(a)
+        return x + self.fc2(F.gelu(self.fc1(self.ln2(x)), approximate="tanh"))
+
+
+class GPT(nn.Module):
+    def __init__(self, V=50258, d=512, L=12, h=16, f=2048, T=512, p=0.1):
+        super().__init__()
+        self.wte, self.wpe, self.drop = nn.Embedding(V, d), nn.Embedding(T, d), nn.Dropout(p)
+        self.blocks = nn.ModuleList(Block(d, h, f) for _ in range(L))
+        self.lnf, self.head = nn.LayerNorm(d, eps=1e-6), nn.Linear(d, V)
+
+    def forward(self, x, y):
+        h = self.drop(self.wte(x) + self.wpe(torch.arange(x.shape[1], device=x.device))[None])
+        for b in self.blocks:
+            h = b(h)
+        logits = self.head(self.lnf(h))
+        return F.cross_entropy(logits.float().view(-1, logits.shape[-1]), y.reshape(-1))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--batch", type=int, default=8)
+    args = ap.parse_args()
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", 0)))
+    dev = torch.device("cuda")
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    torch.manual_seed(0)
+    model = GPT().to(dev)
+    net = nn.parallel.DistributedDataParallel(model, device_ids=[dev.index]) if world > 1 else model
+    opt = torch.optim.AdamW(model.parameters(), lr=3e-4, weight_decay=0.1, eps=1e-8, fused=True)
+    T = 512
+    g = torch.Generator(device=dev).manual_seed(rank)
+
+    def step():
+        tok = torch.randint(0, 50257, (args.batch, T + 1), device=dev, generator=g)
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            loss = net(tok[:, :-1], tok[:, 1:])
+        loss.backward()
+        torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)
+        opt.step()
+        opt.zero_grad(set_to_none=True)
+        return loss
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        loss = step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = ms.item()
+    if rank == 0:
+        print(json.dumps({"impl": "torch-eager stand-in baseline (cuBLAS + SDPA + fused AdamW + NCCL DDP)",
+                          "metric": "training throughput, tokens/s (whole job), DP", "n_gpus": world,
+                          "value": args.batch * world * T * args.steps / (ms / 1e3), "unit": "tokens/s",
+                          "ms_per_step": ms / args.steps, "steps": args.steps, "dtype": "bf16 autocast",
+                          "loss_last": float(loss)}))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -144,6 +144,13 @@ def run(args) -> dict | None:
         ms_e2e = mesh.max_over_ranks(ms_e2e)
     gpu_launches = native.launches() - launches_before
 
+    opt = state.optimizer
+    comm_path = {"dp": ("symmetric-memory reduce-scatter + sharded AdamW + all-gather ("
+                        + ("multimem/NVLS" if getattr(opt, "uses_multicast", False) else "peer loads/stores") + ")")
+                 if type(opt).__name__ == "FusedShardedStep" else ("NCCL bucketed all-reduce" if dp > 1 else "none"),
+                 "tp": ("GEMM epilogue multimem.red all-reduce" if getattr(state.engine, "tp_hooks", None) is not None
+                        else ("GEMM + NCCL all-reduce" if tp > 1 else "none")),
+                 "pp": "NCCL send/recv, one communicator per direction" if pp > 1 else "none"}
     tps = tokens_per_step * args.steps / (ms_dev / 1e3)
     tps_e2e = tokens_per_step * args.steps / (ms_e2e / 1e3)
     # bytes actually copied host->device per step over the whole job: every DP/TP rank stages its own x and y;
@@ -161,7 +168,7 @@ def run(args) -> dict | None:
                    "parallelism": f"{strategy}{world}", "optimizer": "clip_by_global_norm(1.0)+AdamW(3e-4, wd 0.1)",
                    "l2": "no explicit flush: per-step working set (~3 GB/rank) >> 126 MB L2",
                    "backend": state.engine.backend, "cuda_graph": bool(tc.cuda_graph and state.engine.backend == "native"),
-                   "fused_comm": tc.fused_comm},
+                   "fused_comm": tc.fused_comm, "comm_path": comm_path},
         "e2e": {"value": tps_e2e, "unit": "tokens/s", "ms_per_step": ms_e2e / args.steps,
                 "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4 * world},
         "gpu_launches": int(gpu_launches),  # rank 0, both timed regions (2K steps)

@@ -188,33 +188,36 @@ class ParamStore:
 # ----------------------------------------------------------------------------------------------------------
 # Initialisation (Flax defaults, SURVEY.md §2.6 "Init" column)
 # ----------------------------------------------------------------------------------------------------------
-def _gen(seed: int, *key) -> torch.Generator:
+def _gen(seed: int, device, *key) -> torch.Generator:
     h = zlib.crc32(repr(key).encode())
-    g = torch.Generator(device="cpu")
+    g = torch.Generator(device=device)
     g.manual_seed((seed * 1000003 + h) % (2 ** 63 - 1))
     return g
 
 
 def _lecun_normal(shape, fan_in: int, g: torch.Generator) -> torch.Tensor:
     std = math.sqrt(1.0 / fan_in) / 0.87962566103423978  # truncated-normal variance correction (jax)
-    t = torch.empty(shape, dtype=torch.float32)
+    t = torch.empty(shape, dtype=torch.float32, device=g.device)
     torch.nn.init.trunc_normal_(t, mean=0.0, std=std, a=-2 * std, b=2 * std, generator=g)
     return t
 
 
-def init_logical_leaf(cfg: ModelConfig, path: str, layer: int | None, seed: int, key_prefix=()) -> torch.Tensor:
-    """One logical (unsharded, unpadded) leaf — for stacked leaves, the slice of layer ``layer``."""
+def init_logical_leaf(cfg: ModelConfig, path: str, layer: int | None, seed: int, key_prefix=(),
+                      device="cpu") -> torch.Tensor:
+    """One logical (unsharded, unpadded) leaf — for stacked leaves, the slice of layer ``layer``.  The random
+    stream depends on (seed, path, layer) and on the DEVICE TYPE the generator runs on: every rank of a job
+    draws identical values, CPU and CUDA jobs draw different (equally distributed) ones."""
     D, F, V, T = cfg.d_model, cfg.d_ff, cfg.vocab_size, cfg.max_seq_len
-    g = _gen(seed, *key_prefix, path, layer)
+    g = _gen(seed, device, *key_prefix, path, layer)
     if path == "wte/embedding":
-        return torch.randn((V, D), generator=g) / math.sqrt(D)
+        return torch.randn((V, D), generator=g, device=g.device) / math.sqrt(D)
     if path == "wpe/embedding":
-        return torch.randn((T, D), generator=g) / math.sqrt(D)
+        return torch.randn((T, D), generator=g, device=g.device) / math.sqrt(D)
     if path.endswith("/scale"):
-        return torch.ones(D)
+        return torch.ones(D, device=g.device)
     if path.endswith("/bias"):
         n = {f"{MLP_}/fc1/bias": F, "lm_head/bias": V}.get(path, D)
-        return torch.zeros(n)
+        return torch.zeros(n, device=g.device)
     if path.endswith("fc1/kernel"):
         return _lecun_normal((D, F), D, g)
     if path.endswith("fc2/kernel"):
@@ -236,12 +239,14 @@ def init_params(store: ParamStore, seed: int, pp_stage_keys: bool = False, stage
     Dl, Fl, Vl = lo.d_local, lo.ff_local, lo.vocab_local
     p = store.p
 
+    dev = store.device
+
     def leaf(path, layer=None):
         if pp_stage_keys and layer is not None:
-            return init_logical_leaf(cfg, path, layer - lo.layer_start, seed, key_prefix=("pp-stage", stage_index))
+            return init_logical_leaf(cfg, path, layer - lo.layer_start, seed, ("pp-stage", stage_index), dev)
         if pp_stage_keys:
-            return init_logical_leaf(cfg, path, None, seed, key_prefix=("pp",))
-        return init_logical_leaf(cfg, path, layer, seed)
+            return init_logical_leaf(cfg, path, None, seed, ("pp",), dev)
+        return init_logical_leaf(cfg, path, layer, seed, (), dev)
 
     def put(dst: torch.Tensor, src: torch.Tensor) -> None:
         dst.copy_(src.to(dst.device))
