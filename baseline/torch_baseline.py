@@ -56,8 +56,9 @@ def main():
     ap.add_argument("--batch", type=int, default=8)
     args = ap.parse_args()
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
-    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", 0)))
-    dev = torch.device("cuda")
+    local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     torch.manual_seed(0)

@@ -640,11 +640,343 @@ static int launch_gemm_persistent(const void* A, long long lda, const void* B, l
   return 0;
 }
 
+
+// =========================================================================================================
+// CTA-pair variant (cta_group::2): two CTAs on the two SMs of a TPC share one 256 x BN output tile.
+// Each CTA TMA-loads its own 128 rows of A and HALF of the B tile; the leader CTA's elected thread issues
+// tcgen05.mma.cta_group::2 (UMMA M = 256), which reads both CTAs' shared memory and writes 128 accumulator rows
+// into each CTA's tensor memory.  Per CTA and per MMA cycle only half the B bytes cross L2 -> SM and shared
+// memory, which is what lets a 4..6-stage ring cover the L2 latency at tensor-core rate (the 1-CTA kernel is
+// bound by bytes-in-flight: 34 % tensor-pipe activity on the lm_head GEMM, profiles/r1/ncu_gemm_persistent.md).
+//   full[s]       lives in the leader; both CTAs' TMA loads complete_tx on it (expect_tx = bytes of both CTAs)
+//   empty[s]      one per CTA; tcgen05.commit multicasts the arrival to both
+//   tmem_full[b]  one per CTA (commit multicast); tmem_empty[b] lives in the leader, 16 arrivals (8 epilogue warps x 2 CTAs)
+// Epilogue as in the persistent kernel, in 128-column halves (BN = 256 has two).
+// =========================================================================================================
+template <int BN>
+struct P2Smem {
+  static constexpr int A_BYTES = BM * BK * 2;             // this CTA's 128 rows of A
+  static constexpr int B_BYTES = (BN / 2) * BK * 2;       // this CTA's half of the B tile
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int HALF_BYTES = BM * 128;             // 128 rows x 64 bf16 (one TMA box)
+  static constexpr int OUT_BYTES = 2 * HALF_BYTES;        // staging for one 128-column half of the output
+  static constexpr int AUX_BYTES = (BN / 64) * HALF_BYTES;  // whole [128 x BN] aux tile / out2 staging
+  static constexpr int bytes(int stages) { return stages * STAGE_BYTES + OUT_BYTES + AUX_BYTES + 1024 + 256; }
+};
+
+template <bool A_MN, bool B_MN, int BN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(PG_THREADS)
+gemm_2cta_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                 const __grid_constant__ CUtensorMap tma_out, const __grid_constant__ CUtensorMap tma_out2,
+                 const __grid_constant__ CUtensorMap tma_aux, int M, int N, int K, int m_blocks /* of 256 rows */,
+                 int n_blocks, int splits, int kb_per_split, int num_stages, GemmEpi epi) {
+  using S = P2Smem<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* stage_out = smem + num_stages * S::STAGE_BYTES;
+  uint8_t* stage_aux = stage_out + S::OUT_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(stage_aux + S::AUX_BYTES);
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = bars + PG_STAGE_MAX;
+  uint64_t* tmem_full = bars + 2 * PG_STAGE_MAX;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint64_t* aux_full = tmem_empty + 2;
+  uint64_t* aux_empty = aux_full + 1;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(aux_empty + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t cta = cluster_ctarank();  // 0 = leader
+  const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+  const int total_kb = (K + BK - 1) / BK;
+  const int tiles_mn = m_blocks * n_blocks;
+  const int total_tiles = tiles_mn * splits;
+  const int mode = epi.mode;
+  const bool bf16_out = mode <= EPI_DGELU;
+  const bool use_aux = (mode == EPI_BIAS_RESIDUAL || mode == EPI_DGELU);
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tma_a);
+    tma_prefetch_desc(&tma_b);
+    if (bf16_out) tma_prefetch_desc(&tma_out);
+    for (int s = 0; s < num_stages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&tmem_full[b], 1);
+      mbar_init(&tmem_empty[b], 16);  // 8 epilogue warps of each CTA (used in the leader only)
+    }
+    mbar_init(aux_full, 1);
+    mbar_init(aux_empty, 8);
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc_2sm(tmem_ptr_smem, 2 * BN);
+    tmem_relinquish_2sm();
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();  // the peer's barriers are initialised before anything may arrive on them remotely
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp == 0) {
+    // ------------------------------ TMA producer (both CTAs) ------------------------------
+    if (elect_one()) {
+      uint32_t kit = 0;
+      int it = 0;
+      for (int tile = pair; tile < total_tiles; tile += num_pairs, ++it) {
+        const int split = tile / tiles_mn, mn = tile % tiles_mn;
+        const int m_blk = mn % m_blocks, n_blk = mn / m_blocks;
+        const int row0 = m_blk * 256 + (int)cta * BM;       // this CTA's rows of A / of the output
+        const int bcol0 = n_blk * BN + (int)cta * (BN / 2);  // this CTA's half of the B tile
+        const int kb_begin = split * kb_per_split;
+        const int nkb = min(total_kb, kb_begin + kb_per_split) - kb_begin;
+        if (use_aux) {
+          mbar_wait(aux_empty, (it & 1) ^ 1);
+          mbar_expect_tx(aux_full, S::AUX_BYTES);
+#pragma unroll
+          for (int hf = 0; hf < BN / 64; ++hf)
+            tma_load_2d(stage_aux + hf * S::HALF_BYTES, &tma_aux, aux_full, n_blk * BN + hf * 64, row0);
+        }
+        for (int i = 0; i < nkb; ++i, ++kit) {
+          const int s = kit % num_stages;
+          const uint32_t ph = (kit / num_stages) & 1;
+          mbar_wait(&empty_bar[s], ph ^ 1);
+          uint8_t* sa = smem + s * S::STAGE_BYTES;
+          uint8_t* sb = sa + S::A_BYTES;
+          const uint32_t full_leader = mapa_shared(smem_u32(&full_bar[s]), 0);
+          if (cta == 0) mbar_expect_tx(&full_bar[s], 2 * S::STAGE_BYTES);  // bytes of both CTAs
+          const int k0 = (kb_begin + i) * BK;
+          if (A_MN) {
+#pragma unroll
+            for (int j = 0; j < BM / 64; ++j) tma_load_2d_2sm(sa + j * (BK * 128), &tma_a, full_leader, row0 + j * 64, k0);
+          } else {
+            tma_load_2d_2sm(sa, &tma_a, full_leader, k0, row0);
+          }
+          if (B_MN) {
+#pragma unroll
+            for (int j = 0; j < BN / 128; ++j) tma_load_2d_2sm(sb + j * (BK * 128), &tma_b, full_leader, bcol0 + j * 64, k0);
+          } else {
+            tma_load_2d_2sm(sb, &tma_b, full_leader, k0, bcol0);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------ MMA issuer (leader CTA only) ------------------------------
+    if (cta == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(256, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+      constexpr uint32_t A_LBO = A_MN ? BK * 128 : 16, A_STEP = A_MN ? 2048 : 32;
+      constexpr uint32_t B_LBO = B_MN ? BK * 128 : 16, B_STEP = B_MN ? 2048 : 32;
+      uint32_t kit = 0;
+      int it = 0;
+      for (int tile = pair; tile < total_tiles; tile += num_pairs, ++it) {
+        const int split = tile / tiles_mn;
+        const int kb_begin = split * kb_per_split;
+        const int nkb = min(total_kb, kb_begin + kb_per_split) - kb_begin;
+        const int buf = it & 1;
+        mbar_wait(&tmem_empty[buf], ((it >> 1) & 1) ^ 1);  // both CTAs' epilogues have drained this buffer
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + buf * BN;
+        for (int i = 0; i < nkb; ++i, ++kit) {
+          const int s = kit % num_stages;
+          const uint32_t ph = (kit / num_stages) & 1;
+          mbar_wait(&full_bar[s], ph);
+          tc_fence_after();
+          if (elect_one()) {
+            const uint32_t sa = smem_u32(smem + s * S::STAGE_BYTES);
+            const uint32_t sb = sa + S::A_BYTES;
+#pragma unroll
+            for (int k = 0; k < BK / 16; ++k) {
+              const uint64_t da = make_smem_desc(sa + k * A_STEP, A_LBO, 1024, SWZ_128B);
+              const uint64_t db = make_smem_desc(sb + k * B_STEP, B_LBO, 1024, SWZ_128B);
+              umma_bf16_2sm(tmem_d, da, db, idesc, (i > 0 || k > 0) ? 1u : 0u);
+            }
+            umma_commit_2sm(&empty_bar[s], 0x3);
+            if (i == nkb - 1) umma_commit_2sm(&tmem_full[buf], 0x3);
+          }
+          __syncwarp();
+        }
+      }
+    }
+  } else {
+    // ------------------------------ epilogue (warps 2..9 of both CTAs) ------------------------------
+    const int q = warp & 3;
+    const int chalf = (warp - 2) >> 2;
+    const int row = q * 32 + lane;
+    const bool store_leader = (threadIdx.x == 64);
+    const float alpha = epi.alpha;
+    int it = 0;
+    for (int tile = pair; tile < total_tiles; tile += num_pairs, ++it) {
+      const int mn = tile % tiles_mn;
+      const int m_blk = mn % m_blocks, n_blk = mn / m_blocks;
+      const int buf = it & 1;
+      const int row0 = m_blk * 256 + (int)cta * BM;
+      const long long gm = (long long)row0 + row;
+      const bool row_ok = gm < M;
+      mbar_wait(&tmem_full[buf], (it >> 1) & 1);
+      tc_fence_after();
+      if (use_aux) mbar_wait(aux_full, it & 1);
+      const uint32_t tmem_d = tmem_base + buf * BN + ((uint32_t)(q * 32) << 16);
+#pragma unroll 1
+      for (int hp = 0; hp < BN / 128; ++hp) {  // 128-column halves of the tile
+        if (bf16_out) {
+          if (store_leader) tma_store_wait_read();  // previous stores have finished reading the staging tiles
+          epi_bar_sync();
+        }
+#pragma unroll 1
+        for (int c = chalf * 2; c < chalf * 2 + 2; ++c) {  // two 32-column chunks per warp and half
+          uint32_t r[32];
+          tmem_ld_32x32b_x32(tmem_d + hp * 128 + c * 32, r);
+          tmem_ld_wait();
+          const int n0 = n_blk * BN + hp * 128 + c * 32;
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            const int n = n0 + g * 8;
+            float v[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]) * alpha;
+            if (epi.bias != nullptr && mode != EPI_ATOMIC_F32 && mode != EPI_DGELU && n < N) {
+              const uint4 bb = *reinterpret_cast<const uint4*>(epi.bias + n);
+              const uint32_t bw[4] = {bb.x, bb.y, bb.z, bb.w};
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const float2 f = unpack_bf16x2(bw[j]);
+                v[2 * j] += f.x;
+                v[2 * j + 1] += f.y;
+              }
+            }
+            if (!bf16_out) {
+              if (!row_ok || n >= N) continue;
+              float* o = reinterpret_cast<float*>(epi.out) + gm * epi.ldo + n;
+              if (mode == EPI_ATOMIC_F32) {
+                red_add_v4_f32(o, v[0], v[1], v[2], v[3]);
+                red_add_v4_f32(o + 4, v[4], v[5], v[6], v[7]);
+              } else {
+                *reinterpret_cast<float4*>(o) = make_float4(v[0], v[1], v[2], v[3]);
+                *reinterpret_cast<float4*>(o + 4) = make_float4(v[4], v[5], v[6], v[7]);
+              }
+              continue;
+            }
+            // offsets inside the out staging (one 128-column half) and inside the whole-tile aux / out2 staging
+            const uint32_t off = (uint32_t)(c >> 1) * S::HALF_BYTES + swizzle_offset<3>(row * 128 + ((c & 1) * 4 + g) * 16);
+            const uint32_t aoff = (uint32_t)(hp * 2) * S::HALF_BYTES + off;
+            if (use_aux) {
+              const uint4 a = *reinterpret_cast<const uint4*>(stage_aux + aoff);
+              const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const float2 f = unpack_bf16x2(aw[j]);
+                if (mode == EPI_BIAS_RESIDUAL) {
+                  v[2 * j] += f.x;
+                  v[2 * j + 1] += f.y;
+                } else {
+                  v[2 * j] *= gelu_tanh_grad(f.x);
+                  v[2 * j + 1] *= gelu_tanh_grad(f.y);
+                }
+              }
+            }
+            *reinterpret_cast<uint4*>(stage_out + off) = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]),
+                                                                   pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+            if (mode == EPI_BIAS_GELU) {
+              *reinterpret_cast<uint4*>(stage_aux + aoff) = make_uint4(
+                  pack_bf16x2(gelu_tanh(v[0]), gelu_tanh(v[1])), pack_bf16x2(gelu_tanh(v[2]), gelu_tanh(v[3])),
+                  pack_bf16x2(gelu_tanh(v[4]), gelu_tanh(v[5])), pack_bf16x2(gelu_tanh(v[6]), gelu_tanh(v[7])));
+            }
+          }
+        }
+        if (hp == BN / 128 - 1) {
+          // accumulator buffer drained: tell the leader's MMA warp (and free the aux tile for the producer)
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) {
+            mbar_arrive_cluster(mapa_shared(smem_u32(&tmem_empty[buf]), 0));
+            if (use_aux) mbar_arrive(aux_empty);
+          }
+        }
+        if (bf16_out) {
+          fence_proxy_async_smem();
+          epi_bar_sync();
+          if (store_leader) {
+#pragma unroll
+            for (int hf = 0; hf < 2; ++hf) {
+              const int col = n_blk * BN + hp * 128 + hf * 64;
+              tma_store_2d(&tma_out, stage_out + hf * S::HALF_BYTES, col, row0);
+              if (mode == EPI_BIAS_GELU) tma_store_2d(&tma_out2, stage_aux + (hp * 2 + hf) * S::HALF_BYTES, col, row0);
+            }
+            tma_store_commit();
+          }
+        }
+      }
+    }
+    if (bf16_out && store_leader) tma_store_wait_all();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();  // neither CTA leaves (or frees TMEM) while its peer may still touch its smem / barriers
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc_2sm(tmem_base, 2 * BN);
+  }
+}
+
+template <bool A_MN, bool B_MN, int BN>
+static int launch_gemm_2cta(const void* A, long long lda, const void* B, long long ldb, int M, int N, int K, int splits,
+                            int stages, const GemmEpi& epi, cudaStream_t stream) {
+  using S = P2Smem<BN>;
+  CUtensorMap ta, tb, tout, tout2, taux;
+  int rc;
+  if (A_MN) rc = make_tmap_2d_bf16(&ta, A, K, M, lda, BK, 64, CU_TENSOR_MAP_SWIZZLE_128B);
+  else rc = make_tmap_2d_bf16(&ta, A, M, K, lda, BM, BK, CU_TENSOR_MAP_SWIZZLE_128B);
+  if (rc) return rc;
+  if (B_MN) rc = make_tmap_2d_bf16(&tb, B, K, N, ldb, BK, 64, CU_TENSOR_MAP_SWIZZLE_128B);
+  else rc = make_tmap_2d_bf16(&tb, B, N, K, ldb, BN / 2, BK, CU_TENSOR_MAP_SWIZZLE_128B);
+  if (rc) return rc;
+  tout = ta;
+  tout2 = ta;
+  taux = ta;
+  if (epi.mode <= EPI_DGELU) {
+    if ((rc = make_tmap_2d_bf16(&tout, epi.out, M, N, epi.ldo, BM, 64, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+    if (epi.mode == EPI_BIAS_GELU &&
+        (rc = make_tmap_2d_bf16(&tout2, epi.out2, M, N, epi.ldo2, BM, 64, CU_TENSOR_MAP_SWIZZLE_128B)))
+      return rc;
+    if ((epi.mode == EPI_BIAS_RESIDUAL || epi.mode == EPI_DGELU) &&
+        (rc = make_tmap_2d_bf16(&taux, epi.aux, M, N, epi.ld_aux, BM, 64, CU_TENSOR_MAP_SWIZZLE_128B)))
+      return rc;
+  }
+  const int total_kb = (K + BK - 1) / BK;
+  if (splits < 1) splits = 1;
+  if (splits > total_kb) splits = total_kb;
+  const int kb_per_split = (total_kb + splits - 1) / splits;
+  splits = (total_kb + kb_per_split - 1) / kb_per_split;
+  if (stages < 2) stages = 2;
+  if (stages > PG_STAGE_MAX) stages = PG_STAGE_MAX;
+  while (S::bytes(stages) > 227 * 1024) --stages;
+  const int smem_bytes = S::bytes(stages);
+  auto kern = gemm_2cta_kernel<A_MN, B_MN, BN>;
+  static bool configured = false;
+  if (!configured) {
+    DTC_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    configured = true;
+  }
+  const int m_blocks = (M + 255) / 256, n_blocks = (N + BN - 1) / BN;
+  const int total_tiles = m_blocks * n_blocks * splits;
+  const int max_pairs = num_sms() / 2;
+  const int pairs = total_tiles < max_pairs ? total_tiles : max_pairs;
+  kern<<<2 * pairs, PG_THREADS, smem_bytes, stream>>>(ta, tb, tout, tout2, taux, M, N, K, m_blocks, n_blocks, splits,
+                                                      kb_per_split, stages, epi);
+  DTC_CHECK_LAUNCH();
+  return 0;
+}
+
 }  // namespace dtc
 
 using namespace dtc;
 
-static int g_gemm_impl = 0;  // 0 = persistent kernel (default), 1 = one-tile-per-CTA kernel
+static int g_gemm_impl = 0;  // 0 = persistent 1-CTA kernel, 1 = one-tile-per-CTA kernel, 2 = CTA-pair 256x128, 3 = CTA-pair, 256x256 where it fits
 // Tuning / A-B switch used by tools/gemm_bench.py.
 extern "C" int dtc_gemm_set_impl(int impl) {
   g_gemm_impl = impl;
@@ -685,6 +1017,25 @@ extern "C" int dtc_gemm_bf16(const void* A, long long lda, int a_mn_major, const
   static const bool env_v1 = getenv("DTC_GEMM_V1") != nullptr;  // A/B switch: one-tile-per-CTA kernel
   const bool use_v1 = (env_v1 || g_gemm_impl == 1) && epi_mode != EPI_MC_RED_BF16;
   if (epi_mode == EPI_MC_RED_BF16 && block_n == 256) block_n = 128;
+  // CTA-pair kernel: needs >= 256 rows; 256-wide tiles when that still leaves enough pair-tiles to fill the GPU
+  // default policy (impl 0): the CTA-pair kernel pays off on the big GEMMs (lm_head: +27 % on dgrad / wgrad,
+  // profiles/r1/gemm_microbench.txt); the layer GEMMs of this model are launch/latency-bound and stay 1-CTA
+  const bool big = 2.0 * M * N * (double)K >= 1e11;
+  const bool want_2cta = (g_gemm_impl == 2 || g_gemm_impl == 3 || (g_gemm_impl == 0 && big && !env_v1)) &&
+                         epi_mode != EPI_MC_RED_BF16 && M >= 256 && N >= 128;
+  if (want_2cta) {
+    const long long tiles256 = (long long)((M + 255) / 256) * ((N + 255) / 256) * (splits > 1 ? splits : 1);
+    const bool wide = (block_n == 256) || (g_gemm_impl == 3 && block_n == 0 && N % 256 == 0 && tiles256 >= 64);
+    if (stages == 0) stages = PG_STAGE_MAX;
+#define DTC_2CTA_DISPATCH(AMN, BMN)                                                                               \
+  if (wide) return launch_gemm_2cta<AMN, BMN, 256>(A, lda, B, ldb, M, N, K, splits, stages, epi, stream);         \
+  return launch_gemm_2cta<AMN, BMN, 128>(A, lda, B, ldb, M, N, K, splits, stages, epi, stream);
+    if (!a_mn_major && !b_mn_major) { DTC_2CTA_DISPATCH(false, false) }
+    if (!a_mn_major && b_mn_major) { DTC_2CTA_DISPATCH(false, true) }
+    if (a_mn_major && !b_mn_major) { DTC_2CTA_DISPATCH(true, false) }
+    DTC_2CTA_DISPATCH(true, true)
+#undef DTC_2CTA_DISPATCH
+  }
   if (!use_v1 && block_n != 256) {
     if (stages == 0) stages = PG_STAGE_MAX;
 #define DTC_PGEMM_DISPATCH(AMN, BMN)                                                                              \

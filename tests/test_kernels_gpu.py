@@ -90,6 +90,33 @@ def test_gemm_strided_views_and_vocab_shape():
     assert out[:, V:].abs().max().item() == 0.0
 
 
+@pytest.mark.parametrize("impl", [1, 2, 3])
+def test_gemm_kernel_variants_agree(impl):
+    """one-tile-per-CTA (1), CTA-pair 256x128 (2) and CTA-pair 256x256 (3) kernels against the fp32 reference."""
+    lib = native.load()
+    try:
+        lib.dtc_gemm_set_impl(impl)
+        M, K, N = 1024, 320, 768
+        x, w, bias, res = randn(M, K), randn(K, N, scale=0.1), randn(N), randn(M, N)
+        assert rel_err(Fn.gemm(x, w, b_mn=True, bias=bias), R.gemm(x, w, b_mn=True, bias=bias)) < 1e-2
+        assert rel_err(Fn.gemm(x, w, b_mn=True, bias=bias, epi="bias_residual", aux=res),
+                       R.gemm(x, w, b_mn=True, bias=bias, epi="bias_residual", aux=res)) < 1e-2
+        pre, act = Fn.gemm(x, w, b_mn=True, bias=bias, epi="bias_gelu")
+        wpre, wact = R.gemm(x, w, b_mn=True, bias=bias, epi="bias_gelu")
+        assert rel_err(pre, wpre) < 1e-2 and rel_err(act, wact) < 1e-2
+        dy, f1 = randn(M, N), randn(M, K)
+        assert rel_err(Fn.gemm(dy, w, epi="dgelu", aux=f1), R.gemm(dy, w, epi="dgelu", aux=f1)) < 1e-2   # K-major B
+        acc = torch.randn(K, N, device="cuda")
+        want = R.gemm(x, dy, a_mn=True, b_mn=True, epi="atomic_f32", out=acc.clone())
+        Fn.gemm(x, dy, a_mn=True, b_mn=True, epi="atomic_f32", out=acc, splits=4)
+        assert rel_err(acc, want) < 1e-2
+        # ragged edges: M, N not multiples of the pair tile
+        a2, b2 = randn(600, 200), randn(200, 392, scale=0.1)
+        assert rel_err(Fn.gemm(a2, b2, b_mn=True), R.gemm(a2, b2, b_mn=True)) < 1e-2
+    finally:
+        lib.dtc_gemm_set_impl(0)
+
+
 # ------------------------------------------------------------------------------------------- attention
 @pytest.mark.parametrize("B,H,T,hd", [(2, 4, 256, 32), (1, 2, 512, 32), (2, 2, 256, 64), (1, 16, 128, 32)])
 def test_flash_attention_fwd_bwd(B, H, T, hd):

@@ -66,11 +66,14 @@ def main():
         peak = json.load(open(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json")))["bf16_tflops_sustained"]
     except Exception:
         pass
-    print(f"{'gemm':22s} {'persistent us':>14s} {'TFLOP/s':>9s} {'frac':>6s} | {'1-tile/CTA us':>14s} {'TFLOP/s':>9s}")
+    print(f"{'gemm':22s} {'1-CTA persistent us':>20s} {'TFLOP/s':>8s} {'frac':>5s} | {'pair 256x128 us':>15s} {'TFLOP/s':>8s} | "
+          f"{'pair 256x256 us':>15s} {'TFLOP/s':>8s} {'frac':>5s}")
     for name, ash, bsh, a_mn, b_mn, epi, splits in SHAPES:
         u2, t2 = run(name, ash, bsh, a_mn, b_mn, epi, splits, 0)
-        u1, t1 = run(name, ash, bsh, a_mn, b_mn, epi, splits, 1)
-        line = f"{name:22s} {u2:14.1f} {t2:9.1f} {t2 / peak:6.2f} | {u1:14.1f} {t1:9.1f}"
+        u1, t1 = run(name, ash, bsh, a_mn, b_mn, epi, splits, 2)
+        u3, t3 = run(name, ash, bsh, a_mn, b_mn, epi, splits, 3)
+        line = (f"{name:22s} {u2:20.1f} {t2:8.1f} {t2 / peak:5.2f} | {u1:15.1f} {t1:8.1f} | {u3:15.1f} {t3:8.1f} "
+                f"{t3 / peak:5.2f}")
         if "--torch" in sys.argv and not a_mn and epi == "store":
             a = torch.randn(ash, device="cuda").to(torch.bfloat16)
             b = torch.randn(bsh, device="cuda").to(torch.bfloat16)
@@ -85,6 +88,7 @@ def main():
             torch.cuda.synchronize()
             line += f" | cuBLAS {e0.elapsed_time(e1) * 50:.1f} us (L2-warm)"
         print(line, flush=True)
+    native.load().dtc_gemm_set_impl(0)
 
 
 if __name__ == "__main__":

@@ -1,0 +1,39 @@
+"""Small single-GPU target for `ncu --set full`: a few launches of the hot kernels on the model's shapes.
+Usage: python tools/profile_target.py [gemm|attn|all]"""
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from distributed_training_compare_jax_b200.ops import functional as Fn  # noqa: E402
+
+what = sys.argv[1] if len(sys.argv) > 1 else "all"
+M, D, F, V = 4096, 512, 2048, 50304
+bf = torch.bfloat16
+
+
+def r(*s, scale=1.0):
+    return (torch.randn(*s, device="cuda") * scale).to(bf)
+
+
+if what in ("gemm", "all"):
+    x, wqkv, bq = r(M, D), r(D, 3 * D, scale=0.05), r(3 * D)
+    w1, b1 = r(D, F, scale=0.05), r(F)
+    wlm = r(D, V, scale=0.05)
+    res = r(M, D)
+    w2, b2, g = r(F, D, scale=0.05), r(D), r(M, F)
+    for _ in range(3):
+        Fn.gemm(x, wqkv, b_mn=True, bias=bq)                                   # qkv fwd
+        Fn.gemm(x, w1, b_mn=True, bias=b1, epi="bias_gelu")                    # fc1 fwd + GELU
+        Fn.gemm(g, w2, b_mn=True, bias=b2, epi="bias_residual", aux=res)       # fc2 fwd + residual
+        Fn.gemm(x, wlm, b_mn=True)                                             # lm_head fwd
+if what in ("attn", "all"):
+    B, H, T, hd = 8, 16, 512, 32
+    qkv = r(B * T, 3 * H * hd)
+    d_o = r(B * T, H * hd)
+    for _ in range(3):
+        out, lse2 = Fn.flash_attn_fwd(qkv, B, H, T, hd)
+        Fn.flash_attn_bwd(qkv, out, d_o, lse2, B, H, T, hd)
+torch.cuda.synchronize()
+print("profile target done")
