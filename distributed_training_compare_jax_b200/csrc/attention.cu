@@ -84,6 +84,8 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
+  pdl_launch_dependents();  // PDL: only after this CTA owns its TMEM (a dependent may not allocate first)
+  pdl_wait();               // inputs come from the previous kernel: no global access before it has completed
   const uint32_t tmem_s = tmem_base, tmem_pv = tmem_base + 128;
   const uint32_t lane_sel = (uint32_t)(warp * 32) << 16;
 
@@ -213,6 +215,8 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
 template <int HD>
 __global__ void attn_bwd_prep_kernel(const bf16* __restrict__ o, long long ldo, const bf16* __restrict__ d_o,
                                      long long lddo, float* __restrict__ delta, int M, int T, int H) {
+  pdl_launch_dependents();  // PDL: let the next kernel's prologue overlap this kernel
+  pdl_wait();               // ... and do not touch global memory before the previous kernel has completed
   constexpr int TPR = HD / 8;
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const long long item = idx / TPR;
@@ -291,6 +295,8 @@ flash_attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
+  pdl_launch_dependents();  // PDL: only after this CTA owns its TMEM (a dependent may not allocate first)
+  pdl_wait();               // inputs come from the previous kernel: no global access before it has completed
   const uint32_t tm_st = tmem_base, tm_dpt = tmem_base + 128, tm_dk = tmem_base + 256, tm_dv = tmem_base + 256 + HD,
                  tm_dq = tmem_base + 256 + 2 * HD;
   const uint32_t lane_sel = (uint32_t)(warp * 32) << 16;
@@ -476,7 +482,7 @@ static int launch_fwd(const void* q, const void* k, const void* v, long long ld,
   }
   const float scale = 1.f / sqrtf((float)HD);
   dim3 grid(T / ATT_BLK, H, B);
-  kern<<<grid, 128, smem, stream>>>(tq, tk, tv, reinterpret_cast<bf16*>(out), ldo, lse2, T, H, scale * LOG2E);
+  DTC_CHECK_CUDA(dtc::launch(kern, grid, 128, smem, stream, tq, tk, tv, reinterpret_cast<bf16*>(out), ldo, lse2, T, H, scale * LOG2E));
   DTC_CHECK_LAUNCH();
   return 0;
 }
@@ -495,8 +501,8 @@ static int launch_bwd(const void* q, const void* k, const void* v, long long ld,
   if ((rc = attn_tmap<HD>(&tdo, d_o, M, H, lddo))) return rc;
   {
     const long long threads = M * H * (HD / 8);
-    attn_bwd_prep_kernel<HD><<<(int)((threads + 255) / 256), 256, 0, stream>>>(
-        reinterpret_cast<const bf16*>(o), ldo, reinterpret_cast<const bf16*>(d_o), lddo, delta, (int)M, T, H);
+    DTC_CHECK_CUDA(dtc::launch(attn_bwd_prep_kernel<HD>, (int)((threads + 255) / 256), 256, 0, stream, 
+        reinterpret_cast<const bf16*>(o), ldo, reinterpret_cast<const bf16*>(d_o), lddo, delta, (int)M, T, H));
     DTC_CHECK_LAUNCH();
   }
   const int smem = 6 * C::TILE_BYTES + 2 * C::P_BYTES + 4 * ATT_BLK * 4 + 1024 + 128;
@@ -508,8 +514,8 @@ static int launch_bwd(const void* q, const void* k, const void* v, long long ld,
   }
   const float scale = 1.f / sqrtf((float)HD);
   dim3 grid(T / ATT_BLK, H, B);
-  kern<<<grid, 128, smem, stream>>>(tq, tk, tv, tdo, lse2, delta, dq_accum, lddq, reinterpret_cast<bf16*>(dk),
-                                    reinterpret_cast<bf16*>(dv), lddkv, T, H, scale, scale * LOG2E);
+  DTC_CHECK_CUDA(dtc::launch(kern, grid, 128, smem, stream, tq, tk, tv, tdo, lse2, delta, dq_accum, lddq, reinterpret_cast<bf16*>(dk),
+                                    reinterpret_cast<bf16*>(dv), lddkv, T, H, scale, scale * LOG2E));
   DTC_CHECK_LAUNCH();
   return 0;
 }

@@ -62,6 +62,8 @@ DTC_DEVICE void flag_barrier(const PeerPtrs& flags, int rank, int world, int slo
 }
 
 __global__ void symm_barrier_kernel(PeerPtrs flags, int rank, int world, int slot) {
+  pdl_launch_dependents();  // PDL: let the next kernel's prologue overlap this kernel
+  pdl_wait();               // ... and do not touch global memory before the previous kernel has completed
   flag_barrier(flags, rank, world, slot, threadIdx.x);
 }
 
@@ -84,6 +86,8 @@ template <bool USE_MC>
 __global__ void __launch_bounds__(256)
 dp_reduce_scatter_kernel(float* __restrict__ local_grad, const float* __restrict__ mc_grad, PeerPtrs peers, int rank,
                          int world, long long off, long long n, float* __restrict__ partials) {
+  pdl_launch_dependents();  // PDL: let the next kernel's prologue overlap this kernel
+  pdl_wait();               // ... and do not touch global memory before the previous kernel has completed
   __shared__ float s[8];
   float acc = 0.f;
   const long long n4 = n >> 2;
@@ -117,6 +121,8 @@ dp_reduce_scatter_kernel(float* __restrict__ local_grad, const float* __restrict
 __global__ void __launch_bounds__(1024)
 dp_norm_exchange_kernel(const float* __restrict__ partials, int n_partials, PeerPtrs norm_slots, PeerPtrs flags, int rank,
                         int world, int slot, float max_norm, float* __restrict__ scalars, int* __restrict__ step) {
+  pdl_launch_dependents();  // PDL: let the next kernel's prologue overlap this kernel
+  pdl_wait();               // ... and do not touch global memory before the previous kernel has completed
   __shared__ float s[32];
   __shared__ float total;
   float v = 0.f;
@@ -151,6 +157,8 @@ dp_adamw_allgather_kernel(float* __restrict__ p, float* __restrict__ m, float* _
                           bf16* __restrict__ mc_compute, PeerPtrs compute_peers, int world, long long off, long long n,
                           long long total_n, const float* __restrict__ scalars, const int* __restrict__ step_ptr, float lr,
                           float b1, float b2, float eps, float wd) {
+  pdl_launch_dependents();  // PDL: let the next kernel's prologue overlap this kernel
+  pdl_wait();               // ... and do not touch global memory before the previous kernel has completed
   const float clip = scalars[1];
   const float t = (float)*step_ptr;
   const float bc1 = 1.f / (1.f - powf(b1, t));
@@ -214,7 +222,7 @@ extern "C" int dtc_symm_barrier(const unsigned long long* flag_ptrs, int rank, i
   PeerPtrs f;
   int rc = fill_peers(&f, flag_ptrs, world);
   if (rc) return rc;
-  symm_barrier_kernel<<<1, 32, 0, stream>>>(f, rank, world, slot);
+  DTC_CHECK_CUDA(dtc::launch(symm_barrier_kernel, 1, 32, 0, stream, f, rank, world, slot));
   DTC_CHECK_LAUNCH();
   return 0;
 }
@@ -236,10 +244,10 @@ extern "C" int dtc_dp_reduce_scatter(float* local_grad, unsigned long long mc_gr
   if (rc) return rc;
   const int blocks = dtc_dp_num_partials(n);
   if (mc_grad)
-    dp_reduce_scatter_kernel<true><<<blocks, 256, 0, stream>>>(local_grad, reinterpret_cast<const float*>(mc_grad), peers,
-                                                               rank, world, off, n, partials);
+    DTC_CHECK_CUDA(dtc::launch(dp_reduce_scatter_kernel<true>, blocks, 256, 0, stream, local_grad, reinterpret_cast<const float*>(mc_grad), peers,
+                                                               rank, world, off, n, partials));
   else
-    dp_reduce_scatter_kernel<false><<<blocks, 256, 0, stream>>>(local_grad, nullptr, peers, rank, world, off, n, partials);
+    DTC_CHECK_CUDA(dtc::launch(dp_reduce_scatter_kernel<false>, blocks, 256, 0, stream, local_grad, nullptr, peers, rank, world, off, n, partials));
   DTC_CHECK_LAUNCH();
   return 0;
 }
@@ -251,7 +259,7 @@ extern "C" int dtc_dp_norm_exchange(const float* partials, int n_partials, const
   int rc = fill_peers(&ns, norm_slot_ptrs, world);
   if (rc) return rc;
   if ((rc = fill_peers(&fl, flag_ptrs, world))) return rc;
-  dp_norm_exchange_kernel<<<1, 1024, 0, stream>>>(partials, n_partials, ns, fl, rank, world, slot, max_norm, scalars, step);
+  DTC_CHECK_CUDA(dtc::launch(dp_norm_exchange_kernel, 1, 1024, 0, stream, partials, n_partials, ns, fl, rank, world, slot, max_norm, scalars, step));
   DTC_CHECK_LAUNCH();
   return 0;
 }
@@ -268,12 +276,12 @@ extern "C" int dtc_dp_adamw_allgather(float* p, float* m, float* v, float* g, un
   if (blocks > 148 * 8) blocks = 148 * 8;
   if (blocks < 148) blocks = 148;  // the gradient clear covers the whole buffer
   if (mc_compute)
-    dp_adamw_allgather_kernel<true><<<(int)blocks, 256, 0, stream>>>(p, m, v, g, reinterpret_cast<bf16*>(mc_compute), peers,
+    DTC_CHECK_CUDA(dtc::launch(dp_adamw_allgather_kernel<true>, (int)blocks, 256, 0, stream, p, m, v, g, reinterpret_cast<bf16*>(mc_compute), peers,
                                                                       world, off, n, total_n, scalars, step_ptr, lr, b1, b2,
-                                                                      eps, wd);
+                                                                      eps, wd));
   else
-    dp_adamw_allgather_kernel<false><<<(int)blocks, 256, 0, stream>>>(p, m, v, g, nullptr, peers, world, off, n, total_n,
-                                                                       scalars, step_ptr, lr, b1, b2, eps, wd);
+    DTC_CHECK_CUDA(dtc::launch(dp_adamw_allgather_kernel<false>, (int)blocks, 256, 0, stream, p, m, v, g, nullptr, peers, world, off, n, total_n,
+                                                                       scalars, step_ptr, lr, b1, b2, eps, wd));
   DTC_CHECK_LAUNCH();
   return 0;
 }

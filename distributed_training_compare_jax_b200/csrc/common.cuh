@@ -32,7 +32,33 @@ void dtc_set_error(const char* fmt, ...);
   } while (0)
 #define DTC_CHECK_LAUNCH() DTC_CHECK_CUDA(cudaGetLastError())
 
+// Programmatic dependent launch (PDL): kernels are launched with the programmatic-stream-serialization attribute,
+// call pdl_launch_dependents() once their prologue can no longer conflict with a dependent's (TMEM-owning kernels:
+// after tcgen05.alloc) and pdl_wait() before their first global-memory access.  The launch latency and prologue
+// (barrier init, TMEM alloc, tensor-map fetch) of kernel N+1 then overlap the tail of kernel N; correctness is
+// unchanged because griddepcontrol.wait returns only after the previous grid has completed and flushed.
+// The attribute is opt-in (dtc_set_pdl(1) / DTC_PDL=1); without it the device-side instructions are no-ops.
+extern int g_dtc_pdl_enabled;
+
 namespace dtc {
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = g_dtc_pdl_enabled ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 // ----------------------------------------------------------------------------------------------
 // misc

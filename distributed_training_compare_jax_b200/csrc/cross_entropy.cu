@@ -125,6 +125,8 @@ DTC_DEVICE void block_row_grad(bf16* __restrict__ row, int V, int ld, float lse,
 __global__ void __launch_bounds__(CE_THREADS)
 ce_fwd_bwd_kernel(bf16* __restrict__ logits, long long ld, const int* __restrict__ labels, float* __restrict__ loss_rows,
                   int V, float gscale) {
+  pdl_launch_dependents();  // PDL: let the next kernel's prologue overlap this kernel
+  pdl_wait();               // ... and do not touch global memory before the previous kernel has completed
   __shared__ float s_red[34];
   bf16* row = logits + (long long)blockIdx.x * ld;
   int y = labels[blockIdx.x];
@@ -141,6 +143,8 @@ ce_fwd_bwd_kernel(bf16* __restrict__ logits, long long ld, const int* __restrict
 __global__ void __launch_bounds__(CE_THREADS)
 ce_stats_kernel(const bf16* __restrict__ logits, long long ld, const int* __restrict__ labels, float* __restrict__ stats,
                 int V_local, int vocab_start) {
+  pdl_launch_dependents();  // PDL: let the next kernel's prologue overlap this kernel
+  pdl_wait();               // ... and do not touch global memory before the previous kernel has completed
   __shared__ float s_red[34];
   const bf16* row = logits + (long long)blockIdx.x * ld;
   const RowStat st = block_row_stats(row, V_local, s_red);
@@ -155,6 +159,8 @@ ce_stats_kernel(const bf16* __restrict__ logits, long long ld, const int* __rest
 // Combine per-shard stats [n_shards, M, 3] into lse[M] and loss_rows[M].
 __global__ void ce_combine_kernel(const float* __restrict__ stats, int n_shards, int M, float* __restrict__ lse,
                                   float* __restrict__ loss_rows) {
+  pdl_launch_dependents();  // PDL: let the next kernel's prologue overlap this kernel
+  pdl_wait();               // ... and do not touch global memory before the previous kernel has completed
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= M) return;
   float m = -INFINITY, s = 0.f, tgt = 0.f;
@@ -172,6 +178,8 @@ __global__ void ce_combine_kernel(const float* __restrict__ stats, int n_shards,
 __global__ void __launch_bounds__(CE_THREADS)
 ce_grad_kernel(bf16* __restrict__ logits, long long ld, const int* __restrict__ labels, const float* __restrict__ lse,
                int V_local, int vocab_start, float gscale) {
+  pdl_launch_dependents();  // PDL: let the next kernel's prologue overlap this kernel
+  pdl_wait();               // ... and do not touch global memory before the previous kernel has completed
   bf16* row = logits + (long long)blockIdx.x * ld;
   block_row_grad(row, V_local, (int)ld, lse[blockIdx.x], labels[blockIdx.x] - vocab_start, gscale);
 }
@@ -179,6 +187,8 @@ ce_grad_kernel(bf16* __restrict__ logits, long long ld, const int* __restrict__ 
 // out[0] (+)= scale * sum(in[0..n))   — deterministic single-CTA tree reduction
 __global__ void __launch_bounds__(1024) reduce_sum_kernel(const float* __restrict__ in, int n, float scale,
                                                           float* __restrict__ out, int accumulate) {
+  pdl_launch_dependents();  // PDL: let the next kernel's prologue overlap this kernel
+  pdl_wait();               // ... and do not touch global memory before the previous kernel has completed
   __shared__ float s[32];
   float v = 0.f;
   for (int i = threadIdx.x; i < n; i += blockDim.x) v += in[i];
@@ -201,7 +211,7 @@ using namespace dtc;
 extern "C" int dtc_ce_fwd_bwd(void* logits, long long ld, const int* labels, float* loss_rows, int M, int V, float gscale,
                               cudaStream_t stream) {
   DTC_CHECK_ARG(M > 0 && V > 0 && ld >= V && ld % 8 == 0, "ce_fwd_bwd: bad shape M=%d V=%d ld=%lld", M, V, ld);
-  ce_fwd_bwd_kernel<<<M, CE_THREADS, 0, stream>>>(reinterpret_cast<bf16*>(logits), ld, labels, loss_rows, V, gscale);
+  DTC_CHECK_CUDA(dtc::launch(ce_fwd_bwd_kernel, M, CE_THREADS, 0, stream, reinterpret_cast<bf16*>(logits), ld, labels, loss_rows, V, gscale));
   DTC_CHECK_LAUNCH();
   return 0;
 }
@@ -209,15 +219,15 @@ extern "C" int dtc_ce_fwd_bwd(void* logits, long long ld, const int* labels, flo
 extern "C" int dtc_ce_stats(const void* logits, long long ld, const int* labels, float* stats, int M, int V_local,
                             int vocab_start, cudaStream_t stream) {
   DTC_CHECK_ARG(M > 0 && V_local > 0 && ld >= V_local && ld % 8 == 0, "ce_stats: bad shape");
-  ce_stats_kernel<<<M, CE_THREADS, 0, stream>>>(reinterpret_cast<const bf16*>(logits), ld, labels, stats, V_local,
-                                                vocab_start);
+  DTC_CHECK_CUDA(dtc::launch(ce_stats_kernel, M, CE_THREADS, 0, stream, reinterpret_cast<const bf16*>(logits), ld, labels, stats, V_local,
+                                                vocab_start));
   DTC_CHECK_LAUNCH();
   return 0;
 }
 
 extern "C" int dtc_ce_combine(const float* stats, int n_shards, int M, float* lse, float* loss_rows, cudaStream_t stream) {
   DTC_CHECK_ARG(M > 0 && n_shards > 0, "ce_combine: bad shape");
-  ce_combine_kernel<<<(M + 255) / 256, 256, 0, stream>>>(stats, n_shards, M, lse, loss_rows);
+  DTC_CHECK_CUDA(dtc::launch(ce_combine_kernel, (M + 255) / 256, 256, 0, stream, stats, n_shards, M, lse, loss_rows));
   DTC_CHECK_LAUNCH();
   return 0;
 }
@@ -225,15 +235,15 @@ extern "C" int dtc_ce_combine(const float* stats, int n_shards, int M, float* ls
 extern "C" int dtc_ce_grad(void* logits, long long ld, const int* labels, const float* lse, int M, int V_local,
                            int vocab_start, float gscale, cudaStream_t stream) {
   DTC_CHECK_ARG(M > 0 && V_local > 0 && ld >= V_local && ld % 8 == 0, "ce_grad: bad shape");
-  ce_grad_kernel<<<M, CE_THREADS, 0, stream>>>(reinterpret_cast<bf16*>(logits), ld, labels, lse, V_local, vocab_start,
-                                               gscale);
+  DTC_CHECK_CUDA(dtc::launch(ce_grad_kernel, M, CE_THREADS, 0, stream, reinterpret_cast<bf16*>(logits), ld, labels, lse, V_local, vocab_start,
+                                               gscale));
   DTC_CHECK_LAUNCH();
   return 0;
 }
 
 extern "C" int dtc_reduce_sum(const float* in, int n, float scale, float* out, int accumulate, cudaStream_t stream) {
   DTC_CHECK_ARG(n > 0, "reduce_sum: empty input");
-  reduce_sum_kernel<<<1, 1024, 0, stream>>>(in, n, scale, out, accumulate);
+  DTC_CHECK_CUDA(dtc::launch(reduce_sum_kernel, 1, 1024, 0, stream, in, n, scale, out, accumulate));
   DTC_CHECK_LAUNCH();
   return 0;
 }

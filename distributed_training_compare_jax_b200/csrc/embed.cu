@@ -35,6 +35,8 @@ __global__ void embed_fwd_kernel(const int* __restrict__ ids, const bf16* __rest
                                  bf16* __restrict__ out, int M, int T, int D, int V, unsigned long long seed,
                                  const int* __restrict__ step_ptr, uint32_t stream, uint32_t threshold, float keep_scale,
                                  long long row_offset) {
+  pdl_launch_dependents();  // PDL: let the next kernel's prologue overlap this kernel
+  pdl_wait();               // ... and do not touch global memory before the previous kernel has completed
   const int cpr = D / 8;
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (long long)M * cpr) return;
@@ -65,6 +67,8 @@ __global__ void embed_bwd_kernel(const int* __restrict__ ids, const bf16* __rest
                                  float* __restrict__ dwpe, int Bsz, int T, int D, int V, unsigned long long seed,
                                  const int* __restrict__ step_ptr, uint32_t stream, uint32_t threshold, float keep_scale,
                                  long long row_offset) {
+  pdl_launch_dependents();  // PDL: let the next kernel's prologue overlap this kernel
+  pdl_wait();               // ... and do not touch global memory before the previous kernel has completed
   const int cpr = D / 8;
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (long long)T * cpr) return;
@@ -121,9 +125,9 @@ extern "C" int dtc_embed_fwd(const int* ids, const void* wte, const void* wpe, v
   DTC_CHECK_ARG(dropout_p >= 0.f && dropout_p < 1.f, "embed_fwd: dropout must be in [0,1)");
   const long long total = (long long)M * (D / 8);
   const int blocks = (int)((total + 255) / 256);
-  embed_fwd_kernel<<<blocks, 256, 0, stream>>>(ids, reinterpret_cast<const bf16*>(wte), reinterpret_cast<const bf16*>(wpe),
+  DTC_CHECK_CUDA(dtc::launch(embed_fwd_kernel, blocks, 256, 0, stream, ids, reinterpret_cast<const bf16*>(wte), reinterpret_cast<const bf16*>(wpe),
                                                reinterpret_cast<bf16*>(out), M, T, D, V, seed, step_ptr, stream_id,
-                                               dropout_threshold(dropout_p), 1.f / (1.f - dropout_p), row_offset);
+                                               dropout_threshold(dropout_p), 1.f / (1.f - dropout_p), row_offset));
   DTC_CHECK_LAUNCH();
   return 0;
 }
@@ -135,9 +139,9 @@ extern "C" int dtc_embed_bwd(const int* ids, const void* dh, float* dwte, float*
   DTC_CHECK_ARG(M > 0 && T > 0 && D % 8 == 0 && M % T == 0, "embed_bwd: bad shape M=%d T=%d D=%d", M, T, D);
   const long long total = (long long)T * (D / 8);
   const int blocks = (int)((total + 127) / 128);
-  embed_bwd_kernel<<<blocks, 128, 0, stream>>>(ids, reinterpret_cast<const bf16*>(dh), dwte, dwpe, M / T, T, D, V, seed,
+  DTC_CHECK_CUDA(dtc::launch(embed_bwd_kernel, blocks, 128, 0, stream, ids, reinterpret_cast<const bf16*>(dh), dwte, dwpe, M / T, T, D, V, seed,
                                                step_ptr, stream_id, dropout_threshold(dropout_p), 1.f / (1.f - dropout_p),
-                                               row_offset);
+                                               row_offset));
   DTC_CHECK_LAUNCH();
   return 0;
 }

@@ -112,6 +112,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
+  pdl_launch_dependents();  // PDL: only after this CTA owns its TMEM (a dependent may not allocate first)
+  pdl_wait();               // inputs come from the previous kernel: no global access before it has completed
 
   if (warp == 0) {
     // ------------------------------ TMA producer ------------------------------
@@ -285,7 +287,7 @@ static int launch_gemm(const void* A, long long lda, const void* B, long long ld
   }
   const int m_blocks = (M + BM - 1) / BM, n_blocks = (N + BN - 1) / BN;
   dim3 grid(m_blocks * n_blocks, splits, 1);
-  kern<<<grid, GEMM_THREADS, smem_bytes, stream>>>(ta, tb, M, N, K, m_blocks, kb_per_split, stages, epi);
+  DTC_CHECK_CUDA(dtc::launch(kern, grid, GEMM_THREADS, smem_bytes, stream, ta, tb, M, N, K, m_blocks, kb_per_split, stages, epi));
   DTC_CHECK_LAUNCH();
   return 0;
 }
@@ -368,6 +370,8 @@ gemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
+  pdl_launch_dependents();  // PDL: only after this CTA owns its TMEM (a dependent may not allocate first)
+  pdl_wait();               // inputs come from the previous kernel: no global access before it has completed
 
   if (warp == 0) {
     // ------------------------------ TMA producer ------------------------------
@@ -634,8 +638,8 @@ static int launch_gemm_persistent(const void* A, long long lda, const void* B, l
   const int m_blocks = (M + BM - 1) / BM, n_blocks = (N + BN - 1) / BN;
   const int total_tiles = m_blocks * n_blocks * splits;
   const int grid = total_tiles < num_sms() ? total_tiles : num_sms();
-  kern<<<grid, PG_THREADS, smem_bytes, stream>>>(ta, tb, tout, tout2, taux, M, N, K, m_blocks, n_blocks, splits,
-                                                   kb_per_split, stages, epi);
+  DTC_CHECK_CUDA(dtc::launch(kern, grid, PG_THREADS, smem_bytes, stream, ta, tb, tout, tout2, taux, M, N, K, m_blocks, n_blocks, splits,
+                                                   kb_per_split, stages, epi));
   DTC_CHECK_LAUNCH();
   return 0;
 }
@@ -720,6 +724,8 @@ gemm_2cta_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
   cluster_sync_all();  // the peer's barriers are initialised before anything may arrive on them remotely
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
+  pdl_launch_dependents();  // PDL: only after this CTA owns its TMEM (a dependent may not allocate first)
+  pdl_wait();               // inputs come from the previous kernel: no global access before it has completed
 
   if (warp == 0) {
     // ------------------------------ TMA producer (both CTAs) ------------------------------
@@ -966,8 +972,8 @@ static int launch_gemm_2cta(const void* A, long long lda, const void* B, long lo
   const int total_tiles = m_blocks * n_blocks * splits;
   const int max_pairs = num_sms() / 2;
   const int pairs = total_tiles < max_pairs ? total_tiles : max_pairs;
-  kern<<<2 * pairs, PG_THREADS, smem_bytes, stream>>>(ta, tb, tout, tout2, taux, M, N, K, m_blocks, n_blocks, splits,
-                                                      kb_per_split, stages, epi);
+  DTC_CHECK_CUDA(dtc::launch(kern, 2 * pairs, PG_THREADS, smem_bytes, stream, ta, tb, tout, tout2, taux, M, N, K, m_blocks, n_blocks, splits,
+                                                      kb_per_split, stages, epi));
   DTC_CHECK_LAUNCH();
   return 0;
 }

@@ -13,6 +13,8 @@ __global__ void __launch_bounds__(LN_WARPS * 32)
 layernorm_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ gamma, const bf16* __restrict__ beta,
                      bf16* __restrict__ y, float* __restrict__ mean_out, float* __restrict__ rstd_out, int M, int D,
                      float eps) {
+  pdl_launch_dependents();  // PDL: let the next kernel's prologue overlap this kernel
+  pdl_wait();               // ... and do not touch global memory before the previous kernel has completed
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long row = (long long)blockIdx.x * LN_WARPS + warp;
   if (row >= M) return;
@@ -59,6 +61,8 @@ __global__ void __launch_bounds__(LN_WARPS * 32)
 layernorm_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, const float* __restrict__ mean,
                      const float* __restrict__ rstd, const bf16* __restrict__ gamma, const bf16* __restrict__ dres,
                      bf16* __restrict__ dx, float* __restrict__ dgamma, float* __restrict__ dbeta, int M) {
+  pdl_launch_dependents();  // PDL: let the next kernel's prologue overlap this kernel
+  pdl_wait();               // ... and do not touch global memory before the previous kernel has completed
   constexpr int D = NCH * 256;
   __shared__ float s_dg[D];
   __shared__ float s_db[D];
@@ -157,9 +161,9 @@ extern "C" int dtc_layernorm_fwd(const void* x, const void* gamma, const void* b
                                  int M, int D, float eps, cudaStream_t stream) {
   DTC_CHECK_ARG(M > 0 && D > 0 && D % 8 == 0, "layernorm_fwd: need D %% 8 == 0 (M=%d D=%d)", M, D);
   const int blocks = (M + LN_WARPS - 1) / LN_WARPS;
-  layernorm_fwd_kernel<<<blocks, LN_WARPS * 32, 0, stream>>>(
+  DTC_CHECK_CUDA(dtc::launch(layernorm_fwd_kernel, blocks, LN_WARPS * 32, 0, stream, 
       reinterpret_cast<const bf16*>(x), reinterpret_cast<const bf16*>(gamma), reinterpret_cast<const bf16*>(beta),
-      reinterpret_cast<bf16*>(y), mean, rstd, M, D, eps);
+      reinterpret_cast<bf16*>(y), mean, rstd, M, D, eps));
   DTC_CHECK_LAUNCH();
   return 0;
 }
@@ -173,10 +177,10 @@ extern "C" int dtc_layernorm_bwd(const void* dy, const void* x, const float* mea
   if (blocks > 148 * 2) blocks = 148 * 2;
 #define DTC_LN_BWD(NCH)                                                                                             \
   case NCH:                                                                                                         \
-    layernorm_bwd_kernel<NCH><<<blocks, LN_WARPS * 32, 0, stream>>>(                                                \
+    DTC_CHECK_CUDA(dtc::launch(layernorm_bwd_kernel<NCH>, blocks, LN_WARPS * 32, 0, stream,                                                 \
         reinterpret_cast<const bf16*>(dy), reinterpret_cast<const bf16*>(x), mean, rstd,                            \
         reinterpret_cast<const bf16*>(gamma), reinterpret_cast<const bf16*>(dres), reinterpret_cast<bf16*>(dx),     \
-        dgamma, dbeta, M);                                                                                          \
+        dgamma, dbeta, M));                                                                                          \
     break;
   switch (D / 256) {
     DTC_LN_BWD(1) DTC_LN_BWD(2) DTC_LN_BWD(3) DTC_LN_BWD(4) DTC_LN_BWD(5) DTC_LN_BWD(6) DTC_LN_BWD(7) DTC_LN_BWD(8)

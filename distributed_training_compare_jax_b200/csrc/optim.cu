@@ -14,6 +14,8 @@ namespace dtc {
 
 __global__ void __launch_bounds__(256) sumsq_partials_kernel(const float* __restrict__ g, long long n,
                                                              float* __restrict__ partials) {
+  pdl_launch_dependents();  // PDL: let the next kernel's prologue overlap this kernel
+  pdl_wait();               // ... and do not touch global memory before the previous kernel has completed
   __shared__ float s[8];
   float acc = 0.f;
   const long long n4 = n >> 2;
@@ -38,6 +40,8 @@ __global__ void __launch_bounds__(256) sumsq_partials_kernel(const float* __rest
 __global__ void __launch_bounds__(1024) clip_finalize_kernel(const float* __restrict__ partials, int n, float grad_scale,
                                                              float max_norm, float* __restrict__ scalars,
                                                              int* __restrict__ step) {
+  pdl_launch_dependents();  // PDL: let the next kernel's prologue overlap this kernel
+  pdl_wait();               // ... and do not touch global memory before the previous kernel has completed
   __shared__ float s[32];
   float v = 0.f;
   for (int i = threadIdx.x; i < n; i += blockDim.x) v += partials[i];
@@ -60,6 +64,8 @@ __global__ void __launch_bounds__(256)
 adamw_kernel(float* __restrict__ p, float* __restrict__ m, float* __restrict__ v, float* __restrict__ g,
              bf16* __restrict__ p_bf16, long long n, const float* __restrict__ scalars, const int* __restrict__ step_ptr,
              float lr, float b1, float b2, float eps, float wd, float grad_scale, int zero_grad) {
+  pdl_launch_dependents();  // PDL: let the next kernel's prologue overlap this kernel
+  pdl_wait();               // ... and do not touch global memory before the previous kernel has completed
   const float clip = scalars ? scalars[1] : 1.f;
   const float gs = grad_scale * clip;
   const float t = (float)(step_ptr ? *step_ptr : 1);
@@ -104,6 +110,8 @@ adamw_kernel(float* __restrict__ p, float* __restrict__ m, float* __restrict__ v
 // grid.x over 256-column slabs, grid.y row splits; block (32 column-groups of 8) x 8 row lanes.
 __global__ void __launch_bounds__(256) colsum_kernel(const bf16* __restrict__ x, long long ld, int M, int N,
                                                      float* __restrict__ out) {
+  pdl_launch_dependents();  // PDL: let the next kernel's prologue overlap this kernel
+  pdl_wait();               // ... and do not touch global memory before the previous kernel has completed
   __shared__ float s[8][256 + 8];
   const int cg = threadIdx.x & 31, rl = threadIdx.x >> 5;
   const int c = blockIdx.x * 256 + cg * 8;
@@ -148,7 +156,7 @@ extern "C" int dtc_sumsq_num_partials(long long n) {
 // partials must hold dtc_sumsq_num_partials(n) floats.
 extern "C" int dtc_sumsq_partials(const float* g, long long n, float* partials, cudaStream_t stream) {
   DTC_CHECK_ARG(n > 0 && ((uintptr_t)g & 15) == 0, "sumsq: n must be > 0 and g 16-byte aligned");
-  sumsq_partials_kernel<<<dtc_sumsq_num_partials(n), 256, 0, stream>>>(g, n, partials);
+  DTC_CHECK_CUDA(dtc::launch(sumsq_partials_kernel, dtc_sumsq_num_partials(n), 256, 0, stream, g, n, partials));
   DTC_CHECK_LAUNCH();
   return 0;
 }
@@ -156,7 +164,7 @@ extern "C" int dtc_sumsq_partials(const float* g, long long n, float* partials, 
 extern "C" int dtc_clip_finalize(const float* partials, int n_partials, float grad_scale, float max_norm, float* scalars,
                                  int* step, cudaStream_t stream) {
   DTC_CHECK_ARG(n_partials > 0, "clip_finalize: no partials");
-  clip_finalize_kernel<<<1, 1024, 0, stream>>>(partials, n_partials, grad_scale, max_norm, scalars, step);
+  DTC_CHECK_CUDA(dtc::launch(clip_finalize_kernel, 1, 1024, 0, stream, partials, n_partials, grad_scale, max_norm, scalars, step));
   DTC_CHECK_LAUNCH();
   return 0;
 }
@@ -170,8 +178,8 @@ extern "C" int dtc_adamw(float* p, float* m, float* v, float* g, void* p_bf16, l
   long long blocks = (n / 4 + 255) / 256;
   if (blocks < 1) blocks = 1;
   if (blocks > 148 * 8) blocks = 148 * 8;
-  adamw_kernel<<<(int)blocks, 256, 0, stream>>>(p, m, v, g, reinterpret_cast<bf16*>(p_bf16), n, scalars, step_ptr, lr, b1,
-                                                b2, eps, wd, grad_scale, zero_grad);
+  DTC_CHECK_CUDA(dtc::launch(adamw_kernel, (int)blocks, 256, 0, stream, p, m, v, g, reinterpret_cast<bf16*>(p_bf16), n, scalars, step_ptr, lr, b1,
+                                                b2, eps, wd, grad_scale, zero_grad));
   DTC_CHECK_LAUNCH();
   return 0;
 }
@@ -182,7 +190,7 @@ extern "C" int dtc_colsum(const void* x, long long ld, int M, int N, float* out,
   int ysplit = (M + 31) / 32;  // >= 4 rows per thread; enough CTAs to fill 148 SMs even for N = 512
   if (ysplit > 128) ysplit = 128;
   dim3 grid((N + 255) / 256, ysplit);
-  colsum_kernel<<<grid, 256, 0, stream>>>(reinterpret_cast<const bf16*>(x), ld, M, N, out);
+  DTC_CHECK_CUDA(dtc::launch(colsum_kernel, grid, 256, 0, stream, reinterpret_cast<const bf16*>(x), ld, M, N, out));
   DTC_CHECK_LAUNCH();
   return 0;
 }

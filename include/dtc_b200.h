@@ -21,6 +21,7 @@ extern "C" {
 /* ---- runtime --------------------------------------------------------------------------------------- */
 const char* dtc_last_error(void);
 int dtc_version(void);
+int dtc_set_pdl(int enabled); /* programmatic dependent launch for all kernels: 0 (default) / 1; env DTC_PDL=1 */
 int dtc_device_arch(void); /* compute capability major*10+minor of the current device, <0 on error */
 int dtc_cast_f32_to_bf16(const float* in, void* out, long long n, cudaStream_t stream);
 int dtc_cast_f32_to_bf16_2d(const float* in, long long ld_in, void* out, long long ld_out, int rows, int cols,
