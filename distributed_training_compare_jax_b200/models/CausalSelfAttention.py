@@ -47,11 +47,17 @@ class CausalSelfAttention:
     def native_backward(self, eng, ws, l: int, dh: torch.Tensor) -> None:
         """dh = dL/dhmid[l].  Accumulates attention grads; leaves dL/d(ln1 out) in ws.dln (TP-reduced)."""
         c, g = eng.c, eng.g
-        Fn.colsum(dh, g["bo"][l])
-        Fn.gemm(ws.attn[l], dh, a_mn=True, b_mn=True, epi="atomic_f32", out=g["wo"][l], splits=eng.wgrad_splits)
+        def out_param_grads():
+            Fn.colsum(dh, g["bo"][l])
+            Fn.gemm(ws.attn[l], dh, a_mn=True, b_mn=True, epi="atomic_f32", out=g["wo"][l], splits=eng.wgrad_splits)
+
+        def qkv_param_grads():
+            Fn.colsum(ws.dqkv, g["bqkv"][l])
+            Fn.gemm(ws.ln1[l], ws.dqkv, a_mn=True, b_mn=True, epi="atomic_f32", out=g["wqkv"][l], splits=eng.wgrad_splits)
+
+        eng.side_work(out_param_grads)
         Fn.gemm(dh, c["wo"][l], out=ws.dattn)
         Fn.flash_attn_bwd(ws.qkv[l], ws.attn[l], ws.dattn, ws.lse2[l], ws.B, self.local.heads_local, ws.T,
                           self.config.head_dim, dqkv=ws.dqkv, dq_accum=ws.dq_accum, delta=ws.delta)
-        Fn.colsum(ws.dqkv, g["bqkv"][l])
-        Fn.gemm(ws.ln1[l], ws.dqkv, a_mn=True, b_mn=True, epi="atomic_f32", out=g["wqkv"][l], splits=eng.wgrad_splits)
+        eng.side_work(qkv_param_grads)
         eng.tp_reduced_gemm(ws.dqkv, c["wqkv"][l], out=ws.dln)

@@ -86,8 +86,12 @@ class GPTModel:
         cur = dh_top
         for l in reversed(range(self.local.L)):
             nxt = bufs[0] if cur is not bufs[0] else bufs[1]
+            # the side stream (parameter gradients of layer l+1) still reads the scratch buffers this layer rewrites
+            eng.side_join()
             self.block.native_backward(eng, ws, l, cur, ws.dh_mid, nxt)
-            eng.on_layer_grads_ready(l)
+            if eng.has_grad_hooks:
+                eng.side_join()
+                eng.on_layer_grads_ready(l)
             cur = nxt
         return cur
 
@@ -107,9 +111,14 @@ class GPTModel:
             Fn.ce_combine(ws.ce_stats_all, tp.size, ws.M, ws.lse, ws.loss_rows)
             Fn.ce_grad(ws.logits, ws.labels, ws.lse, nv, lo.vocab_start, gscale)
         # logits now hold dlogits (pad columns are zero)
-        Fn.colsum(ws.logits, g["blm"])
-        Fn.gemm(ws.lnf, ws.logits, a_mn=True, b_mn=True, epi="atomic_f32", out=g["wlm"], splits=1)
+        def head_param_grads():
+            Fn.colsum(ws.logits, g["blm"])
+            Fn.gemm(ws.lnf, ws.logits, a_mn=True, b_mn=True, epi="atomic_f32", out=g["wlm"], splits=1)
+
+        eng.side_work(head_param_grads)
         eng.tp_reduced_gemm(ws.logits, c["wlm"], out=ws.dln)
         Fn.layernorm_bwd(ws.dln, ws.h[L], ws.meanf, ws.rstdf, c["lnf_g"], g["lnf_g"], g["lnf_b"], dres=None, out=ws.dh_a)
-        eng.on_head_grads_ready()
+        if eng.has_grad_hooks:
+            eng.side_join()
+            eng.on_head_grads_ready()
         return ws.dh_a

@@ -39,9 +39,15 @@ class MLP:
     def native_backward(self, eng, ws, l: int, dh: torch.Tensor) -> None:
         """dh = dL/dh[l+1].  Accumulates fc1/fc2 grads; leaves dL/d(ln2 out) in ws.dln (TP-reduced)."""
         c, g = eng.c, eng.g
-        Fn.colsum(dh, g["b2"][l])
-        Fn.gemm(ws.g[l], dh, a_mn=True, b_mn=True, epi="atomic_f32", out=g["w2"][l], splits=eng.wgrad_splits)
+        def fc2_param_grads():
+            Fn.colsum(dh, g["b2"][l])
+            Fn.gemm(ws.g[l], dh, a_mn=True, b_mn=True, epi="atomic_f32", out=g["w2"][l], splits=eng.wgrad_splits)
+
+        def fc1_param_grads():
+            Fn.colsum(ws.df1, g["b1"][l])
+            Fn.gemm(ws.ln2[l], ws.df1, a_mn=True, b_mn=True, epi="atomic_f32", out=g["w1"][l], splits=eng.wgrad_splits)
+
+        eng.side_work(fc2_param_grads)
         Fn.gemm(dh, c["w2"][l], epi="dgelu", aux=ws.f1[l], out=ws.df1)
-        Fn.colsum(ws.df1, g["b1"][l])
-        Fn.gemm(ws.ln2[l], ws.df1, a_mn=True, b_mn=True, epi="atomic_f32", out=g["w1"][l], splits=eng.wgrad_splits)
+        eng.side_work(fc1_param_grads)
         eng.tp_reduced_gemm(ws.df1, c["w1"][l], out=ws.dln)

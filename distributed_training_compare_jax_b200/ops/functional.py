@@ -15,6 +15,26 @@ BF16 = torch.bfloat16
 F32 = torch.float32
 
 
+class gemm_impl:
+    """Context manager selecting the GEMM kernel variant for the calls issued inside it (host-side dispatch, so it
+    also works while a CUDA graph is being captured): 0 persistent 1-CTA (default policy), 1 one-tile-per-CTA
+    (98 KB smem, 128 TMEM columns: two of them fit on one SM, which lets GEMMs from two streams overlap),
+    2 / 3 CTA-pair kernels."""
+    current = 0
+
+    def __init__(self, impl: int):
+        self.impl, self.prev = impl, 0
+
+    def __enter__(self):
+        self.prev = gemm_impl.current
+        gemm_impl.current = self.impl
+        native.load().dtc_gemm_set_impl(self.impl)
+
+    def __exit__(self, *exc):
+        gemm_impl.current = self.prev
+        native.load().dtc_gemm_set_impl(self.prev)
+
+
 def _check_rowmajor(t: torch.Tensor, name: str) -> None:
     if t.dim() != 2 or t.stride(1) != 1:
         raise ValueError(f"{name}: expected a 2-D tensor with unit inner stride, got shape {tuple(t.shape)} "

@@ -31,6 +31,7 @@ class BucketedAllReduce:
         self.stream = torch.cuda.Stream(device=engine.device)
         engine.on_layer_grads_ready = self._layer_ready
         engine.on_head_grads_ready = self._head_ready
+        engine.has_grad_hooks = True
         st = self.store
         L = engine.local.L
 

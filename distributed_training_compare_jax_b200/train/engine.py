@@ -74,6 +74,7 @@ class StageEngineBase:
         self.model = GPTModel(cfg, local, mesh)
         self.device = store.device
         self.loss_sum = torch.zeros(1, device=self.device, dtype=F32)  # sum over local rows / global_tokens
+        self.has_grad_hooks = False  # set by the bucketed DP reducer
 
     # hooks used by the data-parallel engine to overlap gradient reduction with the backward pass
     def on_layer_grads_ready(self, l: int) -> None:
@@ -89,8 +90,12 @@ class StageEngineBase:
 class NativeStageEngine(StageEngineBase):
     backend = "native"
 
-    def __init__(self, *a, wgrad_splits: int = 0, **kw):
+    def __init__(self, *a, wgrad_splits: int = 0, overlap_wgrad: bool = True, **kw):
         super().__init__(*a, **kw)
+        # Weight-gradient work (wgrad GEMMs + bias column sums) does not feed the backward chain: it runs on a side
+        # stream concurrently with the dgrad / attention / LayerNorm chain.  Both streams then use the light GEMM
+        # kernel (98 KB smem, 128 TMEM columns) so that two GEMM CTAs fit on one SM.
+        self.side = torch.cuda.Stream(device=self.store.device) if overlap_wgrad else None
         if self.device.type != "cuda":
             raise RuntimeError("the native engine needs a CUDA device (sm_100a)")
         if self.seq_len % 128:
@@ -126,6 +131,23 @@ class NativeStageEngine(StageEngineBase):
             Fn.gemm(x, w, b_mn=True, out=out)
         tp.all_reduce(out)
 
+    def side_work(self, fn) -> None:
+        """Run ``fn`` (kernel launches that only produce parameter gradients) on the side stream, after everything
+        issued so far on the main stream."""
+        if self.side is None:
+            fn()
+            return
+        self.side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(self.side):
+            fn()
+
+    def side_join(self) -> None:
+        if self.side is not None:
+            torch.cuda.current_stream().wait_stream(self.side)
+
+    def backward_gemm_impl(self):
+        return Fn.gemm_impl(1 if self.side is not None else Fn.gemm_impl.current)
+
     def tp_reduced_gemm(self, a, w, out) -> None:
         """out = sum over TP ranks of a · wᵀ (dX of a column-parallel Linear, collectives X5 / X8)."""
         if self.tp_hooks is not None:
@@ -156,6 +178,7 @@ class NativeStageEngine(StageEngineBase):
             return ws.h[self.local.L]
         ws.dh_top = self.model.native_head_forward_backward(self, ws, 1.0 / self.global_tokens)
         Fn.reduce_sum(ws.loss_rows, 1.0 / self.global_tokens, self.loss_sum, accumulate=True)
+        self.side_join()
         return None
 
     def grad_input_buffer(self, mb: int) -> torch.Tensor:
@@ -165,7 +188,9 @@ class NativeStageEngine(StageEngineBase):
     def backward(self, mb: int) -> torch.Tensor | None:
         ws = self.ws[mb]
         top = ws.dh_top if self.local.has_head else ws.dh_b
-        dh0 = self.model.native_stage_backward(self, ws, top)
+        with self.backward_gemm_impl():
+            dh0 = self.model.native_stage_backward(self, ws, top)
+        self.side_join()
         if self.local.has_embed:
             self.model.native_embed_backward(self, ws, dh0)
             return None
