@@ -92,7 +92,8 @@ def run(args) -> dict | None:
     else:
         global_batch = per_rank_batch * dp
         local = LocalShape(mc, tp_rank=mesh.tp.rank, tp_size=tp)
-        state = build_state(tc, mc, oc, mesh, per_rank_batch, 1, global_batch * T, local)
+        chains = args.chains if tp == 1 else 1
+        state = build_state(tc, mc, oc, mesh, per_rank_batch // chains, chains, global_batch * T, local)
         train_step = create_train_step(strategy, cuda_graph=tc.cuda_graph)
         it = get_batch_iterator(global_batch, T + 1, seed=0, rank=mesh.dp.rank, world=dp)
     tokens_per_step = global_batch * T
@@ -191,6 +192,7 @@ def main() -> int:
     ap.add_argument("--backend", default="auto")
     ap.add_argument("--no-fused-comm", action="store_true")
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--chains", type=int, default=1, help="concurrent chains the local batch is split into (DP)")
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm(args)

@@ -198,7 +198,10 @@ __global__ void __launch_bounds__(1024) reduce_sum_kernel(const float* __restric
   if (threadIdx.x < 32) {
     v = s[threadIdx.x];
     v = warp_sum(v);
-    if (threadIdx.x == 0) out[0] = (accumulate ? out[0] : 0.f) + v * scale;
+    if (threadIdx.x == 0) {
+      if (accumulate) atomicAdd(out, v * scale);  // several chains (streams) may accumulate into the same scalar
+      else out[0] = v * scale;
+    }
   }
 }
 

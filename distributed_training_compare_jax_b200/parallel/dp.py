@@ -29,9 +29,12 @@ class BucketedAllReduce:
         self.engine, self.mesh = engine, mesh
         self.store = engine.store
         self.stream = torch.cuda.Stream(device=engine.device)
-        engine.on_layer_grads_ready = self._layer_ready
-        engine.on_head_grads_ready = self._head_ready
-        engine.has_grad_hooks = True
+        # with several concurrent chains a layer's gradient is final only when ALL chains have passed it: reduce at the end
+        self.overlap = engine.n_micro == 1
+        if self.overlap:
+            engine.on_layer_grads_ready = self._layer_ready
+            engine.on_head_grads_ready = self._head_ready
+            engine.has_grad_hooks = True
         st = self.store
         L = engine.local.L
 
@@ -69,6 +72,9 @@ class BucketedAllReduce:
 
     def __call__(self) -> None:
         """Called by the optimizer after backward: reduce the embedding bucket, then join the side stream."""
+        if not self.overlap:
+            self.mesh.dp.all_reduce(self.store.flat_grad)
+            return
         self._reduce(self.embed_slices)
         torch.cuda.current_stream().wait_stream(self.stream)
 

@@ -115,13 +115,29 @@ def create_train_step(parallel: str = "dp", cuda_graph: bool = True) -> Any:
         eng, opt, mesh = state.engine, state.optimizer, state.mesh
         dev = eng.device
         # DP: the loader already yields this rank's slice (reference: P("data", None)); TP: replicated batch
-        eng.set_batch(0, _to_i32(batch.x, dev, cache, "x"), _to_i32(batch.y, dev, cache, "y"))
+        x, y = _to_i32(batch.x, dev, cache, "x"), _to_i32(batch.y, dev, cache, "y")
+        n = eng.n_micro  # > 1: the local batch is split into independent chains that run concurrently on the GPU
+        per = x.shape[0] // n
+        for m in range(n):
+            eng.set_batch(m, x[m * per:(m + 1) * per], y[m * per:(m + 1) * per])
         _mark_copied(dev, cache)
 
         def body():
             eng.begin_step()
-            eng.forward(0)
-            eng.backward(0)
+            if n == 1:
+                eng.forward(0)
+                eng.backward(0)
+            else:
+                main = torch.cuda.current_stream()
+                if "chains" not in cache:
+                    cache["chains"] = [torch.cuda.Stream(device=dev) for _ in range(n)]
+                for m, st in enumerate(cache["chains"]):
+                    st.wait_stream(main)
+                    with torch.cuda.stream(st):
+                        eng.forward(m)
+                        eng.backward(m)
+                for st in cache["chains"]:
+                    main.wait_stream(st)
             opt.step()
             mesh.dp.all_reduce(eng.loss_sum)  # mean over the GLOBAL batch (reference: loss.mean() over P("data"))
 

@@ -95,7 +95,8 @@ class NativeStageEngine(StageEngineBase):
         # Weight-gradient work (wgrad GEMMs + bias column sums) does not feed the backward chain: it runs on a side
         # stream concurrently with the dgrad / attention / LayerNorm chain.  Both streams then use the light GEMM
         # kernel (98 KB smem, 128 TMEM columns) so that two GEMM CTAs fit on one SM.
-        self.side = torch.cuda.Stream(device=self.store.device) if overlap_wgrad else None
+        self.overlap_wgrad = overlap_wgrad
+        self.side = None  # side stream of the workspace currently being processed (set in forward / backward)
         if self.device.type != "cuda":
             raise RuntimeError("the native engine needs a CUDA device (sm_100a)")
         if self.seq_len % 128:
@@ -111,6 +112,7 @@ class NativeStageEngine(StageEngineBase):
                           stream_id=0)
             # global row index of local row 0: distinct dropout masks per DP rank / microbatch, identical across TP
             w.row_offset = (dp.rank * self.n_micro + i) * M
+            w.side = torch.cuda.Stream(device=self.device) if self.overlap_wgrad else None
             self.ws.append(w)
         self.tp_hooks = None  # set by parallel/tp.py when the fused GEMM+collective kernels are enabled
 
@@ -171,6 +173,7 @@ class NativeStageEngine(StageEngineBase):
         """Runs embed (first stage) + local layers (+ head, loss and head backward on the last stage).
         Returns the activation buffer to send downstream, or None on the last stage."""
         ws = self.ws[mb]
+        self.side = ws.side
         if self.local.has_embed:
             self.model.native_embed_forward(self, ws)
         self.model.native_stage_forward(self, ws)
@@ -187,6 +190,7 @@ class NativeStageEngine(StageEngineBase):
 
     def backward(self, mb: int) -> torch.Tensor | None:
         ws = self.ws[mb]
+        self.side = ws.side
         top = ws.dh_top if self.local.has_head else ws.dh_b
         with self.backward_gemm_impl():
             dh0 = self.model.native_stage_backward(self, ws, top)

@@ -130,7 +130,9 @@ def train_dp_tp(train_config: TrainConfig, model_config: ModelConfig, opt_config
     local_batch = global_batch // dp
     T = model_config.max_seq_len
     local = LocalShape(model_config, tp_rank=mesh.tp.rank, tp_size=tp)
-    state = build_state(train_config, model_config, opt_config, mesh, local_batch, 1, global_batch * T, local)
+    chains = train_config.micro_chains if (tp == 1 and local_batch % max(train_config.micro_chains, 1) == 0) else 1
+    state = build_state(train_config, model_config, opt_config, mesh, local_batch // chains, chains, global_batch * T,
+                        local)
     train_step = create_train_step(parallel=parallel_strategy, cuda_graph=train_config.cuda_graph)
     data_iterator = get_batch_iterator(batch_size=global_batch, seq_len=T + 1, seed=train_config.seed, rank=mesh.dp.rank,
                                        world=dp, synthetic=train_config.synthetic_data)
