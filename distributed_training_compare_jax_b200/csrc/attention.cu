@@ -16,6 +16,8 @@
 //   Pt  = exp2(St*c - lse2_i) ; dSt = Pt o (dPt - delta_i)     -> two swizzled smem tiles
 //   dV += Pt dO_i ; dK += dSt Q_i     (accumulate in TMEM across i)
 //   dQ_i = dS K_j                     (the dSt tile re-read as an MN-major A operand) -> fp32 red.add to dq_accum
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "tma_host.h"
 
@@ -208,6 +210,176 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
   if (warp == 0) {
     tc_fence_after();
     tmem_dealloc(tmem_base, 256);
+  }
+}
+
+// Forward, 64-key blocks (default): same algorithm as flash_attn_fwd_kernel, but a key/value block is 64 rows, so the
+// S accumulator needs 64 TMEM columns and the P tile 16 KB: with 128 allocated TMEM columns and ~42 KB of shared
+// memory FOUR CTAs fit on an SM (the 128-key version: two), which doubles the warps available to hide the
+// MMA -> tcgen05.ld -> exp2 -> st.shared -> MMA round trips this latency-bound kernel consists of.
+template <int HD>
+__global__ void __launch_bounds__(128, 4)
+flash_attn_fwd_kv64_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
+                           const __grid_constant__ CUtensorMap tm_v, bf16* __restrict__ out, long long ldo,
+                           float* __restrict__ lse2_out, int T, int H, float scale_log2) {
+  using C = AttnCfg<HD>;
+  constexpr int KVB = 64;
+  constexpr int KV_BYTES = KVB * C::ROW_BYTES;
+  constexpr int P64_BYTES = ATT_BLK * 128;  // [128 x 64] bf16, one K-major 128B-swizzled block
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* sQ = smem;
+  uint8_t* sP = sQ + C::TILE_BYTES;
+  uint8_t* sK = sP + P64_BYTES;     // 2 stages
+  uint8_t* sV = sK + 2 * KV_BYTES;  // 2 stages
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sV + 2 * KV_BYTES);
+  uint64_t* bar_q = bars;
+  uint64_t* bar_kv = bars + 1;  // [2]
+  uint64_t* bar_s = bars + 3;
+  uint64_t* bar_o = bars + 4;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 5);
+
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int qblk = gridDim.x - 1 - blockIdx.x, h = blockIdx.y, b = blockIdx.z;  // heaviest query blocks first
+  const int row0 = b * T + qblk * ATT_BLK;
+  const int nkv = 2 * (qblk + 1);  // causal: 64-key blocks 0 .. 2*qblk+1
+  const int qrow = qblk * ATT_BLK + tid;  // position of this thread's query inside the sequence
+
+  if (tid == 0) {
+    tma_prefetch_desc(&tm_q);
+    tma_prefetch_desc(&tm_k);
+    tma_prefetch_desc(&tm_v);
+    mbar_init(bar_q, 1);
+    mbar_init(&bar_kv[0], 1);
+    mbar_init(&bar_kv[1], 1);
+    mbar_init(bar_s, 1);
+    mbar_init(bar_o, 1);
+    fence_barrier_init();
+  }
+  if (warp == 0) {
+    tmem_alloc(tmem_ptr_smem, 128);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+  pdl_launch_dependents();
+  pdl_wait();
+  const uint32_t tmem_s = tmem_base, tmem_pv = tmem_base + 64;
+  const uint32_t lane_sel = (uint32_t)(warp * 32) << 16;
+
+  if (tid == 0) {
+    mbar_expect_tx(bar_q, C::TILE_BYTES);
+    tma_load_2d(sQ, &tm_q, bar_q, h * HD, row0);
+    mbar_expect_tx(&bar_kv[0], 2 * KV_BYTES);
+    tma_load_2d(sK, &tm_k, &bar_kv[0], h * HD, b * T);
+    tma_load_2d(sV, &tm_v, &bar_kv[0], h * HD, b * T);
+  }
+
+  constexpr uint32_t idesc_s = make_idesc_bf16(128, KVB, 0, 0);
+  constexpr uint32_t idesc_pv = make_idesc_bf16(128, HD, 0, 1);
+
+  float o_acc[HD];
+#pragma unroll
+  for (int j = 0; j < HD; ++j) o_acc[j] = 0.f;
+  float m_run = -INFINITY, l_run = 0.f;
+
+  for (int j = 0; j < nkv; ++j) {
+    const int st = j & 1;
+    if (j == 0) mbar_wait(bar_q, 0);
+    mbar_wait(&bar_kv[st], (j >> 1) & 1);
+    tc_fence_after();
+    if (tid == 0) {
+      const uint32_t aq = smem_u32(sQ), ak = smem_u32(sK + st * KV_BYTES);
+#pragma unroll
+      for (int k = 0; k < HD / 16; ++k)
+        umma_bf16(tmem_s, make_smem_desc(aq + k * 32, 16, C::SBO, C::SWZ), make_smem_desc(ak + k * 32, 16, C::SBO, C::SWZ),
+                  idesc_s, k > 0);
+      umma_commit(bar_s);
+      if (j + 1 < nkv) {
+        const int ns = st ^ 1;
+        mbar_expect_tx(&bar_kv[ns], 2 * KV_BYTES);
+        tma_load_2d(sK + ns * KV_BYTES, &tm_k, &bar_kv[ns], h * HD, b * T + (j + 1) * KVB);
+        tma_load_2d(sV + ns * KV_BYTES, &tm_v, &bar_kv[ns], h * HD, b * T + (j + 1) * KVB);
+      }
+    }
+    mbar_wait(bar_s, j & 1);
+    tc_fence_after();
+
+    // key column c of this block is visible to this query iff j*64 + c <= qrow  <=>  c <= lim
+    const int lim = qrow - j * KVB;
+    uint32_t r0[32], r1[32];
+    tmem_ld_32x32b_x32(tmem_s + lane_sel, r0);
+    tmem_ld_32x32b_x32(tmem_s + lane_sel + 32, r1);
+    tmem_ld_wait();
+    float mx = -INFINITY;
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+      if (i <= lim) mx = fmaxf(mx, __uint_as_float(r0[i]));
+      if (i + 32 <= lim) mx = fmaxf(mx, __uint_as_float(r1[i]));
+    }
+    const float m_new = fmaxf(m_run, mx * scale_log2);  // block 0 always has a visible key, so m_new is finite
+    const float alpha = exp2f(m_run - m_new);
+    float l_blk = 0.f;
+#pragma unroll
+    for (int g = 0; g < 8; ++g) {
+      float p[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int col = g * 8 + i;
+        const float sv = __uint_as_float(g < 4 ? r0[col] : r1[col - 32]);
+        p[i] = (col <= lim) ? exp2f(sv * scale_log2 - m_new) : 0.f;
+        l_blk += p[i];
+      }
+      *reinterpret_cast<uint4*>(sP + swizzle_offset<3>(tid * 128 + g * 16)) =
+          make_uint4(pack_bf16x2(p[0], p[1]), pack_bf16x2(p[2], p[3]), pack_bf16x2(p[4], p[5]), pack_bf16x2(p[6], p[7]));
+    }
+    l_run = l_run * alpha + l_blk;
+    m_run = m_new;
+    fence_proxy_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    if (tid == 0) {
+      tc_fence_after();
+      const uint32_t ap = smem_u32(sP), av = smem_u32(sV + st * KV_BYTES);
+#pragma unroll
+      for (int k = 0; k < KVB / 16; ++k)
+        umma_bf16(tmem_pv, make_smem_desc(ap + k * 32, 16, 1024, SWZ_128B),
+                  make_smem_desc(av + k * 16 * C::ROW_BYTES, 16, C::SBO, C::SWZ), idesc_pv, k > 0);
+      umma_commit(bar_o);
+    }
+    mbar_wait(bar_o, j & 1);
+    tc_fence_after();
+#pragma unroll
+    for (int c = 0; c < HD / 32; ++c) {
+      uint32_t r[32];
+      tmem_ld_32x32b_x32(tmem_pv + lane_sel + c * 32, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 32; ++i) o_acc[c * 32 + i] = o_acc[c * 32 + i] * alpha + __uint_as_float(r[i]);
+    }
+    tc_fence_before();
+    __syncthreads();
+  }
+
+  const float inv_l = 1.f / l_run;
+  bf16* orow = out + (long long)(row0 + tid) * ldo + h * HD;
+#pragma unroll
+  for (int c = 0; c < HD / 8; ++c) {
+    *reinterpret_cast<uint4*>(orow + c * 8) =
+        make_uint4(pack_bf16x2(o_acc[c * 8] * inv_l, o_acc[c * 8 + 1] * inv_l),
+                   pack_bf16x2(o_acc[c * 8 + 2] * inv_l, o_acc[c * 8 + 3] * inv_l),
+                   pack_bf16x2(o_acc[c * 8 + 4] * inv_l, o_acc[c * 8 + 5] * inv_l),
+                   pack_bf16x2(o_acc[c * 8 + 6] * inv_l, o_acc[c * 8 + 7] * inv_l));
+  }
+  lse2_out[((long long)b * H + h) * T + qblk * ATT_BLK + tid] = m_run + log2f(l_run);
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 128);
   }
 }
 
@@ -473,6 +645,25 @@ static int launch_fwd(const void* q, const void* k, const void* v, long long ld,
   if ((rc = attn_tmap<HD>(&tq, q, M, H, ld))) return rc;
   if ((rc = attn_tmap<HD>(&tk, k, M, H, ld))) return rc;
   if ((rc = attn_tmap<HD>(&tv, v, M, H, ld))) return rc;
+  const float scale = 1.f / sqrtf((float)HD);
+  dim3 grid(T / ATT_BLK, H, B);
+  static const bool use_kv128 = getenv("DTC_ATTN_FWD_KV128") != nullptr;  // A/B switch: the 128-key-block kernel
+  if (!use_kv128) {
+    CUtensorMap tk64, tv64;
+    const CUtensorMapSwizzle swz = HD == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
+    if ((rc = make_tmap_2d_bf16(&tk64, k, M, (uint64_t)H * HD, ld, 64, HD, swz))) return rc;
+    if ((rc = make_tmap_2d_bf16(&tv64, v, M, (uint64_t)H * HD, ld, 64, HD, swz))) return rc;
+    const int smem64 = C::TILE_BYTES + ATT_BLK * 128 + 4 * 64 * C::ROW_BYTES + 1024 + 128;
+    auto kern64 = flash_attn_fwd_kv64_kernel<HD>;
+    static bool configured64 = false;
+    if (!configured64) {
+      DTC_CHECK_CUDA(cudaFuncSetAttribute(kern64, cudaFuncAttributeMaxDynamicSharedMemorySize, smem64));
+      configured64 = true;
+    }
+    DTC_CHECK_CUDA(dtc::launch(kern64, grid, 128, smem64, stream, tq, tk64, tv64, reinterpret_cast<bf16*>(out), ldo, lse2, T, H,
+                               scale * LOG2E));
+    return 0;
+  }
   const int smem = 5 * C::TILE_BYTES + C::P_BYTES + 1024 + 128;
   auto kern = flash_attn_fwd_kernel<HD>;
   static bool configured = false;
@@ -480,8 +671,6 @@ static int launch_fwd(const void* q, const void* k, const void* v, long long ld,
     DTC_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured = true;
   }
-  const float scale = 1.f / sqrtf((float)HD);
-  dim3 grid(T / ATT_BLK, H, B);
   DTC_CHECK_CUDA(dtc::launch(kern, grid, 128, smem, stream, tq, tk, tv, reinterpret_cast<bf16*>(out), ldo, lse2, T, H, scale * LOG2E));
   DTC_CHECK_LAUNCH();
   return 0;
