@@ -629,6 +629,220 @@ flash_attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
   }
 }
 
+// Backward, register-accumulator variant (head_dim 32, default): dK / dV accumulate in registers (one key row per
+// thread, like the forward's O) instead of tensor memory, and the per-iteration dV / dK / dQ products land in the
+// St / dPt columns once those have been consumed.  The CTA then needs 256 TMEM columns and ~107 KB of shared
+// memory (dO single-buffered), so TWO CTAs fit on an SM (flash_attn_bwd_kernel: 512 columns -> one CTA, 4 warps per SM).
+template <int HD>
+__global__ void __launch_bounds__(128, 2)
+flash_attn_bwd_regacc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
+                             const __grid_constant__ CUtensorMap tm_v, const __grid_constant__ CUtensorMap tm_do,
+                             const float* __restrict__ lse2, const float* __restrict__ delta, float* __restrict__ dq_accum,
+                             long long lddq, bf16* __restrict__ dk, bf16* __restrict__ dv, long long lddkv, int T, int H,
+                             float scale, float scale_log2) {
+  using C = AttnCfg<HD>;
+  static_assert(HD == 32, "register accumulators are sized for head_dim 32");
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* sK = smem;
+  uint8_t* sV = sK + C::TILE_BYTES;
+  uint8_t* sQ = sV + C::TILE_BYTES;       // 2 stages
+  uint8_t* sDO = sQ + 2 * C::TILE_BYTES;  // 1 stage
+  uint8_t* sPt = sDO + C::TILE_BYTES;
+  uint8_t* sDSt = sPt + C::P_BYTES;
+  float* s_lse = reinterpret_cast<float*>(sDSt + C::P_BYTES);  // [128]
+  float* s_delta = s_lse + ATT_BLK;                            // [128]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_delta + ATT_BLK);
+  uint64_t* bar_kv = bars;
+  uint64_t* bar_q = bars + 1;  // [2]
+  uint64_t* bar_do = bars + 3;
+  uint64_t* bar_s = bars + 4;
+  uint64_t* bar_d = bars + 5;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 6);
+
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int jblk = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  const int nblk = T / ATT_BLK;
+  const int kv_row0 = b * T + jblk * ATT_BLK;
+  const long long stat_base = ((long long)b * H + h) * T;
+
+  if (tid == 0) {
+    tma_prefetch_desc(&tm_q);
+    tma_prefetch_desc(&tm_k);
+    tma_prefetch_desc(&tm_v);
+    tma_prefetch_desc(&tm_do);
+    mbar_init(bar_kv, 1);
+    mbar_init(&bar_q[0], 1);
+    mbar_init(&bar_q[1], 1);
+    mbar_init(bar_do, 1);
+    mbar_init(bar_s, 1);
+    mbar_init(bar_d, 1);
+    fence_barrier_init();
+  }
+  if (warp == 0) {
+    tmem_alloc(tmem_ptr_smem, 256);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+  pdl_launch_dependents();
+  pdl_wait();
+  const uint32_t tm_st = tmem_base, tm_dpt = tmem_base + 128;
+  // per-iteration products, written over the (already consumed) St columns
+  const uint32_t tm_dv = tmem_base, tm_dk = tmem_base + HD, tm_dq = tmem_base + 2 * HD;
+  const uint32_t lane_sel = (uint32_t)(warp * 32) << 16;
+
+  if (tid == 0) {
+    mbar_expect_tx(bar_kv, 2 * C::TILE_BYTES);
+    tma_load_2d(sK, &tm_k, bar_kv, h * HD, kv_row0);
+    tma_load_2d(sV, &tm_v, bar_kv, h * HD, kv_row0);
+    mbar_expect_tx(&bar_q[0], C::TILE_BYTES);
+    tma_load_2d(sQ, &tm_q, &bar_q[0], h * HD, b * T + jblk * ATT_BLK);
+    mbar_expect_tx(bar_do, C::TILE_BYTES);
+    tma_load_2d(sDO, &tm_do, bar_do, h * HD, b * T + jblk * ATT_BLK);
+  }
+
+  constexpr uint32_t idesc_kk = make_idesc_bf16(128, 128, 0, 0);
+  constexpr uint32_t idesc_kn = make_idesc_bf16(128, HD, 0, 1);
+  constexpr uint32_t idesc_nn = make_idesc_bf16(128, HD, 1, 1);
+
+  float acc_dk[HD], acc_dv[HD];
+#pragma unroll
+  for (int e = 0; e < HD; ++e) {
+    acc_dk[e] = 0.f;
+    acc_dv[e] = 0.f;
+  }
+
+  int it = 0;
+  for (int i = jblk; i < nblk; ++i, ++it) {
+    const int st = it & 1;
+    s_lse[tid] = lse2[stat_base + i * ATT_BLK + tid];
+    s_delta[tid] = delta[stat_base + i * ATT_BLK + tid];
+    if (it == 0) mbar_wait(bar_kv, 0);
+    mbar_wait(&bar_q[st], (it >> 1) & 1);
+    mbar_wait(bar_do, it & 1);
+    tc_fence_after();
+    __syncthreads();
+    if (tid == 0) {
+      const uint32_t ak = smem_u32(sK), av = smem_u32(sV), aq = smem_u32(sQ + st * C::TILE_BYTES), ado = smem_u32(sDO);
+#pragma unroll
+      for (int k = 0; k < HD / 16; ++k)
+        umma_bf16(tm_st, make_smem_desc(ak + k * 32, 16, C::SBO, C::SWZ), make_smem_desc(aq + k * 32, 16, C::SBO, C::SWZ),
+                  idesc_kk, k > 0);
+#pragma unroll
+      for (int k = 0; k < HD / 16; ++k)
+        umma_bf16(tm_dpt, make_smem_desc(av + k * 32, 16, C::SBO, C::SWZ), make_smem_desc(ado + k * 32, 16, C::SBO, C::SWZ),
+                  idesc_kk, k > 0);
+      umma_commit(bar_s);
+      if (i + 1 < nblk) {  // next Q tile (its buffer was last read by the MMAs of the previous iteration)
+        const int ns = st ^ 1;
+        mbar_expect_tx(&bar_q[ns], C::TILE_BYTES);
+        tma_load_2d(sQ + ns * C::TILE_BYTES, &tm_q, &bar_q[ns], h * HD, b * T + (i + 1) * ATT_BLK);
+      }
+    }
+    mbar_wait(bar_s, it & 1);
+    tc_fence_after();
+
+    const bool diag = (i == jblk);
+#pragma unroll 1
+    for (int c = 0; c < 4; ++c) {
+      uint32_t rs[32], rp[32];
+      tmem_ld_32x32b_x32(tm_st + lane_sel + c * 32, rs);
+      tmem_ld_32x32b_x32(tm_dpt + lane_sel + c * 32, rp);
+      tmem_ld_wait();
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        float p[8], ds[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const int q = c * 32 + g * 8 + e;
+          const float sv = __uint_as_float(rs[g * 8 + e]);
+          const float pv = (!diag || q >= tid) ? exp2f(sv * scale_log2 - s_lse[q]) : 0.f;
+          p[e] = pv;
+          ds[e] = pv * (__uint_as_float(rp[g * 8 + e]) - s_delta[q]);
+        }
+        const uint32_t off = p_tile_offset(tid, c * 4 + g);
+        *reinterpret_cast<uint4*>(sPt + off) =
+            make_uint4(pack_bf16x2(p[0], p[1]), pack_bf16x2(p[2], p[3]), pack_bf16x2(p[4], p[5]), pack_bf16x2(p[6], p[7]));
+        *reinterpret_cast<uint4*>(sDSt + off) = make_uint4(pack_bf16x2(ds[0], ds[1]), pack_bf16x2(ds[2], ds[3]),
+                                                           pack_bf16x2(ds[4], ds[5]), pack_bf16x2(ds[6], ds[7]));
+      }
+    }
+    fence_proxy_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    if (tid == 0) {
+      tc_fence_after();
+      const uint32_t apt = smem_u32(sPt), adst = smem_u32(sDSt), aq = smem_u32(sQ + st * C::TILE_BYTES),
+                     ado = smem_u32(sDO), ak = smem_u32(sK);
+#pragma unroll
+      for (int k = 0; k < ATT_BLK / 16; ++k) {
+        const uint32_t a_off = (k >> 2) * (ATT_BLK * 128) + (k & 3) * 32;
+        umma_bf16(tm_dv, make_smem_desc(apt + a_off, 16, 1024, SWZ_128B),
+                  make_smem_desc(ado + k * 16 * C::ROW_BYTES, 16, C::SBO, C::SWZ), idesc_kn, k > 0);
+      }
+#pragma unroll
+      for (int k = 0; k < ATT_BLK / 16; ++k) {
+        const uint32_t a_off = (k >> 2) * (ATT_BLK * 128) + (k & 3) * 32;
+        umma_bf16(tm_dk, make_smem_desc(adst + a_off, 16, 1024, SWZ_128B),
+                  make_smem_desc(aq + k * 16 * C::ROW_BYTES, 16, C::SBO, C::SWZ), idesc_kn, k > 0);
+      }
+#pragma unroll
+      for (int k = 0; k < ATT_BLK / 16; ++k)
+        umma_bf16(tm_dq, make_smem_desc(adst + k * 2048, ATT_BLK * 128, 1024, SWZ_128B),
+                  make_smem_desc(ak + k * 16 * C::ROW_BYTES, 16, C::SBO, C::SWZ), idesc_nn, k > 0);
+      umma_commit(bar_d);
+    }
+    mbar_wait(bar_d, it & 1);
+    tc_fence_after();
+    if (tid == 0 && i + 1 < nblk) {  // the dO tile is free again: fetch the next one behind this iteration's tail
+      mbar_expect_tx(bar_do, C::TILE_BYTES);
+      tma_load_2d(sDO, &tm_do, bar_do, h * HD, b * T + (i + 1) * ATT_BLK);
+    }
+    {
+      uint32_t rq[32], rv[32], rk[32];
+      tmem_ld_32x32b_x32(tm_dq + lane_sel, rq);
+      tmem_ld_32x32b_x32(tm_dv + lane_sel, rv);
+      tmem_ld_32x32b_x32(tm_dk + lane_sel, rk);
+      tmem_ld_wait();
+      float* dq_row = dq_accum + (long long)(b * T + i * ATT_BLK + tid) * lddq + h * HD;
+#pragma unroll
+      for (int e = 0; e < 32; e += 4)
+        asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dq_row + e), "f"(__uint_as_float(rq[e]) * scale),
+                     "f"(__uint_as_float(rq[e + 1]) * scale), "f"(__uint_as_float(rq[e + 2]) * scale),
+                     "f"(__uint_as_float(rq[e + 3]) * scale)
+                     : "memory");
+#pragma unroll
+      for (int e = 0; e < 32; ++e) {
+        acc_dv[e] += __uint_as_float(rv[e]);
+        acc_dk[e] += __uint_as_float(rk[e]);
+      }
+    }
+    tc_fence_before();
+    __syncthreads();
+  }
+
+  bf16* dk_row = dk + (long long)(kv_row0 + tid) * lddkv + h * HD;
+  bf16* dv_row = dv + (long long)(kv_row0 + tid) * lddkv + h * HD;
+#pragma unroll
+  for (int g = 0; g < HD / 8; ++g) {
+    const int e = g * 8;
+    *reinterpret_cast<uint4*>(dk_row + e) =
+        make_uint4(pack_bf16x2(acc_dk[e] * scale, acc_dk[e + 1] * scale), pack_bf16x2(acc_dk[e + 2] * scale, acc_dk[e + 3] * scale),
+                   pack_bf16x2(acc_dk[e + 4] * scale, acc_dk[e + 5] * scale), pack_bf16x2(acc_dk[e + 6] * scale, acc_dk[e + 7] * scale));
+    *reinterpret_cast<uint4*>(dv_row + e) = make_uint4(pack_bf16x2(acc_dv[e], acc_dv[e + 1]), pack_bf16x2(acc_dv[e + 2], acc_dv[e + 3]),
+                                                       pack_bf16x2(acc_dv[e + 4], acc_dv[e + 5]), pack_bf16x2(acc_dv[e + 6], acc_dv[e + 7]));
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 256);
+  }
+}
+
 template <int HD>
 static int attn_tmap(CUtensorMap* m, const void* p, long long rows, int H, long long ld) {
   return make_tmap_2d_bf16(m, p, rows, (uint64_t)H * HD, ld, ATT_BLK, HD,
@@ -693,6 +907,24 @@ static int launch_bwd(const void* q, const void* k, const void* v, long long ld,
     DTC_CHECK_CUDA(dtc::launch(attn_bwd_prep_kernel<HD>, (int)((threads + 255) / 256), 256, 0, stream, 
         reinterpret_cast<const bf16*>(o), ldo, reinterpret_cast<const bf16*>(d_o), lddo, delta, (int)M, T, H));
     DTC_CHECK_LAUNCH();
+  }
+  const float scale_ = 1.f / sqrtf((float)HD);
+  static const bool use_v1 = getenv("DTC_ATTN_BWD_V1") != nullptr;  // A/B switch: TMEM-accumulator kernel
+  if constexpr (HD == 32) {
+    if (!use_v1) {
+      const int smem2 = 5 * C::TILE_BYTES + 2 * C::P_BYTES + 2 * ATT_BLK * 4 + 1024 + 128;
+      auto kern2 = flash_attn_bwd_regacc_kernel<HD>;
+      static bool configured2 = false;
+      if (!configured2) {
+        DTC_CHECK_CUDA(cudaFuncSetAttribute(kern2, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
+        configured2 = true;
+      }
+      dim3 grid2(T / ATT_BLK, H, B);
+      DTC_CHECK_CUDA(dtc::launch(kern2, grid2, 128, smem2, stream, tq, tk, tv, tdo, lse2, delta, dq_accum, lddq,
+                                 reinterpret_cast<bf16*>(dk), reinterpret_cast<bf16*>(dv), lddkv, T, H, scale_,
+                                 scale_ * LOG2E));
+      return 0;
+    }
   }
   const int smem = 6 * C::TILE_BYTES + 2 * C::P_BYTES + 4 * ATT_BLK * 4 + 1024 + 128;
   auto kern = flash_attn_bwd_kernel<HD>;
