@@ -1026,12 +1026,16 @@ extern "C" int dtc_gemm_bf16(const void* A, long long lda, int a_mn_major, const
   // CTA-pair kernel: needs >= 256 rows; 256-wide tiles when that still leaves enough pair-tiles to fill the GPU
   // default policy (impl 0): the CTA-pair kernel pays off on the big GEMMs (lm_head: +27 % on dgrad / wgrad,
   // profiles/r1/gemm_microbench.txt); the layer GEMMs of this model are launch/latency-bound and stay 1-CTA
-  const bool big = 2.0 * M * N * (double)K >= 1e11;
+  // (measured, device time: lm_head dgrad 306 -> 237 us, wgrad 309 -> 246 us; the forward orientation — A K-major,
+  // B MN-major, 412 MB of output — is no faster with pairs: 299 vs 288 us, so it keeps the 1-CTA kernel)
+  const bool big = 2.0 * M * N * (double)K >= 1e11 && (a_mn_major || !b_mn_major);
   const bool want_2cta = (g_gemm_impl == 2 || g_gemm_impl == 3 || (g_gemm_impl == 0 && big && !env_v1)) &&
-                         epi_mode != EPI_MC_RED_BF16 && M >= 256 && N >= 128;
+                         epi_mode != EPI_MC_RED_BF16 && M >= 256 && N >= 128;  // impl 4 forces the 1-CTA persistent kernel
   if (want_2cta) {
     const long long tiles256 = (long long)((M + 255) / 256) * ((N + 255) / 256) * (splits > 1 ? splits : 1);
-    const bool wide = (block_n == 256) || (g_gemm_impl == 3 && block_n == 0 && N % 256 == 0 && tiles256 >= 64);
+    // 256-wide pair tiles (half the operand bytes per MMA cycle again) whenever they still fill all 74 CTA pairs;
+    // ragged N is fine: TMA zero-fills the loads and clips the stores
+    const bool wide = (block_n == 256) || ((g_gemm_impl == 3 || g_gemm_impl == 0) && block_n == 0 && tiles256 >= 74);
     if (stages == 0) stages = PG_STAGE_MAX;
 #define DTC_2CTA_DISPATCH(AMN, BMN)                                                                               \
   if (wide) return launch_gemm_2cta<AMN, BMN, 256>(A, lda, B, ldb, M, N, K, splits, stages, epi, stream);         \
