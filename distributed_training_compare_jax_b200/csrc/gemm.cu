@@ -52,6 +52,7 @@ struct GemmEpi {
   long long ldo;
   bf16* out2;
   long long ldo2;
+  unsigned long long* trace;  // debug: per-k-block clock64 timestamps of CTA 0 (null in production)
 };
 
 template <int BN>
@@ -311,14 +312,22 @@ struct PgSmem {
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int HALF_BYTES = BM * 128;                   // 128 rows x 64 bf16
   static constexpr int TILE_BYTES = (BN / 64) * HALF_BYTES;     // staging tile [128 x BN] bf16
-  static constexpr int bytes(int stages) { return stages * STAGE_BYTES + 2 * TILE_BYTES + 1024 + 256; }
+  // staging tiles: 2 (out + aux/out2), 1 in the DUAL variant, none for the fp32 register-path epilogues of DUAL
+  static constexpr int bytes(int stages, bool dual = false, bool staging = true) {
+    return stages * STAGE_BYTES + (dual ? (staging ? 1 : 0) : 2) * TILE_BYTES + 1024 + 256;
+  }
 };
 
 constexpr int PG_THREADS = 64 + 256;  // TMA warp, MMA warp, 8 epilogue warps (two per TMEM lane quadrant)
 DTC_DEVICE void epi_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
-template <bool A_MN, bool B_MN, int BN>
-__global__ void __launch_bounds__(PG_THREADS)
+// DUAL = two CTAs per SM.  Clock traces (tools/gemm_trace.py) show that ONE CTA gets its TMA tile loads served at a
+// fixed ~48 B/cycle (one 32 KB stage per 676 cycles, against 256 cycles of MMA work), whatever the number of stages
+// or issuing warps, while two co-resident CTAs are each served at that rate.  The DUAL variant therefore keeps the
+// CTA under 113 KB of shared memory (2-3 stages, ONE staging tile: the residual / pre-activation tile is TMA-loaded
+// into the output staging tile by the epilogue leader and overwritten in place) and 256 TMEM columns.
+template <bool A_MN, bool B_MN, int BN, bool DUAL>
+__global__ void __launch_bounds__(PG_THREADS, DUAL ? 2 : 1)
 gemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                        const __grid_constant__ CUtensorMap tma_out, const __grid_constant__ CUtensorMap tma_out2,
                        const __grid_constant__ CUtensorMap tma_aux, int M, int N, int K, int m_blocks, int n_blocks,
@@ -327,8 +336,8 @@ gemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* stage_out = smem + num_stages * S::STAGE_BYTES;  // out tile (bf16)
-  uint8_t* stage_aux = stage_out + S::TILE_BYTES;           // aux tile (input) or out2 tile (GELU output)
-  uint64_t* bars = reinterpret_cast<uint64_t*>(stage_aux + S::TILE_BYTES);
+  uint8_t* stage_aux = DUAL ? stage_out : stage_out + S::TILE_BYTES;  // aux tile (input) or out2 tile (GELU output)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(stage_out + (DUAL ? (epi.mode <= EPI_DGELU ? 1 : 0) : 2) * S::TILE_BYTES);
   uint64_t* full_bar = bars;                       // [PG_STAGE_MAX]
   uint64_t* empty_bar = bars + PG_STAGE_MAX;       // [PG_STAGE_MAX]
   uint64_t* tmem_full = bars + 2 * PG_STAGE_MAX;   // [2]
@@ -383,7 +392,7 @@ gemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
         const int m_blk = mn % m_blocks, n_blk = mn / m_blocks;
         const int kb_begin = split * kb_per_split;
         const int nkb = min(total_kb, kb_begin + kb_per_split) - kb_begin;
-        if (use_aux) {  // stage the residual / pre-activation tile for this output tile
+        if (use_aux && !DUAL) {  // stage the residual / pre-activation tile for this output tile
           mbar_wait(aux_empty, (it & 1) ^ 1);
           mbar_expect_tx(aux_full, S::TILE_BYTES);
 #pragma unroll
@@ -394,6 +403,7 @@ gemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
           const int s = kit % num_stages;
           const uint32_t ph = (kit / num_stages) & 1;
           mbar_wait(&empty_bar[s], ph ^ 1);
+          if (epi.trace && blockIdx.x == 0 && kit < 256) epi.trace[kit * 4 + 0] = clock64();
           uint8_t* sa = smem + s * S::STAGE_BYTES;
           uint8_t* sb = sa + S::A_BYTES;
           mbar_expect_tx(&full_bar[s], S::STAGE_BYTES);
@@ -410,6 +420,7 @@ gemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
           } else {
             tma_load_2d(sb, &tma_b, &full_bar[s], k0, n_blk * BN);
           }
+          if (epi.trace && blockIdx.x == 0 && kit < 256) epi.trace[kit * 4 + 1] = clock64();
         }
       }
     }
@@ -434,6 +445,7 @@ gemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
         mbar_wait(&full_bar[s], ph);
         tc_fence_after();
         if (elect_one()) {
+          if (epi.trace && blockIdx.x == 0 && kit < 256) epi.trace[kit * 4 + 2] = clock64();
           const uint32_t sa = smem_u32(smem + s * S::STAGE_BYTES);
           const uint32_t sb = sa + S::A_BYTES;
 #pragma unroll
@@ -444,6 +456,7 @@ gemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
           }
           umma_commit(&empty_bar[s]);
           if (i == nkb - 1) umma_commit(&tmem_full[buf]);
+          if (epi.trace && blockIdx.x == 0 && kit < 256) epi.trace[kit * 4 + 3] = clock64();
         }
         __syncwarp();
       }
@@ -457,6 +470,13 @@ gemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
     const bool store_leader = (threadIdx.x == 64);  // first epilogue thread issues the TMA stores
     const float alpha = epi.alpha;
     int it = 0;
+    if (DUAL && use_aux && store_leader && blockIdx.x < total_tiles) {  // aux tile of the first output tile
+      const int mn = blockIdx.x % tiles_mn;
+      mbar_expect_tx(aux_full, S::TILE_BYTES);
+#pragma unroll
+      for (int hf = 0; hf < BN / 64; ++hf)
+        tma_load_2d(stage_aux + hf * S::HALF_BYTES, &tma_aux, aux_full, (mn / m_blocks) * BN + hf * 64, (mn % m_blocks) * BM);
+    }
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
       const int mn = tile % tiles_mn;
       const int m_blk = mn % m_blocks, n_blk = mn / m_blocks;
@@ -466,8 +486,9 @@ gemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
       mbar_wait(&tmem_full[buf], (it >> 1) & 1);
       tc_fence_after();
       if (use_aux) mbar_wait(aux_full, it & 1);
-      if (bf16_out) {
+      if (bf16_out && !(DUAL && use_aux)) {
         // the previous tile's TMA stores must have finished READING the staging tiles before they are rewritten
+        // (DUAL with an aux tile: the leader already waited for that before it fetched this tile's aux tile)
         if (store_leader) tma_store_wait_read();
         epi_bar_sync();
       }
@@ -555,7 +576,7 @@ gemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
       __syncwarp();
       if (lane == 0) {
         mbar_arrive(&tmem_empty[buf]);
-        if (use_aux) mbar_arrive(aux_empty);
+        if (use_aux && !DUAL) mbar_arrive(aux_empty);
       }
       if (bf16_out) {
         fence_proxy_async_smem();
@@ -568,6 +589,16 @@ gemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
               tma_store_2d(&tma_out2, stage_aux + hf * S::HALF_BYTES, n_blk * BN + hf * 64, m_blk * BM);
           }
           tma_store_commit();
+          if (DUAL && use_aux && tile + (int)gridDim.x < total_tiles) {
+            // one staging tile: once the store has read it, fetch the NEXT tile's aux tile into it
+            tma_store_wait_read();
+            const int nmn = (tile + (int)gridDim.x) % tiles_mn;
+            mbar_expect_tx(aux_full, S::TILE_BYTES);
+#pragma unroll
+            for (int hf = 0; hf < BN / 64; ++hf)
+              tma_load_2d(stage_aux + hf * S::HALF_BYTES, &tma_aux, aux_full, (nmn / m_blocks) * BN + hf * 64,
+                          (nmn % m_blocks) * BM);
+          }
         }
       }
     }
@@ -593,7 +624,7 @@ static int num_sms() {
   return n;
 }
 
-template <bool A_MN, bool B_MN, int BN>
+template <bool A_MN, bool B_MN, int BN, bool DUAL>
 static int launch_gemm_persistent(const void* A, long long lda, const void* B, long long ldb, int M, int N, int K,
                                   int splits, int stages, const GemmEpi& epi, cudaStream_t stream) {
   using S = PgSmem<BN>;
@@ -627,17 +658,20 @@ static int launch_gemm_persistent(const void* A, long long lda, const void* B, l
   splits = (total_kb + kb_per_split - 1) / kb_per_split;
   if (stages < 2) stages = 2;
   if (stages > PG_STAGE_MAX) stages = PG_STAGE_MAX;
-  while (S::bytes(stages) > 227 * 1024) --stages;
-  const int smem_bytes = S::bytes(stages);
-  auto kern = gemm_persistent_kernel<A_MN, B_MN, BN>;
+  const int smem_cap = DUAL ? 112 * 1024 : 227 * 1024;  // DUAL: two CTAs (+1 KB reserved each) per 228 KB SM
+  const bool staging = epi.mode <= EPI_DGELU;
+  while (stages > 2 && S::bytes(stages, DUAL, staging) > smem_cap) --stages;
+  const int smem_bytes = S::bytes(stages, DUAL, staging);
+  auto kern = gemm_persistent_kernel<A_MN, B_MN, BN, DUAL>;
   static bool configured = false;
   if (!configured) {
-    DTC_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    DTC_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, DUAL ? 113 * 1024 : 227 * 1024));
     configured = true;
   }
   const int m_blocks = (M + BM - 1) / BM, n_blocks = (N + BN - 1) / BN;
   const int total_tiles = m_blocks * n_blocks * splits;
-  const int grid = total_tiles < num_sms() ? total_tiles : num_sms();
+  const int max_ctas = (DUAL ? 2 : 1) * num_sms();
+  const int grid = total_tiles < max_ctas ? total_tiles : max_ctas;
   DTC_CHECK_CUDA(dtc::launch(kern, grid, PG_THREADS, smem_bytes, stream, ta, tb, tout, tout2, taux, M, N, K, m_blocks, n_blocks, splits,
                                                    kb_per_split, stages, epi));
   DTC_CHECK_LAUNCH();
@@ -982,6 +1016,19 @@ static int launch_gemm_2cta(const void* A, long long lda, const void* B, long lo
 
 using namespace dtc;
 
+static int g_gemm_dual = 1;  // bit 0: allow the two-CTAs-per-SM persistent variant; bit 1: 64-wide tiles for small grids
+static int g_gemm_bn64 = 1;
+extern "C" int dtc_gemm_set_dual(int on) {
+  g_gemm_dual = on & 1;
+  g_gemm_bn64 = (on >> 1) & 1;
+  return 0;
+}
+static unsigned long long* g_gemm_trace = nullptr;  // debug timestamps (tools/gemm_trace.py)
+extern "C" int dtc_gemm_set_trace(unsigned long long* buf) {
+  g_gemm_trace = buf;
+  return 0;
+}
+
 static int g_gemm_impl = 0;  // 0 = persistent 1-CTA kernel, 1 = one-tile-per-CTA kernel, 2 = CTA-pair 256x128, 3 = CTA-pair, 256x256 where it fits
 // Tuning / A-B switch used by tools/gemm_bench.py.
 extern "C" int dtc_gemm_set_impl(int impl) {
@@ -1019,7 +1066,16 @@ extern "C" int dtc_gemm_bf16(const void* A, long long lda, int a_mn_major, const
   epi.ldo = ldo;
   epi.out2 = reinterpret_cast<bf16*>(out2);
   epi.ldo2 = ldo2;
-  if (block_n == 0) block_n = (N <= 64) ? 64 : 128;
+  epi.trace = g_gemm_trace;
+  if (block_n == 0) {
+    block_n = (N <= 64) ? 64 : 128;
+    // few 128-wide tiles (N = 512 layers: 128 tiles for 148 SMs): 64-wide tiles double the CTA count so that every SM
+    // runs two CTAs, each served by the TMA path at its own ~48 B/cycle
+    const long long t128 = (long long)((M + 127) / 128) * ((N + 127) / 128) * (splits > 1 ? splits : 1);
+    if (g_gemm_dual && g_gemm_bn64 && t128 <= num_sms() && N % 64 == 0 && epi_mode != EPI_BIAS_GELU &&
+        epi_mode != EPI_MC_RED_BF16)
+      block_n = 64;
+  }
   static const bool env_v1 = getenv("DTC_GEMM_V1") != nullptr;  // A/B switch: one-tile-per-CTA kernel
   const bool use_v1 = (env_v1 || g_gemm_impl == 1) && epi_mode != EPI_MC_RED_BF16;
   if (epi_mode == EPI_MC_RED_BF16 && block_n == 256) block_n = 128;
@@ -1048,9 +1104,19 @@ extern "C" int dtc_gemm_bf16(const void* A, long long lda, int a_mn_major, const
   }
   if (!use_v1 && block_n != 256) {
     if (stages == 0) stages = PG_STAGE_MAX;
-#define DTC_PGEMM_DISPATCH(AMN, BMN)                                                                              \
-  if (block_n == 64) return launch_gemm_persistent<AMN, BMN, 64>(A, lda, B, ldb, M, N, K, splits, stages, epi, stream); \
-  return launch_gemm_persistent<AMN, BMN, 128>(A, lda, B, ldb, M, N, K, splits, stages, epi, stream);
+    // two CTAs per SM whenever there is more than one tile per SM to hand out (not for the two-output GELU epilogue
+    // and the multicast-reduce epilogue, which need the second staging tile)
+    const long long tiles128 = (long long)((M + 127) / 128) * ((N + block_n - 1) / block_n) * (splits > 1 ? splits : 1);
+    // (always: the light configuration also lets a GEMM from the side stream share the SM)
+    const bool dual = g_gemm_dual && epi_mode != EPI_BIAS_GELU && epi_mode != EPI_MC_RED_BF16;
+    (void)tiles128;
+#define DTC_PGEMM_DISPATCH(AMN, BMN)                                                                                      \
+  if (dual) {                                                                                                             \
+    if (block_n == 64) return launch_gemm_persistent<AMN, BMN, 64, true>(A, lda, B, ldb, M, N, K, splits, stages, epi, stream);  \
+    return launch_gemm_persistent<AMN, BMN, 128, true>(A, lda, B, ldb, M, N, K, splits, stages, epi, stream);            \
+  }                                                                                                                       \
+  if (block_n == 64) return launch_gemm_persistent<AMN, BMN, 64, false>(A, lda, B, ldb, M, N, K, splits, stages, epi, stream);   \
+  return launch_gemm_persistent<AMN, BMN, 128, false>(A, lda, B, ldb, M, N, K, splits, stages, epi, stream);
     if (!a_mn_major && !b_mn_major) { DTC_PGEMM_DISPATCH(false, false) }
     if (!a_mn_major && b_mn_major) { DTC_PGEMM_DISPATCH(false, true) }
     if (a_mn_major && !b_mn_major) { DTC_PGEMM_DISPATCH(true, false) }

@@ -96,6 +96,7 @@ class NativeStageEngine(StageEngineBase):
         # stream concurrently with the dgrad / attention / LayerNorm chain.  Both streams then use the light GEMM
         # kernel (98 KB smem, 128 TMEM columns) so that two GEMM CTAs fit on one SM.
         self.overlap_wgrad = overlap_wgrad
+        self.bwd_gemm_impl = int(__import__('os').environ.get('DTC_BWD_GEMM_IMPL', '0'))
         self.side = None  # side stream of the workspace currently being processed (set in forward / backward)
         if self.device.type != "cuda":
             raise RuntimeError("the native engine needs a CUDA device (sm_100a)")
@@ -148,7 +149,9 @@ class NativeStageEngine(StageEngineBase):
             torch.cuda.current_stream().wait_stream(self.side)
 
     def backward_gemm_impl(self):
-        return Fn.gemm_impl(1 if self.side is not None else Fn.gemm_impl.current)
+        # default policy: the persistent kernel in its light (<= 113 KB, 256 TMEM columns) configuration, two of which
+        # share an SM — one from the backward chain, one from the parameter-gradient stream
+        return Fn.gemm_impl(self.bwd_gemm_impl)
 
     def tp_reduced_gemm(self, a, w, out) -> None:
         """out = sum over TP ranks of a · wᵀ (dX of a column-parallel Linear, collectives X5 / X8)."""

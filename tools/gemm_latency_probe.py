@@ -13,6 +13,7 @@ M, N = 4096, 512
 
 
 def t(K, impl, cold):
+    global N
     native.load().dtc_gemm_set_impl(impl)
     nset = 24 if cold else 1
     sets = [((torch.randn(M, K, device="cuda")).to(torch.bfloat16), (torch.randn(K, N, device="cuda") * 0.05).to(torch.bfloat16),
@@ -36,9 +37,15 @@ def t(K, impl, cold):
     return e0.elapsed_time(e1) * 1e3 / 48
 
 
-print(f"{'K':>6s} {'persist warm':>13s} {'persist cold':>13s} {'1tile warm':>11s} {'1tile cold':>11s}  (us per launch)")
+print(f"{'K':>6s} {'persist warm':>13s} {'persist cold':>13s} {'1tile warm':>11s} {'1tile cold':>11s} {'pair128 cold':>13s} {'pair256 cold':>13s}  (us per launch)")
 for K in (64, 128, 256, 512, 1024, 2048, 4096):
-    print(f"{K:6d} {t(K, 0, False):13.1f} {t(K, 0, True):13.1f} {t(K, 1, False):11.1f} {t(K, 1, True):11.1f}", flush=True)
+    print(f"{K:6d} {t(K, 4, False):13.1f} {t(K, 4, True):13.1f} {t(K, 1, False):11.1f} {t(K, 1, True):11.1f} "
+          f"{t(K, 2, True):13.1f} {t(K, 3, True):13.1f}", flush=True)
+N = 2048
+print("N = 2048:")
+for K in (64, 512, 2048):
+    print(f"{K:6d} {t(K, 4, False):13.1f} {t(K, 4, True):13.1f} {t(K, 1, False):11.1f} {t(K, 1, True):11.1f} "
+          f"{t(K, 2, True):13.1f} {t(K, 3, True):13.1f}", flush=True)
 # empty-ish kernel launch cost for reference
 x = torch.zeros(8, device="cuda")
 torch.cuda.synchronize()
