@@ -52,6 +52,7 @@ struct GemmEpi {
   long long ldo;
   bf16* out2;
   long long ldo2;
+  int coop_store;             // 1: epilogue warps copy the staged tile to global themselves (no TMA store)
   unsigned long long* trace;  // debug: per-k-block clock64 timestamps of CTA 0 (null in production)
 };
 
@@ -314,7 +315,7 @@ struct PgSmem {
   static constexpr int TILE_BYTES = (BN / 64) * HALF_BYTES;     // staging tile [128 x BN] bf16
   // staging tiles: 2 (out + aux/out2), 1 in the DUAL variant, none for the fp32 register-path epilogues of DUAL
   static constexpr int bytes(int stages, bool dual = false, bool staging = true) {
-    return stages * STAGE_BYTES + (dual ? (staging ? 1 : 0) : 2) * TILE_BYTES + 1024 + 256;
+    return stages * STAGE_BYTES + (dual ? (staging ? 1 : 0) : 2) * TILE_BYTES + 1024 + 256 + 1024 /* bias tiles */;
   }
 };
 
@@ -345,6 +346,7 @@ gemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
   uint64_t* aux_full = tmem_empty + 2;
   uint64_t* aux_empty = aux_full + 1;
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(aux_empty + 1);
+  bf16* s_bias = reinterpret_cast<bf16*>(bars + 32);  // [2][BN] bias slice of the current / next tile (256 B past the barriers)
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -483,10 +485,25 @@ gemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
       const int buf = it & 1;
       const long long gm = (long long)m_blk * BM + row;
       const bool row_ok = gm < M;
+      if (epi.trace && blockIdx.x == 0 && threadIdx.x == 64 && it < 32) epi.trace[1024 + it * 4 + 0] = clock64();
+      // bias slice of this tile -> smem while the mainloop is still running (a global load per 8-column group inside
+      // the accumulator loop costs ~400 cycles each, serialised: 3500 cycles per tile in the clock traces)
+      const bool has_bias = epi.bias != nullptr && mode != EPI_ATOMIC_F32 && mode != EPI_DGELU;
+      if (has_bias) {
+        const int et = threadIdx.x - 64;
+        if (et < BN / 8) {
+          const int n = n_blk * BN + et * 8;
+          uint4 bv = make_uint4(0, 0, 0, 0);
+          if (n < N) bv = *reinterpret_cast<const uint4*>(epi.bias + n);
+          *reinterpret_cast<uint4*>(s_bias + buf * BN + et * 8) = bv;
+        }
+      }
       mbar_wait(&tmem_full[buf], (it >> 1) & 1);
       tc_fence_after();
+      if (has_bias) epi_bar_sync();
+      if (epi.trace && blockIdx.x == 0 && threadIdx.x == 64 && it < 32) epi.trace[1024 + it * 4 + 1] = clock64();
       if (use_aux) mbar_wait(aux_full, it & 1);
-      if (bf16_out && !(DUAL && use_aux)) {
+      if (bf16_out && !(DUAL && use_aux) && !epi.coop_store) {
         // the previous tile's TMA stores must have finished READING the staging tiles before they are rewritten
         // (DUAL with an aux tile: the leader already waited for that before it fetched this tile's aux tile)
         if (store_leader) tma_store_wait_read();
@@ -505,8 +522,8 @@ gemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
           float v[8];
 #pragma unroll
           for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]) * alpha;
-          if (epi.bias != nullptr && mode != EPI_ATOMIC_F32 && mode != EPI_DGELU && n < N) {
-            const uint4 bb = *reinterpret_cast<const uint4*>(epi.bias + n);
+          if (has_bias) {
+            const uint4 bb = *reinterpret_cast<const uint4*>(s_bias + buf * BN + c * 32 + g * 8);
             const uint32_t bw[4] = {bb.x, bb.y, bb.z, bb.w};
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
@@ -572,13 +589,48 @@ gemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
         }
       }
       // accumulator buffer (and the aux tile) may be reused by the MMA / producer warps
+      if (epi.trace && blockIdx.x == 0 && threadIdx.x == 64 && it < 32) epi.trace[1024 + it * 4 + 2] = clock64();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) {
         mbar_arrive(&tmem_empty[buf]);
         if (use_aux && !DUAL) mbar_arrive(aux_empty);
       }
-      if (bf16_out) {
+      if (bf16_out && epi.coop_store) {
+        // The TMA queue of a CTA is served in order at ~48 B/cycle and is already saturated by the operand loads: the
+        // epilogue warps therefore write the staged tile out themselves (8 threads per 128-byte row: coalesced).
+        epi_bar_sync();
+        const int et = threadIdx.x - 64, ch = et & 7, r0 = et >> 3;
+#pragma unroll
+        for (int hf = 0; hf < BN / 64; ++hf) {
+          const int ncol = n_blk * BN + hf * 64 + ch * 8;
+          if (ncol < N) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const int r = r0 + 32 * i;
+              const long long grow = (long long)m_blk * BM + r;
+              if (grow < M) {
+                const uint32_t so = (uint32_t)hf * S::HALF_BYTES + swizzle_offset<3>(r * 128 + ch * 16);
+                *reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(epi.out) + grow * epi.ldo + ncol) =
+                    *reinterpret_cast<const uint4*>(stage_out + so);
+                if (mode == EPI_BIAS_GELU)
+                  *reinterpret_cast<uint4*>(epi.out2 + grow * epi.ldo2 + ncol) = *reinterpret_cast<const uint4*>(stage_aux + so);
+              }
+            }
+          }
+        }
+        epi_bar_sync();  // staging tile(s) free again
+        if (epi.trace && blockIdx.x == 0 && threadIdx.x == 64 && it < 32) epi.trace[1024 + it * 4 + 3] = clock64();
+        if (DUAL && use_aux && store_leader && tile + (int)gridDim.x < total_tiles) {
+          const int nmn = (tile + (int)gridDim.x) % tiles_mn;
+          fence_proxy_async_smem();
+          mbar_expect_tx(aux_full, S::TILE_BYTES);
+#pragma unroll
+          for (int hf = 0; hf < BN / 64; ++hf)
+            tma_load_2d(stage_aux + hf * S::HALF_BYTES, &tma_aux, aux_full, (nmn / m_blocks) * BN + hf * 64,
+                        (nmn % m_blocks) * BM);
+        }
+      } else if (bf16_out) {
         fence_proxy_async_smem();
         epi_bar_sync();
         if (store_leader) {
@@ -1018,9 +1070,11 @@ using namespace dtc;
 
 static int g_gemm_dual = 1;  // bit 0: allow the two-CTAs-per-SM persistent variant; bit 1: 64-wide tiles for small grids
 static int g_gemm_bn64 = 1;
+static int g_gemm_coop_store = 0;  // bit 2 of dtc_gemm_set_dual: epilogue warps store the tile (no TMA store)
 extern "C" int dtc_gemm_set_dual(int on) {
   g_gemm_dual = on & 1;
   g_gemm_bn64 = (on >> 1) & 1;
+  g_gemm_coop_store = (on >> 2) & 1;
   return 0;
 }
 static unsigned long long* g_gemm_trace = nullptr;  // debug timestamps (tools/gemm_trace.py)
@@ -1067,6 +1121,7 @@ extern "C" int dtc_gemm_bf16(const void* A, long long lda, int a_mn_major, const
   epi.out2 = reinterpret_cast<bf16*>(out2);
   epi.ldo2 = ldo2;
   epi.trace = g_gemm_trace;
+  epi.coop_store = g_gemm_coop_store;
   if (block_n == 0) {
     block_n = (N <= 64) ? 64 : 128;
     // few 128-wide tiles (N = 512 layers: 128 tiles for 148 SMs): 64-wide tiles double the CTA count so that every SM

@@ -16,17 +16,20 @@ M = 4096
 lib = native.load()
 lib.dtc_gemm_set_trace.argtypes = [C.c_void_p]
 lib.dtc_gemm_set_impl(4)
+lib.dtc_gemm_set_dual(int(os.environ.get('DUALBITS', '7')))
 a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
 b = (torch.randn(K, N, device="cuda") * 0.05).to(torch.bfloat16)
 o = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
 for _ in range(3):
     Fn.gemm(a, b, b_mn=True, out=o)
-trace = torch.zeros(256 * 4, device="cuda", dtype=torch.int64)
+trace = torch.zeros(256 * 4 + 32 * 4, device="cuda", dtype=torch.int64)
 lib.dtc_gemm_set_trace(trace.data_ptr())
 Fn.gemm(a, b, b_mn=True, out=o)
 torch.cuda.synchronize()
 lib.dtc_gemm_set_trace(None)
-t = trace.cpu().view(256, 4)
+full = trace.cpu()
+t = full[:1024].view(256, 4)
+te = full[1024:].view(32, 4)
 nk = min(K // 64 * ((M // 128) * (N // 128) + 147) // 148, 256)
 t0 = int(t[0, 0])
 print(f"M={M} N={N} K={K}: k-blocks traced {nk}; columns: stage-free, tma-issued, stage-full, mma-issued (cycles since start)")
@@ -37,3 +40,10 @@ for i in range(min(nk, 40)):
     gap = (r[2] - prev_full) if prev_full is not None else 0
     prev_full = r[2]
     print(f"kb {i:3d}: free {r[0]:7d}  issued {r[1]:7d}  full {r[2]:7d}  mma {r[3]:7d} | tma->full {lat:6d}  full-to-full {gap:6d}")
+
+print("epilogue (thread 64) per tile: wait-start, tmem_full seen, compute done, stores done (cycles since start)")
+for i in range(8):
+    r = [int(x) - t0 for x in te[i]]
+    if int(te[i][0]) == 0:
+        break
+    print(f"tile {i}: start {r[0]:7d}  full {r[1]:7d}  computed {r[2]:7d}  stored {r[3]:7d} | compute {r[2]-r[1]:6d}  store {r[3]-r[2]:6d}")
