@@ -207,6 +207,129 @@ dp_adamw_allgather_kernel(float* __restrict__ p, float* __restrict__ m, float* _
     if (i < o4 || i >= e4) reinterpret_cast<float4*>(g)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
 }
 
+
+// ---- bucketed variants: several disjoint ranges per launch, so that a layer's gradient can be reduce-scattered on a
+// ---- communication stream as soon as that layer's backward has finished (overlap with the rest of the backward).
+// Work is balanced over the CTAs: the ranges form one virtual index space (prefix sums), every thread maps its
+// group index back to (range, offset).
+constexpr int MAX_RANGES = 16;
+struct RangeList {
+  long long off[MAX_RANGES];     // first element of the sub-range THIS rank owns (multiple of 4)
+  long long prefix[MAX_RANGES + 1];  // prefix sums of the range lengths in 4-element groups
+  int count;
+};
+
+// grid.x CTAs; partials[blockIdx.x]
+template <bool USE_MC>
+__global__ void __launch_bounds__(256)
+dp_reduce_scatter_ranges_kernel(float* __restrict__ local_grad, const float* __restrict__ mc_grad, PeerPtrs peers, int rank,
+                                int world, RangeList ranges, float* __restrict__ partials) {
+  pdl_launch_dependents();
+  pdl_wait();
+  __shared__ float s[8];
+  const long long total4 = ranges.prefix[ranges.count];
+  float acc = 0.f;
+  // NVLink round trips are ~2 us: keep 4 independent 16-byte reductions in flight per thread
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < total4; i0 += 4 * stride) {
+    float4 v[4];
+    long long e[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long i = i0 + u * stride;
+      e[u] = -1;
+      if (i < total4) {
+        int r = 0;
+        while (r + 1 < ranges.count && i >= ranges.prefix[r + 1]) ++r;
+        e[u] = ranges.off[r] + (i - ranges.prefix[r]) * 4;
+        if (USE_MC) {
+          v[u] = mc_ld_reduce_add_f32x4(mc_grad + e[u]);
+        } else {
+          v[u] = *reinterpret_cast<const float4*>(local_grad + e[u]);
+          for (int pr0 = 1; pr0 < world; ++pr0) {
+            const int pr = (rank + pr0) % world;
+            const float4 w = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(peers.p[pr]) + e[u]);
+            v[u].x += w.x; v[u].y += w.y; v[u].z += w.z; v[u].w += w.w;
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      if (e[u] >= 0) {
+        *reinterpret_cast<float4*>(local_grad + e[u]) = v[u];
+        acc += v[u].x * v[u].x + v[u].y * v[u].y + v[u].z * v[u].z + v[u].w * v[u].w;
+      }
+    }
+  }
+  acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float v = threadIdx.x < 8 ? s[threadIdx.x] : 0.f;
+    v = warp_sum(v);
+    if (threadIdx.x == 0) partials[blockIdx.x] = v;
+  }
+}
+
+// AdamW + all-gather over a device-resident table of the owned sub-ranges: offs[n_ranges] (multiples of 8) and
+// prefix[n_ranges + 1] (prefix sums of the lengths in 8-element groups).  The gradient buffer is cleared by the caller.
+template <bool USE_MC>
+__global__ void __launch_bounds__(256)
+dp_adamw_allgather_ranges_kernel(float* __restrict__ p, float* __restrict__ m, float* __restrict__ v, float* __restrict__ g,
+                                 bf16* __restrict__ mc_compute, PeerPtrs compute_peers, int world,
+                                 const long long* __restrict__ offs, const long long* __restrict__ prefix, int n_ranges,
+                                 const float* __restrict__ scalars, const int* __restrict__ step_ptr, float lr, float b1,
+                                 float b2, float eps, float wd) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const float clip = scalars[1];
+  const float t = (float)*step_ptr;
+  const float bc1 = 1.f / (1.f - powf(b1, t));
+  const float bc2 = 1.f / (1.f - powf(b2, t));
+  const long long total8 = prefix[n_ranges];
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total8; i += (long long)gridDim.x * blockDim.x) {
+    int lo = 0, hi = n_ranges - 1;  // last range whose prefix <= i
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (prefix[mid] <= i) lo = mid; else hi = mid - 1;
+    }
+    const long long e = offs[lo] + (i - prefix[lo]) * 8;
+    float pa[8], ma[8], va[8], ga[8];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const float4 pp = *reinterpret_cast<const float4*>(p + e + 4 * h);
+      const float4 mm = *reinterpret_cast<const float4*>(m + e + 4 * h);
+      const float4 vv = *reinterpret_cast<const float4*>(v + e + 4 * h);
+      const float4 gg = *reinterpret_cast<const float4*>(g + e + 4 * h);
+      pa[4 * h] = pp.x; pa[4 * h + 1] = pp.y; pa[4 * h + 2] = pp.z; pa[4 * h + 3] = pp.w;
+      ma[4 * h] = mm.x; ma[4 * h + 1] = mm.y; ma[4 * h + 2] = mm.z; ma[4 * h + 3] = mm.w;
+      va[4 * h] = vv.x; va[4 * h + 1] = vv.y; va[4 * h + 2] = vv.z; va[4 * h + 3] = vv.w;
+      ga[4 * h] = gg.x; ga[4 * h + 1] = gg.y; ga[4 * h + 2] = gg.z; ga[4 * h + 3] = gg.w;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float gj = ga[j] * clip;
+      ma[j] = b1 * ma[j] + (1.f - b1) * gj;
+      va[j] = b2 * va[j] + (1.f - b2) * gj * gj;
+      pa[j] -= lr * ((ma[j] * bc1) / (sqrtf(va[j] * bc2) + eps) + wd * pa[j]);
+    }
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      *reinterpret_cast<float4*>(p + e + 4 * h) = make_float4(pa[4 * h], pa[4 * h + 1], pa[4 * h + 2], pa[4 * h + 3]);
+      *reinterpret_cast<float4*>(m + e + 4 * h) = make_float4(ma[4 * h], ma[4 * h + 1], ma[4 * h + 2], ma[4 * h + 3]);
+      *reinterpret_cast<float4*>(v + e + 4 * h) = make_float4(va[4 * h], va[4 * h + 1], va[4 * h + 2], va[4 * h + 3]);
+    }
+    const uint4 packed = make_uint4(pack_bf16x2(pa[0], pa[1]), pack_bf16x2(pa[2], pa[3]), pack_bf16x2(pa[4], pa[5]),
+                                    pack_bf16x2(pa[6], pa[7]));
+    if (USE_MC) {
+      mc_st_b32x4(mc_compute + e, packed);
+    } else {
+      for (int r = 0; r < world; ++r) *reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(compute_peers.p[r]) + e) = packed;
+    }
+  }
+}
+
 }  // namespace dtc
 
 using namespace dtc;
@@ -283,5 +406,54 @@ extern "C" int dtc_dp_adamw_allgather(float* p, float* m, float* v, float* g, un
     DTC_CHECK_CUDA(dtc::launch(dp_adamw_allgather_kernel<false>, (int)blocks, 256, 0, stream, p, m, v, g, nullptr, peers, world, off, n, total_n,
                                                                        scalars, step_ptr, lr, b1, b2, eps, wd));
   DTC_CHECK_LAUNCH();
+  return 0;
+}
+
+// ---- bucketed API ------------------------------------------------------------------------------------------------
+// offs / lens: HOST arrays (count <= 16) of the sub-ranges this rank owns inside one bucket (lengths multiples of 4);
+// `blocks` CTAs share the work evenly; partials must hold `blocks` floats.
+extern "C" int dtc_dp_reduce_scatter_ranges(float* local_grad, unsigned long long mc_grad, const unsigned long long* grad_ptrs,
+                                            int rank, int world, const long long* offs, const long long* lens, int count,
+                                            int blocks, float* partials, cudaStream_t stream) {
+  DTC_CHECK_ARG(count >= 1 && count <= MAX_RANGES, "dp_reduce_scatter_ranges: %d ranges (max %d)", count, MAX_RANGES);
+  DTC_CHECK_ARG(blocks >= 1, "dp_reduce_scatter_ranges: blocks");
+  PeerPtrs peers;
+  int rc = fill_peers(&peers, grad_ptrs, world);
+  if (rc) return rc;
+  RangeList rl;
+  rl.count = count;
+  rl.prefix[0] = 0;
+  for (int i = 0; i < MAX_RANGES; ++i) {
+    rl.off[i] = i < count ? offs[i] : 0;
+    const long long n = i < count ? lens[i] : 0;
+    DTC_CHECK_ARG(rl.off[i] % 4 == 0 && n % 4 == 0, "dp_reduce_scatter_ranges: range %d not 4-aligned", i);
+    rl.prefix[i + 1] = rl.prefix[i] + n / 4;
+  }
+  if (mc_grad)
+    DTC_CHECK_CUDA(dtc::launch(dp_reduce_scatter_ranges_kernel<true>, blocks, 256, 0, stream, local_grad,
+                               reinterpret_cast<const float*>(mc_grad), peers, rank, world, rl, partials));
+  else
+    DTC_CHECK_CUDA(dtc::launch(dp_reduce_scatter_ranges_kernel<false>, blocks, 256, 0, stream, local_grad, nullptr, peers, rank,
+                               world, rl, partials));
+  return 0;
+}
+
+// offs [n_ranges] / prefix [n_ranges + 1]: DEVICE arrays (long long); prefix in 8-element groups.
+extern "C" int dtc_dp_adamw_allgather_ranges(float* p, float* m, float* v, float* g, unsigned long long mc_compute,
+                                             const unsigned long long* compute_ptrs, int world, const long long* offs,
+                                             const long long* prefix, int n_ranges, int blocks, const float* scalars,
+                                             const int* step_ptr, float lr, float b1, float b2, float eps, float wd,
+                                             cudaStream_t stream) {
+  DTC_CHECK_ARG(n_ranges >= 1 && blocks >= 1, "dp_adamw_allgather_ranges: empty launch");
+  PeerPtrs peers;
+  int rc = fill_peers(&peers, compute_ptrs, world);
+  if (rc) return rc;
+  if (mc_compute)
+    DTC_CHECK_CUDA(dtc::launch(dp_adamw_allgather_ranges_kernel<true>, blocks, 256, 0, stream, p, m, v, g,
+                               reinterpret_cast<bf16*>(mc_compute), peers, world, offs, prefix, n_ranges, scalars, step_ptr, lr,
+                               b1, b2, eps, wd));
+  else
+    DTC_CHECK_CUDA(dtc::launch(dp_adamw_allgather_ranges_kernel<false>, blocks, 256, 0, stream, p, m, v, g, nullptr, peers,
+                               world, offs, prefix, n_ranges, scalars, step_ptr, lr, b1, b2, eps, wd));
   return 0;
 }

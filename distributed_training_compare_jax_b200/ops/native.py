@@ -45,6 +45,8 @@ _PROTOS: dict[str, list[Any]] = {
     "dtc_dp_reduce_scatter": [P, U64, P, I, I, L, L, P],
     "dtc_dp_norm_exchange": [P, I, P, P, I, I, I, F, P, P],
     "dtc_dp_adamw_allgather": [P, P, P, P, U64, P, I, L, L, L, P, P, F, F, F, F, F],
+    "dtc_dp_reduce_scatter_ranges": [P, U64, P, I, I, P, P, I, I, P],
+    "dtc_dp_adamw_allgather_ranges": [P, P, P, P, U64, P, I, P, P, I, I, P, P, F, F, F, F, F],
 }
 # launches per call (for the gpu_launches accounting in bench.py)
 _LAUNCH_COUNT = {"dtc_flash_attn_bwd": 2}

@@ -80,9 +80,18 @@ class BucketedAllReduce:
 
 
 class FusedShardedStep:
-    """reduce-scatter(+‖g‖²) → norm exchange → sharded AdamW + all-gather, all through symmetric memory."""
+    """reduce-scatter(+‖g‖²) → norm exchange → sharded AdamW + all-gather, all through symmetric memory.
 
-    def __init__(self, cfg, engine, mesh):
+    ``overlap=True`` (default): the gradient is cut into buckets in the order the backward pass finishes them (head,
+    layer L-1 … 0, embeddings); each bucket's tensors are split 1/n per rank and reduce-scattered by ONE multi-range
+    kernel on a communication stream as soon as the bucket is final on every rank (flag barrier on that stream), while
+    the main stream keeps running the backward pass.  ``overlap=False``: one contiguous shard per rank, reduced after
+    the backward pass."""
+
+    RS_BLOCKS = 296            # reduce-scatter CTAs per bucket launch (NVLink latency needs many loads in flight)
+    ADAMW_BLOCKS = 1184
+
+    def __init__(self, cfg, engine, mesh, overlap: bool = True):
         self.cfg, self.engine, self.mesh, self.store = cfg, engine, mesh, engine.store
         st, dp = self.store, mesh.dp
         if not getattr(st, "symm", None):
@@ -90,15 +99,87 @@ class FusedShardedStep:
         self.grad, self.compute = st.symm["grad"], st.symm["compute"]
         self.norm_slots = SymmBuffer(16, torch.float32, st.device, dp.group)
         self.barrier = FlagBarrier(st.device, dp.group)
-        n = st.numel
-        per = -(-(n // dp.size) // 64) * 64
-        self.off = min(dp.rank * per, n)
-        self.n = max(0, min(n, self.off + per) - self.off)
-        self.n_partials = int(native.load().dtc_dp_num_partials(max(self.n, 4)))
-        self.partials = torch.zeros(self.n_partials, device=st.device, dtype=torch.float32)
         self.scalars = torch.zeros(2, device=st.device, dtype=torch.float32)
         self.max_norm = cfg.grad_clip
         self.uses_multicast = bool(self.grad.mc_ptr and self.compute.mc_ptr)
+        self.overlap = overlap and engine.n_micro == 1
+        n = st.numel
+        if not self.overlap:
+            per = -(-(n // dp.size) // 64) * 64
+            self.off = min(dp.rank * per, n)
+            self.n = max(0, min(n, self.off + per) - self.off)
+            self.n_partials = int(native.load().dtc_dp_num_partials(max(self.n, 4)))
+            self.partials = torch.zeros(self.n_partials, device=st.device, dtype=torch.float32)
+            return
+        self._build_buckets()
+        self.stream = torch.cuda.Stream(device=st.device)
+        import os
+        self.late = os.environ.get("DTC_DP_LATE") == "1"  # debugging: bucketed kernels, but all after the backward pass
+        if not self.late:
+            engine.on_head_grads_ready = lambda: self._launch_bucket(self.bucket_of_head)
+            engine.on_layer_grads_ready = lambda l: self._launch_bucket(self.bucket_of_layer[l])
+            engine.has_grad_hooks = True
+
+    # ------------------------------------------------------------------ bucket construction
+    def _build_buckets(self) -> None:
+        import ctypes as C
+        st, dp, L = self.store, self.mesh.dp, self.engine.local.L
+
+        def numel(shape):
+            k = 1
+            for d in shape:
+                k *= d
+            return k
+
+        head = [(st.offsets[k][0], numel(st.offsets[k][1])) for k in ("lnf_g", "lnf_b", "wlm", "blm") if k in st.offsets]
+        embed = [(st.offsets[k][0], numel(st.offsets[k][1])) for k in ("wte", "wpe") if k in st.offsets]
+        layers = []
+        for l in range(L):
+            sl = []
+            for name, (off, shape) in st.offsets.items():
+                if name not in ("wte", "wpe", "wlm", "blm", "lnf_g", "lnf_b"):
+                    per = numel(shape[1:])
+                    sl.append((off + l * per, per))
+            layers.append(sl)
+        full = ([head] if head else []) + [layers[l] for l in reversed(range(L))] + ([embed] if embed else [])
+        self.bucket_of_head = 0 if head else None
+        self.bucket_of_layer = {l: (1 if head else 0) + i for i, l in enumerate(reversed(range(L)))}
+        self.bucket_of_embed = len(full) - 1 if embed else None
+        self.buckets, owned_all, p_off = [], [], 0
+        for ranges in full:
+            offs, lens = [], []
+            for off, cnt in ranges:
+                chunk = -(-(-(-cnt // dp.size)) // 8) * 8          # ceil(cnt / n) rounded up to 8 elements
+                lo = min(dp.rank * chunk, cnt)
+                hi = min((dp.rank + 1) * chunk, cnt)
+                offs.append(off + lo)
+                lens.append(hi - lo)
+                if hi > lo:
+                    owned_all.append((off + lo, hi - lo))
+            k = len(offs)
+            blocks = max(1, min(self.RS_BLOCKS, -(-sum(lens) // (4 * 256 * 4))))
+            self.buckets.append({"offs": (C.c_longlong * k)(*offs), "lens": (C.c_longlong * k)(*lens), "count": k,
+                                 "partials_off": p_off, "blocks": blocks})
+            p_off += blocks
+        self.n_partials = p_off
+        self.partials = torch.zeros(p_off, device=st.device, dtype=torch.float32)
+        self.owned = owned_all
+        prefix = [0]
+        for _, k in owned_all:
+            prefix.append(prefix[-1] + k // 8)
+        self.tab_offs = torch.tensor([o for o, _ in owned_all], dtype=torch.int64, device=st.device)
+        self.tab_prefix = torch.tensor(prefix, dtype=torch.int64, device=st.device)
+        self.n_owned = len(owned_all)
+
+    def _launch_bucket(self, b) -> None:
+        if b is None:
+            return
+        st, dp, bk = self.store, self.mesh.dp, self.buckets[b]
+        self.stream.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(self.stream):
+            self.barrier(3 + b % 12)  # the bucket is final on every rank before anyone reads its peers' copies
+            native.call("dtc_dp_reduce_scatter_ranges", st.flat_grad, self.grad.mc_ptr, self.grad.ptr_array, dp.rank, dp.size,
+                        bk["offs"], bk["lens"], bk["count"], bk["blocks"], self.partials[bk["partials_off"]:])
 
     @property
     def last_norm(self):
@@ -106,26 +187,44 @@ class FusedShardedStep:
 
     def step(self) -> None:
         st, dp, c = self.store, self.mesh.dp, self.cfg
-        self.barrier(0)  # every rank's backward has finished writing its gradient
-        native.call("dtc_dp_reduce_scatter", st.flat_grad, self.grad.mc_ptr, self.grad.ptr_array, dp.rank, dp.size,
-                    self.off, self.n, self.partials)
+        if self.overlap:
+            if self.late:
+                for b in range(len(self.buckets) - 1):
+                    self._launch_bucket(b)
+            self._launch_bucket(self.bucket_of_embed)
+            torch.cuda.current_stream().wait_stream(self.stream)
+        else:
+            self.barrier(0)  # every rank's backward has finished writing its gradient
+            native.call("dtc_dp_reduce_scatter", st.flat_grad, self.grad.mc_ptr, self.grad.ptr_array, dp.rank, dp.size,
+                        self.off, self.n, self.partials)
         native.call("dtc_dp_norm_exchange", self.partials, self.n_partials, self.norm_slots.ptr_array,
                     self.barrier.ptr_array, dp.rank, dp.size, 1, float(self.max_norm), self.scalars, st.step)
-        native.call("dtc_dp_adamw_allgather", st.flat_master, st.flat_m, st.flat_v, st.flat_grad, self.compute.mc_ptr,
-                    self.compute.ptr_array, dp.size, self.off, self.n, st.numel, self.scalars, st.step, float(c.lr),
-                    float(c.b1), float(c.b2), float(c.eps), float(c.weight_decay))
+        if self.overlap:
+            native.call("dtc_dp_adamw_allgather_ranges", st.flat_master, st.flat_m, st.flat_v, st.flat_grad,
+                        self.compute.mc_ptr, self.compute.ptr_array, dp.size, self.tab_offs, self.tab_prefix, self.n_owned,
+                        self.ADAMW_BLOCKS, self.scalars,
+                        st.step, float(c.lr), float(c.b1), float(c.b2), float(c.eps), float(c.weight_decay))
+            st.flat_grad.zero_()  # every rank is past the norm-exchange barrier: nobody reads this gradient any more
+        else:
+            native.call("dtc_dp_adamw_allgather", st.flat_master, st.flat_m, st.flat_v, st.flat_grad, self.compute.mc_ptr,
+                        self.compute.ptr_array, dp.size, self.off, self.n, st.numel, self.scalars, st.step, float(c.lr),
+                        float(c.b1), float(c.b2), float(c.eps), float(c.weight_decay))
         self.barrier(2)  # every rank's compute copy is complete before the next forward reads it
+
+    def _owned_ranges(self):
+        if self.overlap:
+            return list(self.owned)
+        return [(self.off, self.n)] if self.n else []
 
     def sync_full_state(self) -> None:
         """Checkpointing: master weights / Adam moments are only current on the owning rank — gather them."""
         st, dp = self.store, self.mesh.dp
-        per = -(-(st.numel // dp.size) // 64) * 64
+        gathered = [None] * dp.size
+        dist.all_gather_object(gathered, self._owned_ranges(), group=dp.group)
         for flat in (st.flat_master, st.flat_m, st.flat_v):
             for r in range(dp.size):
-                off = min(r * per, st.numel)
-                n = max(0, min(st.numel, off + per) - off)
-                if n:
-                    dist.broadcast(flat[off:off + n], src=dp.ranks[r], group=dp.group)
+                for off, k in gathered[r]:
+                    dist.broadcast(flat[off:off + k], src=dp.ranks[r], group=dp.group)
 
 
 def make_grad_reducer(engine, mesh):

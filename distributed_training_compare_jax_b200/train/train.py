@@ -59,7 +59,7 @@ def build_state(train_config: TrainConfig, model_config: ModelConfig, opt_config
         attach_fused_tp(engine, mesh)
     if fused_dp:
         from ..parallel.dp import FusedShardedStep
-        opt = FusedShardedStep(opt_config, engine, mesh)
+        opt = FusedShardedStep(opt_config, engine, mesh, overlap=train_config.dp_overlap)
     else:
         opt = create_optimizer(opt_config).bind(engine, mesh, clip_scope=clip_scope, clip_scale=clip_scale,
                                                 grad_reducer=reducer)

@@ -99,6 +99,31 @@ int dtc_adamw(float* p, float* m, float* v, float* g, void* p_bf16, long long n,
               cudaStream_t stream);
 int dtc_colsum(const void* x, long long ld, int M, int N, float* out, cudaStream_t stream);
 
+/* ---- symmetric-memory data-parallel step (R10 R11 R13, X1 X2; ref: the gradient all-reduce GSPMD inserts for
+ *      parallel/sharding.py:25-27 + train/create_train_step.py:34-40, then train/create_optimizer.py:9-12) ----
+ * *_ptrs: HOST arrays of `world` device addresses (every rank's copy of a symmetric buffer); mc_*: NVSwitch
+ * multicast address of the same buffer (0 = none: peer loads / stores are used instead). */
+int dtc_symm_barrier(const unsigned long long* flag_ptrs, int rank, int world, int slot, cudaStream_t stream);
+int dtc_dp_num_partials(long long n);
+int dtc_dp_reduce_scatter(float* local_grad, unsigned long long mc_grad, const unsigned long long* grad_ptrs, int rank,
+                          int world, long long off, long long n, float* partials, cudaStream_t stream);
+int dtc_dp_reduce_scatter_ranges(float* local_grad, unsigned long long mc_grad, const unsigned long long* grad_ptrs,
+                                 int rank, int world, const long long* offs, const long long* lens, int count,
+                                 int blocks, float* partials, cudaStream_t stream);
+int dtc_dp_norm_exchange(const float* partials, int n_partials, const unsigned long long* norm_slot_ptrs,
+                         const unsigned long long* flag_ptrs, int rank, int world, int slot, float max_norm,
+                         float* scalars, int* step, cudaStream_t stream);
+int dtc_dp_adamw_allgather(float* p, float* m, float* v, float* g, unsigned long long mc_compute,
+                           const unsigned long long* compute_ptrs, int world, long long off, long long n,
+                           long long total_n, const float* scalars, const int* step_ptr, float lr, float b1, float b2,
+                           float eps, float wd, cudaStream_t stream);
+int dtc_dp_adamw_allgather_ranges(float* p, float* m, float* v, float* g, unsigned long long mc_compute,
+                                  const unsigned long long* compute_ptrs, int world, const long long* offs,
+                                  const long long* prefix, int n_ranges, int blocks, const float* scalars,
+                                  const int* step_ptr, float lr, float b1, float b2, float eps, float wd,
+                                  cudaStream_t stream);
+int dtc_gemm_set_dual(int bits);   /* tuning: bit0 two-CTAs-per-SM GEMM, bit1 64-wide tiles for small grids, bit2 coop stores */
+
 #ifdef __cplusplus
 }
 #endif
