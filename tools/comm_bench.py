@@ -1,0 +1,112 @@
+"""Micro-benchmark of the fused compute+collective kernels against their NCCL counterparts and the NVLink roofline.
+    torchrun --nproc-per-node N tools/comm_bench.py
+DP: reduce-scatter of the 89.6 M-parameter fp32 gradient (multimem.ld_reduce) and sharded AdamW + bf16 all-gather
+(multimem.st) vs one NCCL all-reduce of the same buffer.  TP: row-parallel GEMM whose epilogue all-reduces through
+multimem.red (+ flag barrier) vs the same GEMM followed by an NCCL all-reduce.  CUDA events, max over ranks."""
+import json
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from distributed_training_compare_jax_b200.ops import functional as Fn  # noqa: E402
+from distributed_training_compare_jax_b200.ops import native  # noqa: E402
+from distributed_training_compare_jax_b200.parallel.symm import FlagBarrier, SymmBuffer  # noqa: E402
+
+rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+torch.cuda.set_device(rank)
+dev = torch.device("cuda", rank)
+dist.init_process_group("nccl", device_id=dev)
+grp = dist.group.WORLD
+LINK = 770e9  # measured peer copy bandwidth per direction per GPU (B200_PROFILING.md)
+
+
+def timed(fn, iters=10, warm=3):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) / iters], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return t.item() * 1e3  # us
+
+
+out = {"n_gpus": world}
+# ---------------------------------------------------------------- DP
+n = 89_633_792  # flat buffer of the reference model (64-element aligned)
+grad = SymmBuffer(n, torch.float32, dev, grp)
+comp = SymmBuffer(n, torch.bfloat16, dev, grp)
+bar = FlagBarrier(dev, grp)
+per = -(-(n // world) // 64) * 64
+off = min(rank * per, n)
+cnt = max(0, min(n, off + per) - off)
+npart = int(native.load().dtc_dp_num_partials(cnt))
+partials = torch.zeros(npart, device=dev)
+p = torch.randn(n, device=dev)
+m = torch.zeros(n, device=dev)
+v = torch.zeros(n, device=dev)
+scal = torch.tensor([1.0, 1.0], device=dev)
+step = torch.ones(1, device=dev, dtype=torch.int32)
+grad.tensor.normal_()
+
+
+def rs():
+    bar(0)
+    native.call("dtc_dp_reduce_scatter", grad.tensor, grad.mc_ptr, grad.ptr_array, rank, world, off, cnt, partials)
+
+
+def adam_ag():
+    native.call("dtc_dp_adamw_allgather", p, m, v, grad.tensor, comp.mc_ptr, comp.ptr_array, world, off, cnt, n, scal, step,
+                3e-4, 0.9, 0.999, 1e-8, 0.1)
+    bar(2)
+
+
+g2 = torch.randn(n, device=dev)
+t_rs, t_ag = timed(rs), timed(adam_ag)
+t_nccl = timed(lambda: dist.all_reduce(g2))
+bytes_rs = (world - 1) / world * n * 4        # every rank ships the (n-1)/n of its gradient it does not own
+bytes_ag = (world - 1) / world * n * 2 / 1    # every rank receives the other ranks' bf16 shards
+out["dp"] = {"multicast": bool(grad.mc_ptr), "reduce_scatter_us": t_rs, "reduce_scatter_GBps_per_gpu": bytes_rs / t_rs / 1e3,
+             "reduce_scatter_frac_of_770GBps": bytes_rs / (t_rs * 1e-6) / LINK,
+             "adamw_allgather_us": t_ag, "allgather_GBps_per_gpu": bytes_ag / t_ag / 1e3,
+             "nccl_allreduce_fp32_us": t_nccl, "nccl_busbw_GBps": 2 * (world - 1) / world * n * 4 / t_nccl / 1e3}
+del p, m, v, g2
+# ---------------------------------------------------------------- TP (fc2-like row-parallel GEMM of the reference model)
+M, D, F = 4096, 512, 2048 // world
+x = (torch.randn(M, F, device=dev)).to(torch.bfloat16)
+w = (torch.randn(F, D, device=dev) * 0.05).to(torch.bfloat16)
+buf = SymmBuffer(M * D, torch.bfloat16, dev, grp)
+outb = torch.empty(M, D, device=dev, dtype=torch.bfloat16)
+slot = [0]
+
+
+def fused():
+    Fn.gemm(x, w, b_mn=True, epi="mc_red", mc_out=(buf.mc_ptr, D))
+    bar(3 + slot[0] % 12)
+    slot[0] += 1
+    outb.copy_(buf.tensor.view(M, D))
+    buf.tensor.zero_()
+
+
+def unfused():
+    Fn.gemm(x, w, b_mn=True, out=outb)
+    dist.all_reduce(outb)
+
+
+if buf.mc_ptr:
+    t_f = timed(fused, iters=20)
+    t_u = timed(unfused, iters=20)
+    wire = M * D * 2  # bf16 tile data every rank must push into the switch once
+    out["tp"] = {"fused_gemm_mcred_barrier_copy_zero_us": t_f, "gemm_plus_nccl_allreduce_us": t_u,
+                 "wire_time_at_770GBps_us": wire / LINK * 1e6, "shape": [M, D, F]}
+if rank == 0:
+    print(json.dumps(out))
+dist.destroy_process_group()
