@@ -74,7 +74,7 @@ def run(args) -> dict | None:
                      output_dir="outputs/bench", pp_microbatches=args.pp_microbatches, warmup_steps=args.warmup,
                      global_batch_is_per_device=True, sync_every_step=True, backend=args.backend,
                      pp_schedule=args.pp_schedule, fused_comm=not args.no_fused_comm, cuda_graph=not args.no_graph,
-                     dp_overlap=not args.no_dp_overlap)
+                     dp_overlap=not args.no_dp_overlap, tp_fused=args.tp_fused)
     mc = load_model_config(os.path.join(ROOT, args.model_config), vocab_size=VOCAB_SIZE, parallel=strategy)
     oc = load_optim_config(os.path.join(ROOT, "configs/optim_config.yaml"))
     dp, tp, pp = mesh_shape(tc, world)
@@ -193,6 +193,7 @@ def main() -> int:
     ap.add_argument("--backend", default="auto")
     ap.add_argument("--no-fused-comm", action="store_true")
     ap.add_argument("--no-dp-overlap", action="store_true")
+    ap.add_argument("--tp-fused", action="store_true", help="TP: fused GEMM + multimem.red all-reduce epilogue")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--chains", type=int, default=1, help="concurrent chains the local batch is split into (DP)")
     args = ap.parse_args()

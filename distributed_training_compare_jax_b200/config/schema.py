@@ -73,6 +73,7 @@ class TrainConfig:
     sync_every_step: bool = True      # blocking loss fetch each step like the reference (train/train.py:82-83)
     backend: str = "auto"             # "auto" (native kernels on CUDA, torch oracle on CPU) | "native" | "torch"
     cuda_graph: bool = True           # replay the captured step graph on the native path
+    tp_fused: bool = False            # TP: GEMM epilogue multimem.red all-reduce instead of GEMM + NCCL all-reduce (measured slower)
     dp_overlap: bool = True           # fused DP: reduce-scatter each layer's gradient bucket during the backward pass
     micro_chains: int = 1             # DP/TP: split the local batch into this many concurrently executed chains
     fused_comm: bool = True           # fused compute+collective kernels over symmetric memory (vs plain NCCL)

@@ -60,4 +60,4 @@ class CausalSelfAttention:
         Fn.flash_attn_bwd(ws.qkv[l], ws.attn[l], ws.dattn, ws.lse2[l], ws.B, self.local.heads_local, ws.T,
                           self.config.head_dim, dqkv=ws.dqkv, dq_accum=ws.dq_accum, delta=ws.delta)
         eng.side_work(qkv_param_grads)
-        eng.tp_reduced_gemm(ws.dqkv, c["wqkv"][l], out=ws.dln)
+        ws.dln_cur = eng.tp_reduced_gemm(ws.dqkv, c["wqkv"][l], out=ws.dln)

@@ -116,8 +116,8 @@ class GPTModel:
             Fn.gemm(ws.lnf, ws.logits, a_mn=True, b_mn=True, epi="atomic_f32", out=g["wlm"], splits=1)
 
         eng.side_work(head_param_grads)
-        eng.tp_reduced_gemm(ws.logits, c["wlm"], out=ws.dln)
-        Fn.layernorm_bwd(ws.dln, ws.h[L], ws.meanf, ws.rstdf, c["lnf_g"], g["lnf_g"], g["lnf_b"], dres=None, out=ws.dh_a)
+        ws.dln_cur = eng.tp_reduced_gemm(ws.logits, c["wlm"], out=ws.dln)
+        Fn.layernorm_bwd(ws.dln_cur, ws.h[L], ws.meanf, ws.rstdf, c["lnf_g"], g["lnf_g"], g["lnf_b"], dres=None, out=ws.dh_a)
         if eng.has_grad_hooks:
             eng.side_join()
             eng.on_head_grads_ready()

@@ -50,4 +50,4 @@ class MLP:
         eng.side_work(fc2_param_grads)
         Fn.gemm(dh, c["w2"][l], epi="dgelu", aux=ws.f1[l], out=ws.df1)
         eng.side_work(fc1_param_grads)
-        eng.tp_reduced_gemm(ws.df1, c["w1"][l], out=ws.dln)
+        ws.dln_cur = eng.tp_reduced_gemm(ws.df1, c["w1"][l], out=ws.dln)

@@ -46,8 +46,8 @@ class TransformerBlock:
         """dh_out = dL/dh[l+1] (input); dh_mid is scratch; dh_in receives dL/dh[l]."""
         c, g = eng.c, eng.g
         self.mlp.native_backward(eng, ws, l, dh_out)
-        Fn.layernorm_bwd(ws.dln, ws.hmid[l], ws.mean2[l], ws.rstd2[l], c["ln2_g"][l], g["ln2_g"][l], g["ln2_b"][l],
+        Fn.layernorm_bwd(ws.dln_cur, ws.hmid[l], ws.mean2[l], ws.rstd2[l], c["ln2_g"][l], g["ln2_g"][l], g["ln2_b"][l],
                          dres=dh_out, out=dh_mid)
         self.attn.native_backward(eng, ws, l, dh_mid)
-        Fn.layernorm_bwd(ws.dln, ws.h[l], ws.mean1[l], ws.rstd1[l], c["ln1_g"][l], g["ln1_g"][l], g["ln1_b"][l],
+        Fn.layernorm_bwd(ws.dln_cur, ws.h[l], ws.mean1[l], ws.rstd1[l], c["ln1_g"][l], g["ln1_g"][l], g["ln1_b"][l],
                          dres=dh_mid, out=dh_in)

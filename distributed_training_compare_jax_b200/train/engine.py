@@ -153,13 +153,14 @@ class NativeStageEngine(StageEngineBase):
         # share an SM — one from the backward chain, one from the parameter-gradient stream
         return Fn.gemm_impl(self.bwd_gemm_impl)
 
-    def tp_reduced_gemm(self, a, w, out) -> None:
-        """out = sum over TP ranks of a · wᵀ (dX of a column-parallel Linear, collectives X5 / X8)."""
+    def tp_reduced_gemm(self, a, w, out) -> torch.Tensor:
+        """sum over TP ranks of a · wᵀ (dX of a column-parallel Linear, collectives X5 / X8).  Returns the tensor that
+        holds the result: ``out``, or — on the fused path — a dedicated symmetric buffer."""
         if self.tp_hooks is not None:
-            self.tp_hooks.reduced_gemm(self, a, w, out)
-            return
+            return self.tp_hooks.reduced_gemm(self, a, w, out)
         Fn.gemm(a, w, out=out)
         self.mesh.tp.all_reduce(out)
+        return out
 
     def set_batch(self, mb: int, x: torch.Tensor | None, y: torch.Tensor | None) -> None:
         """x, y: int32 [micro_batch, T] (device or pinned host); copied into the static workspace buffers."""
