@@ -22,6 +22,44 @@ from ..ops import native
 from .symm import FlagBarrier, SymmBuffer
 
 
+def plan_buckets(offsets: dict, n_layers: int, dp_rank: int, dp_size: int) -> tuple[list[dict], dict]:
+    """Gradient buckets in the order the backward pass completes them — head, layer L-1 … 0, embeddings — and, for every
+    tensor (slice) of a bucket, the sub-range rank ``dp_rank`` owns (a 1/dp_size share rounded up to 8 elements).
+
+    ``offsets``: ``ParamStore.offsets`` (name -> (flat offset, shape)).  Returns ``(buckets, index)`` where each bucket is
+    ``{"full": [(off, n)…], "owned": [(off, n)…]}`` and ``index`` maps "head" / "embed" / layer number to a bucket id."""
+    def numel(shape):
+        k = 1
+        for d in shape:
+            k *= d
+        return k
+
+    globals_ = ("wte", "wpe", "wlm", "blm", "lnf_g", "lnf_b")
+    head = [(offsets[k][0], numel(offsets[k][1])) for k in ("lnf_g", "lnf_b", "wlm", "blm") if k in offsets]
+    embed = [(offsets[k][0], numel(offsets[k][1])) for k in ("wte", "wpe") if k in offsets]
+    layers = []
+    for l in range(n_layers):
+        sl = []
+        for name, (off, shape) in offsets.items():
+            if name not in globals_:
+                per = numel(shape[1:])
+                sl.append((off + l * per, per))
+        layers.append(sl)
+    full = ([head] if head else []) + [layers[l] for l in reversed(range(n_layers))] + ([embed] if embed else [])
+    index = {"head": 0 if head else None, "embed": len(full) - 1 if embed else None}
+    for i, l in enumerate(reversed(range(n_layers))):
+        index[l] = (1 if head else 0) + i
+    buckets = []
+    for ranges in full:
+        owned = []
+        for off, cnt in ranges:
+            chunk = -(-(-(-cnt // dp_size)) // 8) * 8          # ceil(cnt / n) rounded up to 8 elements
+            lo, hi = min(dp_rank * chunk, cnt), min((dp_rank + 1) * chunk, cnt)
+            owned.append((off + lo, hi - lo))
+        buckets.append({"full": ranges, "owned": owned})
+    return buckets, index
+
+
 class BucketedAllReduce:
     """Per-layer gradient buckets reduced on a communication stream while the backward pass continues."""
 
@@ -124,38 +162,14 @@ class FusedShardedStep:
     def _build_buckets(self) -> None:
         import ctypes as C
         st, dp, L = self.store, self.mesh.dp, self.engine.local.L
-
-        def numel(shape):
-            k = 1
-            for d in shape:
-                k *= d
-            return k
-
-        head = [(st.offsets[k][0], numel(st.offsets[k][1])) for k in ("lnf_g", "lnf_b", "wlm", "blm") if k in st.offsets]
-        embed = [(st.offsets[k][0], numel(st.offsets[k][1])) for k in ("wte", "wpe") if k in st.offsets]
-        layers = []
-        for l in range(L):
-            sl = []
-            for name, (off, shape) in st.offsets.items():
-                if name not in ("wte", "wpe", "wlm", "blm", "lnf_g", "lnf_b"):
-                    per = numel(shape[1:])
-                    sl.append((off + l * per, per))
-            layers.append(sl)
-        full = ([head] if head else []) + [layers[l] for l in reversed(range(L))] + ([embed] if embed else [])
-        self.bucket_of_head = 0 if head else None
-        self.bucket_of_layer = {l: (1 if head else 0) + i for i, l in enumerate(reversed(range(L)))}
-        self.bucket_of_embed = len(full) - 1 if embed else None
+        plan, index = plan_buckets(st.offsets, L, dp.rank, dp.size)
+        self.bucket_of_head, self.bucket_of_embed = index["head"], index["embed"]
+        self.bucket_of_layer = {l: index[l] for l in range(L)}
         self.buckets, owned_all, p_off = [], [], 0
-        for ranges in full:
-            offs, lens = [], []
-            for off, cnt in ranges:
-                chunk = -(-(-(-cnt // dp.size)) // 8) * 8          # ceil(cnt / n) rounded up to 8 elements
-                lo = min(dp.rank * chunk, cnt)
-                hi = min((dp.rank + 1) * chunk, cnt)
-                offs.append(off + lo)
-                lens.append(hi - lo)
-                if hi > lo:
-                    owned_all.append((off + lo, hi - lo))
+        for b in plan:
+            offs = [o for o, _ in b["owned"]]
+            lens = [k for _, k in b["owned"]]
+            owned_all += [(o, k) for o, k in b["owned"] if k > 0]
             k = len(offs)
             blocks = max(1, min(self.RS_BLOCKS, -(-sum(lens) // (4 * 256 * 4))))
             self.buckets.append({"offs": (C.c_longlong * k)(*offs), "lens": (C.c_longlong * k)(*lens), "count": k,
