@@ -72,6 +72,13 @@ def test_pp2_reference_semantics_runs_and_differs_only_slightly(single, tmp_path
     assert np.all(np.isfinite(loss)) and abs(loss[0] - single[0]) < 0.5
 
 
+def test_pp3_uneven_layers_1f1b_matches_single_device(single, tmp_path):
+    # 4 layers on 3 stages -> [2, 1, 1] (no layer is dropped, unlike the reference's floor division), 4 microbatches, 1F1B:
+    # warm-up / steady state / cool-down phases with different peers on either side of the middle stage
+    loss, _ = _run(tmp_path, "pp3", "pp", 3, pp_microbatches=4, pp_init="shared", pp_clip="global", pp_schedule="1f1b")
+    np.testing.assert_allclose(loss, single, rtol=2e-5)
+
+
 def test_dp2_x_tp2_hybrid_mesh_matches_single_device(single, tmp_path):
     loss, _ = _run(tmp_path, "dptp", "dp_tp", 4, dp_size=2, tp_size=2)
     np.testing.assert_allclose(loss, single, rtol=2e-5)
