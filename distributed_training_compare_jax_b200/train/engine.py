@@ -53,7 +53,6 @@ class Workspace:
         self.dh_a, self.dh_b, self.dh_mid, self.dln = e(M, D), e(M, D), e(M, D), e(M, D)
         self.dqkv, self.dattn, self.df1 = e(M, 3 * Dl), e(M, Dl), e(M, Fl)
         self.dq_accum, self.delta = e(M, Dl, dtype=F32), e(B, Hl, T, dtype=F32)
-        self.dh0 = None  # buffer holding dL/dh[0] after backward (set by the engine)
         if local.has_head:
             self.lnf, self.meanf, self.rstdf = e(M, D), e(M, dtype=F32), e(M, dtype=F32)
             self.logits = e(M, Vl)

@@ -5,13 +5,15 @@ Reads ``outputs/{dp,tp,pp}/log.csv`` (plus ``outputs/dp_tp`` when present), over
 Differences: the bar shows the true average step time (last cumulative ``elapsed_time`` /
 steps) — the reference sums a cumulative column, which is only proportional to it — and because matplotlib is
 not installed on the B200 image the tool always writes ``outputs/summary.csv`` / prints a table and draws the
-PNGs only when matplotlib imports.
+two PNGs with matplotlib when it imports, otherwise with the dependency-free writer in ``utils/png.py``.
 """
 from __future__ import annotations
 
 import csv
 import os
 import sys
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 
 
 def read_log(path: str) -> dict:
@@ -57,7 +59,14 @@ def main(path_root: str = "outputs/") -> list[dict]:
         matplotlib.use("Agg")
         import matplotlib.pyplot as plt
     except Exception:
-        print("matplotlib not available: wrote outputs/summary.csv only")
+        # no matplotlib on this machine: draw the same two figures with the built-in PNG writer
+        from distributed_training_compare_jax_b200.utils.png import bar_chart, line_chart
+        rgb = {"dp": (220, 30, 30), "tp": (30, 160, 30), "pp": (30, 30, 220), "dp_tp": (240, 150, 20)}
+        line_chart(os.path.join(path_root, "loss.png"), {k: (v["step"], v["loss"]) for k, v in logs.items()}, rgb, "step",
+                   "loss")
+        bar_chart(os.path.join(path_root, "average_elapsed_time.png"), {r["strategy"]: r["avg_step_time_s"] for r in rows},
+                  rgb, "method", "average step time [sec]")
+        print("matplotlib not available: figures drawn with the built-in PNG writer")
         return rows
     colors = {"dp": "red", "tp": "green", "pp": "blue", "dp_tp": "orange"}
     for name, log in logs.items():

@@ -93,3 +93,6 @@ def test_metrics_json_and_plot_summary(single, tmp_path):
     rows = plot.main(str(tmp_path) + "/")
     assert rows and rows[0]["strategy"] == "dp" and rows[0]["steps"] == 8
     assert os.path.exists(tmp_path / "summary.csv")
+    for png in ("loss.png", "average_elapsed_time.png"):          # the reference's two figures (plot.py:25,38)
+        data = open(tmp_path / png, "rb").read()
+        assert data[:8] == b"\x89PNG\r\n\x1a\n" and len(data) > 500
