@@ -74,7 +74,8 @@ def run(args) -> dict | None:
                      output_dir="outputs/bench", pp_microbatches=args.pp_microbatches, warmup_steps=args.warmup,
                      global_batch_is_per_device=True, sync_every_step=True, backend=args.backend,
                      pp_schedule=args.pp_schedule, fused_comm=not args.no_fused_comm, cuda_graph=not args.no_graph,
-                     dp_overlap=not args.no_dp_overlap, tp_fused=args.tp_fused)
+                     dp_overlap=not args.no_dp_overlap, tp_fused=args.tp_fused,
+                     tp_seq_parallel=args.tp_seq_parallel)
     mc = load_model_config(os.path.join(ROOT, args.model_config), vocab_size=VOCAB_SIZE, parallel=strategy)
     oc = load_optim_config(os.path.join(ROOT, "configs/optim_config.yaml"))
     dp, tp, pp = mesh_shape(tc, world)
@@ -150,7 +151,10 @@ def run(args) -> dict | None:
     comm_path = {"dp": ("symmetric-memory reduce-scatter + sharded AdamW + all-gather ("
                         + ("multimem/NVLS" if getattr(opt, "uses_multicast", False) else "peer loads/stores") + ")")
                  if type(opt).__name__ == "FusedShardedStep" else ("NCCL bucketed all-reduce" if dp > 1 else "none"),
-                 "tp": ("GEMM epilogue multimem.red all-reduce" if getattr(state.engine, "tp_hooks", None) is not None
+                 "tp": ("sequence-parallel: GEMM-epilogue reduce-scatter (P2P stores) + LayerNorm all-gather ("
+                        + ("multimem.st" if state.engine.sp.use_mc else "peer stores") + ")"
+                        if hasattr(state.engine, "sp") else
+                        "GEMM epilogue multimem.red all-reduce" if getattr(state.engine, "tp_hooks", None) is not None
                         else ("GEMM + NCCL all-reduce" if tp > 1 else "none")),
                  "pp": "NCCL send/recv, one communicator per direction" if pp > 1 else "none"}
     tps = tokens_per_step * args.steps / (ms_dev / 1e3)
@@ -194,6 +198,8 @@ def main() -> int:
     ap.add_argument("--no-fused-comm", action="store_true")
     ap.add_argument("--no-dp-overlap", action="store_true")
     ap.add_argument("--tp-fused", action="store_true", help="TP: fused GEMM + multimem.red all-reduce epilogue")
+    ap.add_argument("--tp-seq-parallel", action="store_true",
+                    help="TP: row-sharded residual stream, GEMM-epilogue reduce-scatter + LayerNorm all-gather")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--chains", type=int, default=1, help="concurrent chains the local batch is split into (DP)")
     args = ap.parse_args()

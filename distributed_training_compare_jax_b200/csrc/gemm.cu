@@ -40,6 +40,11 @@ enum GemmEpiMode : int {
   // bias + residual) into ALL ranks' copies of a zeroed symmetric bf16 buffer with multimem.red (`out` is the
   // multicast address).  Persistent kernel only.
   EPI_MC_RED_BF16 = 6,
+  // Fused GEMM -> reduce-scatter for sequence-parallel TP: output rows [o*sp_rows, (o+1)*sp_rows) belong to rank o; the
+  // bf16 tile is stored over NVLink into THIS rank's partial-sum slot of rank o's symmetric buffer
+  // (peer_out[o] + (sp_rank*sp_rows + row - o*sp_rows)*ldo), tile by tile while later tiles are still in the tensor
+  // cores.  The owner sums the n slots in fp32 inside its next kernel (csrc/seqpar.cu).  Persistent kernel only.
+  EPI_SCATTER_BF16 = 7,
 };
 
 struct GemmEpi {
@@ -55,6 +60,30 @@ struct GemmEpi {
   int coop_store;             // 1: epilogue warps copy the staged tile to global themselves (no TMA store)
   unsigned long long* trace;  // debug: per-k-block clock64 timestamps of CTA 0 (null in production)
 };
+
+// Parameter block of the SCATTER instantiations only (the other kernels keep the plain GemmEpi parameter).
+struct GemmEpiScatter : GemmEpi {
+  bf16* peer_out[8];     // base of every rank's partial-sum buffer ([n_ranks * sp_rows, ldo] bf16)
+  int sp_rank, sp_rows;  // this rank; rows owned per rank
+};
+template <bool SCATTER>
+struct EpiArgT { using type = GemmEpi; };
+template <>
+struct EpiArgT<true> { using type = GemmEpiScatter; };
+
+// destination of the output tile whose first row is m0: (base pointer, row shift)
+DTC_DEVICE void scatter_dest(const GemmEpi& epi, int, bf16*& base, long long& rshift) {
+  base = reinterpret_cast<bf16*>(epi.out);
+  rshift = 0;
+}
+DTC_DEVICE void scatter_dest(const GemmEpiScatter& epi, int m0, bf16*& base, long long& rshift) {
+  const int owner = m0 / epi.sp_rows;  // the rows of this tile belong to rank `owner`: my slot of ITS partial-sum buffer
+  base = epi.peer_out[0];
+#pragma unroll
+  for (int i = 1; i < 8; ++i)
+    if (i == owner) base = epi.peer_out[i];
+  rshift = (long long)(epi.sp_rank - owner) * epi.sp_rows;
+}
 
 template <int BN>
 struct GemmSmem {
@@ -327,18 +356,19 @@ DTC_DEVICE void epi_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); 
 // or issuing warps, while two co-resident CTAs are each served at that rate.  The DUAL variant therefore keeps the
 // CTA under 113 KB of shared memory (2-3 stages, ONE staging tile: the residual / pre-activation tile is TMA-loaded
 // into the output staging tile by the epilogue leader and overwritten in place) and 256 TMEM columns.
-template <bool A_MN, bool B_MN, int BN, bool DUAL>
+template <bool A_MN, bool B_MN, int BN, bool DUAL, bool SCATTER = false>
 __global__ void __launch_bounds__(PG_THREADS, DUAL ? 2 : 1)
 gemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                        const __grid_constant__ CUtensorMap tma_out, const __grid_constant__ CUtensorMap tma_out2,
                        const __grid_constant__ CUtensorMap tma_aux, int M, int N, int K, int m_blocks, int n_blocks,
-                       int splits, int kb_per_split, int num_stages, GemmEpi epi) {
+                       int splits, int kb_per_split, int num_stages, const typename EpiArgT<SCATTER>::type epi) {
   using S = PgSmem<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* stage_out = smem + num_stages * S::STAGE_BYTES;  // out tile (bf16)
   uint8_t* stage_aux = DUAL ? stage_out : stage_out + S::TILE_BYTES;  // aux tile (input) or out2 tile (GELU output)
-  uint64_t* bars = reinterpret_cast<uint64_t*>(stage_out + (DUAL ? (epi.mode <= EPI_DGELU ? 1 : 0) : 2) * S::TILE_BYTES);
+  uint64_t* bars =
+      reinterpret_cast<uint64_t*>(stage_out + (DUAL ? ((epi.mode <= EPI_DGELU || SCATTER) ? 1 : 0) : 2) * S::TILE_BYTES);
   uint64_t* full_bar = bars;                       // [PG_STAGE_MAX]
   uint64_t* empty_bar = bars + PG_STAGE_MAX;       // [PG_STAGE_MAX]
   uint64_t* tmem_full = bars + 2 * PG_STAGE_MAX;   // [2]
@@ -354,13 +384,14 @@ gemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
   const int tiles_mn = m_blocks * n_blocks;
   const int total_tiles = tiles_mn * splits;
   const int mode = epi.mode;
-  const bool bf16_out = mode <= EPI_DGELU;  // outputs that leave through the smem staging tile + TMA store
+  const bool bf16_out = mode <= EPI_DGELU || SCATTER;  // outputs that leave through the smem staging tile
   const bool use_aux = (mode == EPI_BIAS_RESIDUAL || mode == EPI_DGELU || (mode == EPI_MC_RED_BF16 && epi.aux != nullptr));
+  const bool coop_store = SCATTER || epi.coop_store;   // staged tile written out by the epilogue warps (no TMA store)
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tma_a);
     tma_prefetch_desc(&tma_b);
-    if (bf16_out) tma_prefetch_desc(&tma_out);
+    if (bf16_out && !SCATTER) tma_prefetch_desc(&tma_out);
     for (int s = 0; s < num_stages; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
@@ -503,7 +534,7 @@ gemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
       if (has_bias) epi_bar_sync();
       if (epi.trace && blockIdx.x == 0 && threadIdx.x == 64 && it < 32) epi.trace[1024 + it * 4 + 1] = clock64();
       if (use_aux) mbar_wait(aux_full, it & 1);
-      if (bf16_out && !(DUAL && use_aux) && !epi.coop_store) {
+      if (bf16_out && !(DUAL && use_aux) && !coop_store) {
         // the previous tile's TMA stores must have finished READING the staging tiles before they are rewritten
         // (DUAL with an aux tile: the leader already waited for that before it fetched this tile's aux tile)
         if (store_leader) tma_store_wait_read();
@@ -596,11 +627,14 @@ gemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
         mbar_arrive(&tmem_empty[buf]);
         if (use_aux && !DUAL) mbar_arrive(aux_empty);
       }
-      if (bf16_out && epi.coop_store) {
+      if (bf16_out && coop_store) {
         // The TMA queue of a CTA is served in order at ~48 B/cycle and is already saturated by the operand loads: the
         // epilogue warps therefore write the staged tile out themselves (8 threads per 128-byte row: coalesced).
         epi_bar_sync();
         const int et = threadIdx.x - 64, ch = et & 7, r0 = et >> 3;
+        bf16* obase;
+        long long rshift;  // destination row = output row + rshift
+        scatter_dest(epi, m_blk * BM, obase, rshift);
 #pragma unroll
         for (int hf = 0; hf < BN / 64; ++hf) {
           const int ncol = n_blk * BN + hf * 64 + ch * 8;
@@ -611,7 +645,7 @@ gemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
               const long long grow = (long long)m_blk * BM + r;
               if (grow < M) {
                 const uint32_t so = (uint32_t)hf * S::HALF_BYTES + swizzle_offset<3>(r * 128 + ch * 16);
-                *reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(epi.out) + grow * epi.ldo + ncol) =
+                *reinterpret_cast<uint4*>(obase + (grow + rshift) * epi.ldo + ncol) =
                     *reinterpret_cast<const uint4*>(stage_out + so);
                 if (mode == EPI_BIAS_GELU)
                   *reinterpret_cast<uint4*>(epi.out2 + grow * epi.ldo2 + ncol) = *reinterpret_cast<const uint4*>(stage_aux + so);
@@ -676,9 +710,9 @@ static int num_sms() {
   return n;
 }
 
-template <bool A_MN, bool B_MN, int BN, bool DUAL>
+template <bool A_MN, bool B_MN, int BN, bool DUAL, bool SCATTER = false>
 static int launch_gemm_persistent(const void* A, long long lda, const void* B, long long ldb, int M, int N, int K,
-                                  int splits, int stages, const GemmEpi& epi, cudaStream_t stream) {
+                                  int splits, int stages, const typename EpiArgT<SCATTER>::type& epi, cudaStream_t stream) {
   using S = PgSmem<BN>;
   CUtensorMap ta, tb, tout, tout2, taux;
   int rc;
@@ -711,10 +745,10 @@ static int launch_gemm_persistent(const void* A, long long lda, const void* B, l
   if (stages < 2) stages = 2;
   if (stages > PG_STAGE_MAX) stages = PG_STAGE_MAX;
   const int smem_cap = DUAL ? 112 * 1024 : 227 * 1024;  // DUAL: two CTAs (+1 KB reserved each) per 228 KB SM
-  const bool staging = epi.mode <= EPI_DGELU;
+  const bool staging = epi.mode <= EPI_DGELU || SCATTER;
   while (stages > 2 && S::bytes(stages, DUAL, staging) > smem_cap) --stages;
   const int smem_bytes = S::bytes(stages, DUAL, staging);
-  auto kern = gemm_persistent_kernel<A_MN, B_MN, BN, DUAL>;
+  auto kern = gemm_persistent_kernel<A_MN, B_MN, BN, DUAL, SCATTER>;
   static bool configured = false;
   if (!configured) {
     DTC_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, DUAL ? 113 * 1024 : 227 * 1024));
@@ -1104,7 +1138,7 @@ extern "C" int dtc_gemm_bf16(const void* A, long long lda, int a_mn_major, const
   DTC_CHECK_ARG(lda % 8 == 0 && ldb % 8 == 0, "gemm: lda=%lld ldb=%lld must be multiples of 8 elements", lda, ldb);
   DTC_CHECK_ARG(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0 && ((uintptr_t)out & 15) == 0,
                 "gemm: operand pointers must be 16-byte aligned");
-  DTC_CHECK_ARG(epi_mode >= 0 && epi_mode <= 6, "gemm: bad epilogue mode %d", epi_mode);
+  DTC_CHECK_ARG(epi_mode >= 0 && epi_mode <= 6, "gemm: bad epilogue mode %d (the scatter epilogue has its own entry point)", epi_mode);
   DTC_CHECK_ARG(splits <= 1 || epi_mode == EPI_ATOMIC_F32, "gemm: split-K needs the fp32 reduce-add epilogue");
   DTC_CHECK_ARG(!(epi_mode == EPI_BIAS_RESIDUAL || epi_mode == EPI_DGELU) || aux != nullptr, "gemm: aux missing");
   DTC_CHECK_ARG(epi_mode != EPI_BIAS_GELU || out2 != nullptr, "gemm: out2 missing");
@@ -1191,4 +1225,50 @@ extern "C" int dtc_gemm_bf16(const void* A, long long lda, int a_mn_major, const
   if (a_mn_major && !b_mn_major) { DTC_GEMM_DISPATCH(true, false) }
   DTC_GEMM_DISPATCH(true, true)
 #undef DTC_GEMM_DISPATCH
+}
+
+// Fused GEMM -> reduce-scatter (sequence-parallel tensor parallelism; SURVEY.md §8 row R4, collectives X3/X4/X5/X8).
+// D[M,N] = A·Bᵀ as dtc_gemm_bf16 (A [M,K] row-major; B [N,K] row-major, or [K,N] when b_mn_major), but the output never
+// lands in one local matrix: rows [o*M/n, (o+1)*M/n) are stored into slot `rank` of rank o's partial-sum buffer
+//   peer_out[o][(rank*M/n + row - o*M/n) * ldo + col]                (bf16; P2P stores over NVLink, or local for o == rank)
+// `peer_out` is a HOST array of n_ranks device pointers (the symmetric buffer of every rank, each [M, ldo] bf16).
+// The caller separates this kernel from the owner's reduction with a cross-rank barrier (dtc_symm_barrier).
+extern "C" int dtc_gemm_bf16_scatter(const void* A, long long lda, const void* B, long long ldb, int b_mn_major, int M, int N,
+                                     int K, const unsigned long long* peer_out, int n_ranks, int rank, long long ldo,
+                                     int stages, int block_n, cudaStream_t stream) {
+  DTC_CHECK_ARG(M > 0 && N > 0 && K > 0, "gemm_scatter: empty problem M=%d N=%d K=%d", M, N, K);
+  DTC_CHECK_ARG(n_ranks >= 1 && n_ranks <= 8 && rank >= 0 && rank < n_ranks, "gemm_scatter: bad rank %d of %d", rank, n_ranks);
+  DTC_CHECK_ARG(M % (n_ranks * BM) == 0, "gemm_scatter: M=%d must be a multiple of n_ranks*128 (no tile may straddle owners)", M);
+  DTC_CHECK_ARG(N % 64 == 0 && lda % 8 == 0 && ldb % 8 == 0 && ldo % 8 == 0, "gemm_scatter: N %% 64, ld %% 8 required");
+  DTC_CHECK_ARG(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0, "gemm_scatter: operand pointers must be 16-byte aligned");
+  GemmEpiScatter epi;
+  epi.mode = EPI_SCATTER_BF16;
+  epi.alpha = 1.f;
+  epi.bias = nullptr;
+  epi.aux = nullptr;
+  epi.ld_aux = 0;
+  epi.out = nullptr;
+  epi.ldo = ldo;
+  epi.out2 = nullptr;
+  epi.ldo2 = 0;
+  epi.coop_store = 1;
+  epi.trace = nullptr;
+  for (int i = 0; i < 8; ++i) {
+    epi.peer_out[i] = i < n_ranks ? reinterpret_cast<bf16*>(peer_out[i]) : nullptr;
+    DTC_CHECK_ARG(i >= n_ranks || (peer_out[i] != 0 && (peer_out[i] & 15) == 0), "gemm_scatter: peer pointer %d null/unaligned", i);
+  }
+  epi.sp_rank = rank;
+  epi.sp_rows = M / n_ranks;
+  if (block_n == 0) {
+    const long long t128 = (long long)(M / 128) * ((N + 127) / 128);
+    block_n = (N <= 64 || t128 <= num_sms()) ? 64 : 128;
+  }
+  DTC_CHECK_ARG(block_n == 64 || block_n == 128, "gemm_scatter: block_n must be 64 or 128 (got %d)", block_n);
+  if (stages == 0) stages = PG_STAGE_MAX;
+  if (b_mn_major) {
+    if (block_n == 64) return launch_gemm_persistent<false, true, 64, true, true>(A, lda, B, ldb, M, N, K, 1, stages, epi, stream);
+    return launch_gemm_persistent<false, true, 128, true, true>(A, lda, B, ldb, M, N, K, 1, stages, epi, stream);
+  }
+  if (block_n == 64) return launch_gemm_persistent<false, false, 64, true, true>(A, lda, B, ldb, M, N, K, 1, stages, epi, stream);
+  return launch_gemm_persistent<false, false, 128, true, true>(A, lda, B, ldb, M, N, K, 1, stages, epi, stream);
 }

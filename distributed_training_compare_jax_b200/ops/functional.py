@@ -72,6 +72,38 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
     return out if mode != 1 else (out, out2)
 
 
+def gemm_scatter(a: torch.Tensor, b: torch.Tensor, peer_ptrs, n_ranks: int, rank: int, ldo: int, *, b_mn: bool = False,
+                 stages: int = 0, block_n: int = 0) -> None:
+    """GEMM -> reduce-scatter (sequence-parallel TP): D = A·Bᵀ whose row block of rank ``o`` is stored into slot ``rank``
+    of rank ``o``'s partial-sum buffer.  ``peer_ptrs``: ctypes array of the n_ranks buffer addresses (each [M, ldo] bf16)."""
+    _check_rowmajor(a, "a")
+    _check_rowmajor(b, "b")
+    M, K = a.shape
+    Kb, N = (b.shape[0], b.shape[1]) if b_mn else (b.shape[1], b.shape[0])
+    if K != Kb:
+        raise ValueError(f"gemm_scatter: reduction dims differ ({K} vs {Kb})")
+    native.call("dtc_gemm_bf16_scatter", a, a.stride(0), b, b.stride(0), int(b_mn), M, N, K, peer_ptrs, n_ranks, rank, ldo,
+                stages, block_n)
+
+
+def sp_ln_fwd(res, bias, part, n_part: int, gamma, beta, hsum, mean, rstd, mc_out: int, peer_ptrs, n_out: int,
+              out_row0: int, eps: float = 1e-6) -> None:
+    """Owned rows: hsum = res + bias + Σ part[p]; LayerNorm(hsum) pushed to rows [out_row0, out_row0+Ms) of every rank's
+    gathered buffer (``mc_out`` multicast address, or the ``peer_ptrs`` list when 0).  See ``dtc_sp_ln_fwd``."""
+    Ms, D = res.shape
+    native.call("dtc_sp_ln_fwd", res, bias, part, n_part, gamma, beta, hsum, mean, rstd, mc_out, peer_ptrs, n_out,
+                out_row0, Ms, D, float(eps))
+
+
+def sp_ln_bwd(part, n_part: int, x, mean, rstd, gamma, dres, dgamma, dbeta, mc_out: int, peer_ptrs, n_out: int,
+              out_row0: int) -> None:
+    """Owned rows: dx = LayerNorm'(Σ part[p]) + dres, pushed to every rank's gathered gradient buffer; dgamma / dbeta
+    accumulate over the owned rows.  See ``dtc_sp_ln_bwd``."""
+    Ms, D = x.shape
+    native.call("dtc_sp_ln_bwd", part, n_part, x, mean, rstd, gamma, dres, dgamma, dbeta, mc_out, peer_ptrs, n_out,
+                out_row0, Ms, D)
+
+
 def layernorm_fwd(x, gamma, beta, eps: float = 1e-6, out=None, mean=None, rstd=None):
     M, D = x.shape
     out = torch.empty_like(x) if out is None else out

@@ -42,6 +42,9 @@ _PROTOS: dict[str, list[Any]] = {
     "dtc_adamw": [P, P, P, P, P, L, P, P, F, F, F, F, F, F, I],
     "dtc_colsum": [P, L, I, I, P],
     "dtc_symm_barrier": [P, I, I, I],
+    "dtc_gemm_bf16_scatter": [P, L, P, L, I, I, I, I, P, I, I, L, I, I],
+    "dtc_sp_ln_fwd": [P, P, P, I, P, P, P, P, P, U64, P, I, L, I, I, F],
+    "dtc_sp_ln_bwd": [P, I, P, P, P, P, P, P, P, U64, P, I, L, I, I],
     "dtc_dp_reduce_scatter": [P, U64, P, I, I, L, L, P],
     "dtc_dp_norm_exchange": [P, I, P, P, I, I, I, F, P, P],
     "dtc_dp_adamw_allgather": [P, P, P, P, U64, P, I, L, L, L, P, P, F, F, F, F, F],

@@ -68,7 +68,9 @@ class BucketedAllReduce:
         self.store = engine.store
         self.stream = torch.cuda.Stream(device=engine.device)
         # with several concurrent chains a layer's gradient is final only when ALL chains have passed it: reduce at the end
-        self.overlap = engine.n_micro == 1
+        # (and an engine whose replicated-leaf gradients are only partial sums until the end of its backward pass —
+        # sequence-parallel TP — must finish that sum first)
+        self.overlap = engine.n_micro == 1 and not getattr(engine, "defer_grad_reduction", False)
         if self.overlap:
             engine.on_layer_grads_ready = self._layer_ready
             engine.on_head_grads_ready = self._head_ready

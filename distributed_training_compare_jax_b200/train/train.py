@@ -48,13 +48,25 @@ def build_state(train_config: TrainConfig, model_config: ModelConfig, opt_config
     store = ParamStore(local, mesh.device, with_compute_copy=(backend == "native"),
                        symm_group=mesh.dp.group if fused_dp else None)
     init_params(store, train_config.seed, pp_stage_keys=pp_stage_keys, stage_index=mesh.pp.rank)
-    engine = make_engine(backend, model_config, local, mesh, store, micro_batch, model_config.max_seq_len, n_micro,
-                         global_tokens, train_config.seed)
+    engine = None
+    if (backend == "native" and train_config.tp_seq_parallel and mesh.tp.size > 1 and mesh.pp.size == 1 and n_micro == 1
+            and train_config.fused_comm):
+        from ..parallel.tp_sp import SeqParallelEngine
+        try:   # the conditions checked inside are the same on every rank, so all ranks fall back together
+            engine = SeqParallelEngine(model_config, local, mesh, store, micro_batch, model_config.max_seq_len, n_micro,
+                                       global_tokens, train_config.seed)
+        except (ValueError, RuntimeError) as e:
+            if mesh.is_main:
+                print(f"[dtc] sequence-parallel TP unavailable ({e}); using the replicated-activation TP path", flush=True)
+    if engine is None:
+        engine = make_engine(backend, model_config, local, mesh, store, micro_batch, model_config.max_seq_len, n_micro,
+                             global_tokens, train_config.seed)
     reducer = None
     if native_dp and not fused_dp:
         from ..parallel.dp import make_grad_reducer
         reducer = make_grad_reducer(engine, mesh)   # NCCL: per-layer buckets overlapped with the backward pass
-    if backend == "native" and mesh.tp.size > 1 and train_config.fused_comm and train_config.tp_fused:
+    if (backend == "native" and mesh.tp.size > 1 and train_config.fused_comm and train_config.tp_fused
+            and not hasattr(engine, "sp")):
         from ..parallel.tp import attach_fused_tp
         attach_fused_tp(engine, mesh)
     if fused_dp:

@@ -122,6 +122,24 @@ int dtc_dp_adamw_allgather_ranges(float* p, float* m, float* v, float* g, unsign
                                   const long long* prefix, int n_ranges, int blocks, const float* scalars,
                                   const int* step_ptr, float lr, float b1, float b2, float eps, float wd,
                                   cudaStream_t stream);
+
+/* ---- sequence-parallel tensor parallelism (rows R3 / R4 of SURVEY.md section 8; the TP all-reduces X3 / X4 / X5 / X8 the
+ *      reference gets from GSPMD, model/CausalSelfAttention.py:49-50, model/MLP.py:23-24, are split into a reduce-scatter
+ *      that is the GEMM epilogue and an all-gather that is the LayerNorm kernel's store) ----
+ * dtc_gemm_bf16_scatter: D[M,N] = A[M,K] · Bᵀ; the row block owned by rank o (M/n_ranks rows each) is stored into slot
+ *   `rank` of peer_out[o], a [M, ldo] bf16 buffer viewed as [n_ranks, M/n_ranks, ldo] (P2P stores from the epilogue).
+ * dtc_sp_ln_fwd: owned rows x = res + bias + sum_p part[p]  -> hsum (local); LayerNorm(x) -> rows
+ *   [out_row0, out_row0+Ms) of the destination on EVERY rank (mc_out multicast address, else the n_out peer_out bases).
+ * dtc_sp_ln_bwd: dy = sum_p part[p]; dx = LayerNorm'(dy) + dres -> pushed like the forward; dgamma/dbeta += owned rows. */
+int dtc_gemm_bf16_scatter(const void* A, long long lda, const void* B, long long ldb, int b_mn_major, int M, int N, int K,
+                          const unsigned long long* peer_out, int n_ranks, int rank, long long ldo, int stages,
+                          int block_n, cudaStream_t stream);
+int dtc_sp_ln_fwd(const void* res, const void* bias, const void* part, int n_part, const void* gamma, const void* beta,
+                  void* hsum, float* mean, float* rstd, unsigned long long mc_out, const unsigned long long* peer_out,
+                  int n_out, long long out_row0, int Ms, int D, float eps, cudaStream_t stream);
+int dtc_sp_ln_bwd(const void* part, int n_part, const void* x, const float* mean, const float* rstd, const void* gamma,
+                  const void* dres, float* dgamma, float* dbeta, unsigned long long mc_out,
+                  const unsigned long long* peer_out, int n_out, long long out_row0, int Ms, int D, cudaStream_t stream);
 int dtc_gemm_set_dual(int bits);   /* tuning: bit0 two-CTAs-per-SM GEMM, bit1 64-wide tiles for small grids, bit2 coop stores */
 
 #ifdef __cplusplus

@@ -68,3 +68,16 @@ def test_pp2_native(single, tmp_path, schedule):
 def test_dp2_tp2_native(single, tmp_path):
     loss = _run(tmp_path, "dptp", "dp_tp", 4, dp_size=2, tp_size=2)
     np.testing.assert_allclose(loss, single, rtol=5e-3, atol=5e-3)
+
+
+@pytest.mark.skipif(NGPU < 2, reason="needs >= 2 GPUs")
+def test_tp2_sequence_parallel_native(single, tmp_path):
+    """Row-sharded residual stream: GEMM-epilogue reduce-scatter + LayerNorm all-gather (parallel/tp_sp.py)."""
+    loss = _run(tmp_path, "tp2_sp", "tp", 2, tp_seq_parallel=True)
+    np.testing.assert_allclose(loss, single, rtol=5e-3, atol=5e-3)
+
+
+@pytest.mark.skipif(NGPU < 4, reason="needs >= 4 GPUs")
+def test_dp2_tp2_sequence_parallel_native(single, tmp_path):
+    loss = _run(tmp_path, "dptp_sp", "dp_tp", 4, dp_size=2, tp_size=2, tp_seq_parallel=True)
+    np.testing.assert_allclose(loss, single, rtol=5e-3, atol=5e-3)
