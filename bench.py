@@ -75,7 +75,7 @@ def run(args) -> dict | None:
                      global_batch_is_per_device=True, sync_every_step=True, backend=args.backend,
                      pp_schedule=args.pp_schedule, fused_comm=not args.no_fused_comm, cuda_graph=not args.no_graph,
                      dp_overlap=not args.no_dp_overlap, tp_fused=args.tp_fused,
-                     tp_seq_parallel=args.tp_seq_parallel)
+                     tp_seq_parallel=not args.no_tp_seq_parallel)
     mc = load_model_config(os.path.join(ROOT, args.model_config), vocab_size=VOCAB_SIZE, parallel=strategy)
     oc = load_optim_config(os.path.join(ROOT, "configs/optim_config.yaml"))
     dp, tp, pp = mesh_shape(tc, world)
@@ -198,8 +198,9 @@ def main() -> int:
     ap.add_argument("--no-fused-comm", action="store_true")
     ap.add_argument("--no-dp-overlap", action="store_true")
     ap.add_argument("--tp-fused", action="store_true", help="TP: fused GEMM + multimem.red all-reduce epilogue")
-    ap.add_argument("--tp-seq-parallel", action="store_true",
-                    help="TP: row-sharded residual stream, GEMM-epilogue reduce-scatter + LayerNorm all-gather")
+    ap.add_argument("--tp-seq-parallel", action="store_true", help="(default) TP: row-sharded residual stream, "
+                    "GEMM-epilogue reduce-scatter + LayerNorm all-gather")
+    ap.add_argument("--no-tp-seq-parallel", action="store_true", help="TP: replicated activations, GEMM + NCCL all-reduce")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--chains", type=int, default=1, help="concurrent chains the local batch is split into (DP)")
     args = ap.parse_args()
