@@ -18,6 +18,7 @@
 #include <stdarg.h>
 #include <stdio.h>
 #include <stdlib.h>
+#include <string.h>
 
 #include "common.cuh"
 #include "tma_host.h"
@@ -766,6 +767,191 @@ static int launch_gemm_persistent(const void* A, long long lda, const void* B, l
 
 
 // =========================================================================================================
+// Grouped weight-gradient GEMM: up to GG_MAX problems dW_p[M_p, N_p] += X_pᵀ · dY_p that share the reduction length K
+// (the tokens of the microbatch) run as ONE persistent launch — the four weight gradients of a transformer layer
+// (q/k/v, out_proj, fc1, fc2).  Against four split-K launches: one prologue / tail instead of four, no split-K (every
+// tile runs the whole K = B·T mainloop, so the fp32 reduce-add traffic drops by the split factor) and 192 tiles in one
+// wave-packed grid instead of 4 × (16 … 64).  Same pipeline as gemm_persistent_kernel<true, true, BN, DUAL> (both
+// operands MN-major: X is [K, M_p], dY is [K, N_p] row-major), register-path fp32 reduce-add epilogue, 2 CTAs per SM.
+// The tensor maps travel in the parameter block (__grid_constant__), indexed by the problem a tile belongs to.
+// =========================================================================================================
+constexpr int GG_MAX = 4;
+
+struct GemmGroup {
+  CUtensorMap a[GG_MAX];
+  CUtensorMap b[GG_MAX];
+  float* out[GG_MAX];
+  long long ldo[GG_MAX];
+  int M[GG_MAX];
+  int N[GG_MAX];
+  int m_blocks[GG_MAX];
+  int tile_start[GG_MAX + 1];  // prefix sums of m_blocks * n_blocks
+  int count;
+};
+
+DTC_DEVICE void group_decode(const GemmGroup& g, int t, int& p, int& m_blk, int& n_blk) {
+  p = 0;
+#pragma unroll
+  for (int i = 1; i < GG_MAX; ++i)
+    if (i < g.count && t >= g.tile_start[i]) p = i;
+  const int local = t - g.tile_start[p];
+  m_blk = local % g.m_blocks[p];
+  n_blk = local / g.m_blocks[p];
+}
+
+template <int BN>
+__global__ void __launch_bounds__(PG_THREADS, 2)
+gemm_grouped_wgrad_kernel(const __grid_constant__ GemmGroup grp, int K, int splits, int kb_per_split, int num_stages,
+                          float alpha) {
+  using S = PgSmem<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + num_stages * S::STAGE_BYTES);
+  uint64_t* full_bar = bars;                       // [PG_STAGE_MAX]
+  uint64_t* empty_bar = bars + PG_STAGE_MAX;       // [PG_STAGE_MAX]
+  uint64_t* tmem_full = bars + 2 * PG_STAGE_MAX;   // [2]
+  uint64_t* tmem_empty = tmem_full + 2;            // [2]
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int total_kb = (K + BK - 1) / BK;
+  const int tiles_mn = grp.tile_start[grp.count];
+  const int total_tiles = tiles_mn * splits;
+
+  if (warp == 0 && lane == 0) {
+    for (int p = 0; p < grp.count; ++p) {
+      tma_prefetch_desc(&grp.a[p]);
+      tma_prefetch_desc(&grp.b[p]);
+    }
+    for (int s = 0; s < num_stages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&tmem_full[b], 1);
+      mbar_init(&tmem_empty[b], 8);  // one arrival per epilogue warp
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_ptr_smem, 2 * BN);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+  pdl_launch_dependents();
+  pdl_wait();
+
+  if (warp == 0) {
+    // ------------------------------ TMA producer ------------------------------
+    if (elect_one()) {
+      uint32_t kit = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int split = tile / tiles_mn;
+        int p, m_blk, n_blk;
+        group_decode(grp, tile % tiles_mn, p, m_blk, n_blk);
+        const CUtensorMap* ta = &grp.a[p];
+        const CUtensorMap* tb = &grp.b[p];
+        const int kb_begin = split * kb_per_split;
+        const int nkb = min(total_kb, kb_begin + kb_per_split) - kb_begin;
+        for (int i = 0; i < nkb; ++i, ++kit) {
+          const int s = kit % num_stages;
+          const uint32_t ph = (kit / num_stages) & 1;
+          mbar_wait(&empty_bar[s], ph ^ 1);
+          uint8_t* sa = smem + s * S::STAGE_BYTES;
+          uint8_t* sb = sa + S::A_BYTES;
+          mbar_expect_tx(&full_bar[s], S::STAGE_BYTES);
+          const int k0 = (kb_begin + i) * BK;
+#pragma unroll
+          for (int j = 0; j < BM / 64; ++j) tma_load_2d(sa + j * (BK * 128), ta, &full_bar[s], m_blk * BM + j * 64, k0);
+#pragma unroll
+          for (int j = 0; j < BN / 64; ++j) tma_load_2d(sb + j * (BK * 128), tb, &full_bar[s], n_blk * BN + j * 64, k0);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------ MMA issuer ------------------------------
+    constexpr uint32_t idesc = make_idesc_bf16(BM, BN, 1, 1);
+    constexpr uint32_t LBO = BK * 128, STEP = 2048;  // MN-major operands (see gemm_persistent_kernel)
+    uint32_t kit = 0;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+      const int split = tile / tiles_mn;
+      const int kb_begin = split * kb_per_split;
+      const int nkb = min(total_kb, kb_begin + kb_per_split) - kb_begin;
+      const int buf = it & 1;
+      mbar_wait(&tmem_empty[buf], ((it >> 1) & 1) ^ 1);
+      tc_fence_after();
+      const uint32_t tmem_d = tmem_base + buf * BN;
+      for (int i = 0; i < nkb; ++i, ++kit) {
+        const int s = kit % num_stages;
+        const uint32_t ph = (kit / num_stages) & 1;
+        mbar_wait(&full_bar[s], ph);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t sa = smem_u32(smem + s * S::STAGE_BYTES);
+          const uint32_t sb = sa + S::A_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            const uint64_t da = make_smem_desc(sa + k * STEP, LBO, 1024, SWZ_128B);
+            const uint64_t db = make_smem_desc(sb + k * STEP, LBO, 1024, SWZ_128B);
+            umma_bf16(tmem_d, da, db, idesc, (i > 0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[s]);
+          if (i == nkb - 1) umma_commit(&tmem_full[buf]);
+        }
+        __syncwarp();
+      }
+    }
+  } else {
+    // ------------------------------ epilogue (warps 2..9): fp32 reduce-add of the accumulator ------------------------------
+    const int q = warp & 3;
+    const int chalf = (warp - 2) >> 2;
+    const int row = q * 32 + lane;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+      int p, m_blk, n_blk;
+      group_decode(grp, tile % tiles_mn, p, m_blk, n_blk);
+      const int buf = it & 1;
+      const long long gm = (long long)m_blk * BM + row;
+      const bool row_ok = gm < grp.M[p];
+      const int Np = grp.N[p];
+      float* obase = grp.out[p] + gm * grp.ldo[p];
+      mbar_wait(&tmem_full[buf], (it >> 1) & 1);
+      tc_fence_after();
+      const uint32_t tmem_d = tmem_base + buf * BN + ((uint32_t)(q * 32) << 16);
+#pragma unroll 1
+      for (int c = chalf * (BN / 64); c < (chalf + 1) * (BN / 64); ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(tmem_d + c * 32, r);
+        tmem_ld_wait();
+        const int n0 = n_blk * BN + c * 32;
+#pragma unroll
+        for (int g = 0; g < 8; ++g) {
+          const int n = n0 + g * 4;
+          if (row_ok && n < Np)
+            red_add_v4_f32(obase + n, __uint_as_float(r[g * 4]) * alpha, __uint_as_float(r[g * 4 + 1]) * alpha,
+                           __uint_as_float(r[g * 4 + 2]) * alpha, __uint_as_float(r[g * 4 + 3]) * alpha);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty[buf]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 2 * BN);
+  }
+}
+
+// =========================================================================================================
 // CTA-pair variant (cta_group::2): two CTAs on the two SMs of a TPC share one 256 x BN output tile.
 // Each CTA TMA-loads its own 128 rows of A and HALF of the B tile; the leader CTA's elected thread issues
 // tcgen05.mma.cta_group::2 (UMMA M = 256), which reads both CTAs' shared memory and writes 128 accumulator rows
@@ -1271,4 +1457,64 @@ extern "C" int dtc_gemm_bf16_scatter(const void* A, long long lda, const void* B
   }
   if (block_n == 64) return launch_gemm_persistent<false, false, 64, true, true>(A, lda, B, ldb, M, N, K, 1, stages, epi, stream);
   return launch_gemm_persistent<false, false, 128, true, true>(A, lda, B, ldb, M, N, K, 1, stages, epi, stream);
+}
+
+// Grouped weight gradients (see gemm_grouped_wgrad_kernel): for p < count
+//   out[p][M_p, N_p] (fp32, leading dimension ldo[p]) += alpha * A[p]ᵀ · B[p],   A[p] = [K, M_p], B[p] = [K, N_p] bf16 row-major.
+// All arrays are HOST arrays of `count` (<= 4) entries.  M_p, N_p multiples of 8; N_p % 64 == 0.
+extern "C" int dtc_gemm_wgrad_grouped(int count, const unsigned long long* A, const long long* lda,
+                                      const unsigned long long* B, const long long* ldb, const int* Ms, const int* Ns, int K,
+                                      const unsigned long long* out, const long long* ldo, float alpha, int splits,
+                                      int stages, cudaStream_t stream) {
+  DTC_CHECK_ARG(count >= 1 && count <= GG_MAX && K > 0, "wgrad_grouped: count=%d (1..%d), K=%d", count, GG_MAX, K);
+  constexpr int BN = 128;
+  using S = PgSmem<BN>;
+  GemmGroup grp;
+  memset(&grp, 0, sizeof(grp));
+  grp.count = count;
+  int tiles = 0;
+  for (int p = 0; p < count; ++p) {
+    DTC_CHECK_ARG(Ms[p] > 0 && Ns[p] > 0 && Ms[p] % 8 == 0 && Ns[p] % 8 == 0 && lda[p] % 8 == 0 && ldb[p] % 8 == 0 &&
+                      ldo[p] % 4 == 0,
+                  "wgrad_grouped: problem %d: M=%d N=%d lda=%lld ldb=%lld ldo=%lld", p, Ms[p], Ns[p], lda[p], ldb[p], ldo[p]);
+    DTC_CHECK_ARG((A[p] & 15) == 0 && (B[p] & 15) == 0 && (out[p] & 15) == 0 && A[p] && B[p] && out[p],
+                  "wgrad_grouped: problem %d: pointers must be non-null and 16-byte aligned", p);
+    int rc;
+    if ((rc = make_tmap_2d_bf16(&grp.a[p], reinterpret_cast<const void*>(A[p]), K, Ms[p], lda[p], BK, 64,
+                                CU_TENSOR_MAP_SWIZZLE_128B)))
+      return rc;
+    if ((rc = make_tmap_2d_bf16(&grp.b[p], reinterpret_cast<const void*>(B[p]), K, Ns[p], ldb[p], BK, 64,
+                                CU_TENSOR_MAP_SWIZZLE_128B)))
+      return rc;
+    grp.out[p] = reinterpret_cast<float*>(out[p]);
+    grp.ldo[p] = ldo[p];
+    grp.M[p] = Ms[p];
+    grp.N[p] = Ns[p];
+    grp.m_blocks[p] = (Ms[p] + BM - 1) / BM;
+    grp.tile_start[p] = tiles;
+    tiles += grp.m_blocks[p] * ((Ns[p] + BN - 1) / BN);
+  }
+  for (int p = count; p <= GG_MAX; ++p) grp.tile_start[p] = tiles;
+  const int total_kb = (K + BK - 1) / BK;
+  if (splits < 1) splits = 1;
+  if (splits > total_kb) splits = total_kb;
+  const int kb_per_split = (total_kb + splits - 1) / splits;
+  splits = (total_kb + kb_per_split - 1) / kb_per_split;
+  if (stages < 2) stages = 3;
+  if (stages > PG_STAGE_MAX) stages = PG_STAGE_MAX;
+  const int smem_cap = 112 * 1024;  // two CTAs per SM
+  auto smem_of = [](int st) { return st * S::STAGE_BYTES + 1024 + 256; };
+  while (stages > 2 && smem_of(stages) > smem_cap) --stages;
+  auto kern = gemm_grouped_wgrad_kernel<BN>;
+  static bool configured = false;
+  if (!configured) {
+    DTC_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 113 * 1024));
+    configured = true;
+  }
+  const int total_tiles = tiles * splits;
+  const int max_ctas = 2 * num_sms();
+  const int grid = total_tiles < max_ctas ? total_tiles : max_ctas;
+  DTC_CHECK_CUDA(dtc::launch(kern, grid, PG_THREADS, smem_of(stages), stream, grp, K, splits, kb_per_split, stages, alpha));
+  DTC_CHECK_LAUNCH();
+  return 0;
 }

@@ -142,6 +142,54 @@ __global__ void __launch_bounds__(256) colsum_kernel(const bf16* __restrict__ x,
   }
 }
 
+// The bias gradients of one layer in one launch: blockIdx.z selects the problem (same body as colsum_kernel).
+constexpr int CG_MAX = 4;
+struct ColsumGroup {
+  const bf16* x[CG_MAX];
+  long long ld[CG_MAX];
+  int M[CG_MAX];
+  int N[CG_MAX];
+  float* out[CG_MAX];
+};
+
+__global__ void __launch_bounds__(256) colsum_grouped_kernel(const __grid_constant__ ColsumGroup grp) {
+  pdl_launch_dependents();
+  pdl_wait();
+  __shared__ float s[8][256 + 8];
+  const int p = blockIdx.z;
+  const bf16* __restrict__ x = grp.x[p];
+  const long long ld = grp.ld[p];
+  const int M = grp.M[p], N = grp.N[p];
+  if ((int)blockIdx.x * 256 >= N) return;   // uniform per CTA: narrower problems use fewer column blocks
+  const int cg = threadIdx.x & 31, rl = threadIdx.x >> 5;
+  const int c = blockIdx.x * 256 + cg * 8;
+  float acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+  if (c < N) {
+    for (int r = blockIdx.y * 8 + rl; r < M; r += gridDim.y * 8) {
+      const uint4 u = *reinterpret_cast<const uint4*>(x + (long long)r * ld + c);
+      const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 f = unpack_bf16x2(w[j]);
+        acc[2 * j] += f.x;
+        acc[2 * j + 1] += f.y;
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s[rl][cg * 8 + j] = acc[j];
+  __syncthreads();
+  const int col = threadIdx.x;
+  if (blockIdx.x * 256 + col < N) {
+    float t = 0.f;
+#pragma unroll
+    for (int r = 0; r < 8; ++r) t += s[r][col];
+    atomicAdd(grp.out[p] + blockIdx.x * 256 + col, t);
+  }
+}
+
 }  // namespace dtc
 
 using namespace dtc;
@@ -191,6 +239,33 @@ extern "C" int dtc_colsum(const void* x, long long ld, int M, int N, float* out,
   if (ysplit > 128) ysplit = 128;
   dim3 grid((N + 255) / 256, ysplit);
   DTC_CHECK_CUDA(dtc::launch(colsum_kernel, grid, 256, 0, stream, reinterpret_cast<const bf16*>(x), ld, M, N, out));
+  DTC_CHECK_LAUNCH();
+  return 0;
+}
+
+// out[p][n] += sum_m x[p][m, n] for p < count (<= 4): the bias gradients of one layer in one launch.
+// All arrays are HOST arrays; x[p] bf16 [M[p], N[p]] with leading dimension ld[p], N[p] % 8 == 0.
+extern "C" int dtc_colsum_grouped(int count, const unsigned long long* x, const long long* ld, const int* M, const int* N,
+                                  const unsigned long long* out, cudaStream_t stream) {
+  DTC_CHECK_ARG(count >= 1 && count <= CG_MAX, "colsum_grouped: count=%d (1..%d)", count, CG_MAX);
+  ColsumGroup grp;
+  int max_n = 0, max_m = 0;
+  for (int p = 0; p < CG_MAX; ++p) {
+    const int q = p < count ? p : 0;
+    DTC_CHECK_ARG(M[q] > 0 && N[q] > 0 && N[q] % 8 == 0 && ld[q] % 8 == 0 && x[q] && out[q] && (x[q] & 15) == 0,
+                  "colsum_grouped: problem %d: bad shape M=%d N=%d ld=%lld or pointer", q, M[q], N[q], ld[q]);
+    grp.x[p] = reinterpret_cast<const bf16*>(x[q]);
+    grp.ld[p] = ld[q];
+    grp.M[p] = M[q];
+    grp.N[p] = N[q];
+    grp.out[p] = reinterpret_cast<float*>(out[q]);
+    if (p < count && N[p] > max_n) max_n = N[p];
+    if (p < count && M[p] > max_m) max_m = M[p];
+  }
+  int ysplit = (max_m + 31) / 32;
+  if (ysplit > 64) ysplit = 64;
+  dim3 grid((max_n + 255) / 256, ysplit, count);
+  DTC_CHECK_CUDA(dtc::launch(colsum_grouped_kernel, grid, 256, 0, stream, grp));
   DTC_CHECK_LAUNCH();
   return 0;
 }

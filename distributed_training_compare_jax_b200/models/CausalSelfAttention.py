@@ -21,10 +21,10 @@ class CausalSelfAttention:
 
     # ------------------------------------------------------------------ torch path
     def __call__(self, p: dict, l: int, x: torch.Tensor, mask: torch.Tensor | None = None) -> torch.Tensor:
-        B, T, D = x.shape
         Hl, hd, Dl = self.local.heads_local, self.config.head_dim, self.local.d_local
         tp = self.mesh.tp
-        x = tp_ops.copy_to_tp(x, tp)
+        x = tp_ops.copy_to_tp(x, tp)      # sequence-parallel mode: all-gather of the rows, so read the shape afterwards
+        B, T, D = x.shape
         qkv = x @ p["wqkv"][l] + p["bqkv"][l]
         q, k, v = (qkv[..., i * Dl:(i + 1) * Dl].reshape(B, T, Hl, hd) for i in range(3))
         w = torch.einsum("bthd,bshd->bhts", q, k) * (hd ** -0.5)
@@ -55,9 +55,9 @@ class CausalSelfAttention:
             Fn.colsum(ws.dqkv, g["bqkv"][l])
             Fn.gemm(ws.ln1[l], ws.dqkv, a_mn=True, b_mn=True, epi="atomic_f32", out=g["wqkv"][l], splits=eng.wgrad_splits)
 
-        eng.side_work(out_param_grads)
+        eng.side_work(out_param_grads, layer=l)
         Fn.gemm(dh, c["wo"][l], out=ws.dattn)
         Fn.flash_attn_bwd(ws.qkv[l], ws.attn[l], ws.dattn, ws.lse2[l], ws.B, self.local.heads_local, ws.T,
                           self.config.head_dim, dqkv=ws.dqkv, dq_accum=ws.dq_accum, delta=ws.delta)
-        eng.side_work(qkv_param_grads)
+        eng.side_work(qkv_param_grads, layer=l)
         ws.dln_cur = eng.tp_reduced_gemm(ws.dqkv, c["wqkv"][l], out=ws.dln)

@@ -39,6 +39,7 @@ class GPTModel:
         if pd > 0:  # deterministic=False in the reference: dropout is always active
             keep = torch.rand(h.shape, device=h.device, generator=dropout_generator) >= pd
             h = torch.where(keep, h / (1.0 - pd), torch.zeros_like(h))
+        h = tp_ops.slice_rows(h, self.mesh.tp)   # sequence-parallel TP: this rank's sequences only (identity otherwise)
         mask = torch.where(torch.tril(torch.ones(T, T, device=x.device)) == 1, 0.0, -1e9)[None, None]
         return h, mask
 

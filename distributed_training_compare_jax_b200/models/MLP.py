@@ -47,7 +47,7 @@ class MLP:
             Fn.colsum(ws.df1, g["b1"][l])
             Fn.gemm(ws.ln2[l], ws.df1, a_mn=True, b_mn=True, epi="atomic_f32", out=g["w1"][l], splits=eng.wgrad_splits)
 
-        eng.side_work(fc2_param_grads)
+        eng.side_work(fc2_param_grads, layer=l)
         Fn.gemm(dh, c["w2"][l], epi="dgelu", aux=ws.f1[l], out=ws.df1)
-        eng.side_work(fc1_param_grads)
+        eng.side_work(fc1_param_grads, layer=l)
         ws.dln_cur = eng.tp_reduced_gemm(ws.df1, c["w1"][l], out=ws.dln)

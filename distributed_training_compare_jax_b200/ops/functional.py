@@ -198,6 +198,55 @@ def colsum(x, out):
     return out
 
 
+class GroupArgs:
+    """Host-side argument block of a grouped launch (ctypes arrays built once, e.g. per layer at engine construction)."""
+
+    def __init__(self, **arrays):
+        import ctypes as C
+        kinds = {"ptr": C.c_ulonglong, "ll": C.c_longlong, "int": C.c_int}
+        self.count = None
+        for name, (kind, values) in arrays.items():
+            values = list(values)
+            if self.count is None:
+                self.count = len(values)
+            elif self.count != len(values):
+                raise ValueError("grouped launch: all argument lists must have the same length")
+            setattr(self, name, (kinds[kind] * len(values))(*values))
+
+
+def wgrad_group_args(xs, dys, outs) -> GroupArgs:
+    """Argument block for :func:`wgrad_grouped`: out[p] [M_p, N_p] fp32 += xs[p]ᵀ · dys[p] with xs[p] [K, M_p], dys[p] [K, N_p]."""
+    for x, dy, o in zip(xs, dys, outs):
+        _check_rowmajor(x, "x"), _check_rowmajor(dy, "dy"), _check_rowmajor(o, "out")
+        if x.shape[0] != dy.shape[0] or tuple(o.shape) != (x.shape[1], dy.shape[1]) or o.dtype != F32:
+            raise ValueError(f"wgrad_grouped: shapes {tuple(x.shape)} {tuple(dy.shape)} -> {tuple(o.shape)} {o.dtype}")
+    if len({x.shape[0] for x in xs}) != 1:
+        raise ValueError("wgrad_grouped: all problems must share the reduction length")
+    args = GroupArgs(a=("ptr", [x.data_ptr() for x in xs]), lda=("ll", [x.stride(0) for x in xs]),
+                     b=("ptr", [d.data_ptr() for d in dys]), ldb=("ll", [d.stride(0) for d in dys]),
+                     m=("int", [x.shape[1] for x in xs]), n=("int", [d.shape[1] for d in dys]),
+                     out=("ptr", [o.data_ptr() for o in outs]), ldo=("ll", [o.stride(0) for o in outs]))
+    args.K = xs[0].shape[0]
+    return args
+
+
+def wgrad_grouped(args: GroupArgs, alpha: float = 1.0, splits: int = 1, stages: int = 0) -> None:
+    """The weight gradients of one layer (<= 4 GEMMs sharing K = tokens) as ONE persistent tcgen05 launch."""
+    native.call("dtc_gemm_wgrad_grouped", args.count, args.a, args.lda, args.b, args.ldb, args.m, args.n, args.K, args.out,
+                args.ldo, float(alpha), splits, stages)
+
+
+def colsum_group_args(xs, outs) -> GroupArgs:
+    return GroupArgs(x=("ptr", [x.data_ptr() for x in xs]), ld=("ll", [x.stride(0) for x in xs]),
+                     m=("int", [x.shape[0] for x in xs]), n=("int", [x.shape[1] for x in xs]),
+                     out=("ptr", [o.data_ptr() for o in outs]))
+
+
+def colsum_grouped(args: GroupArgs) -> None:
+    """out[p] += column sums of xs[p] for up to 4 matrices in one launch (the bias gradients of one layer)."""
+    native.call("dtc_colsum_grouped", args.count, args.x, args.ld, args.m, args.n, args.out)
+
+
 def cast_bf16(src_f32, dst_bf16):
     native.call("dtc_cast_f32_to_bf16", src_f32, dst_bf16, src_f32.numel())
     return dst_bf16

@@ -43,6 +43,8 @@ _PROTOS: dict[str, list[Any]] = {
     "dtc_colsum": [P, L, I, I, P],
     "dtc_symm_barrier": [P, I, I, I],
     "dtc_gemm_bf16_scatter": [P, L, P, L, I, I, I, I, P, I, I, L, I, I],
+    "dtc_gemm_wgrad_grouped": [I, P, P, P, P, P, P, I, P, P, F, I, I],
+    "dtc_colsum_grouped": [I, P, P, P, P, P],
     "dtc_sp_ln_fwd": [P, P, P, I, P, P, P, P, P, U64, P, I, L, I, I, F],
     "dtc_sp_ln_bwd": [P, I, P, P, P, P, P, P, P, U64, P, I, L, I, I],
     "dtc_dp_reduce_scatter": [P, U64, P, I, I, L, L, P],

@@ -28,6 +28,7 @@ class Axis:
     group: object | None = None
     ranks: list[int] = field(default_factory=lambda: [0])
     group2: object | None = None  # second communicator over the same ranks (PP: upstream gradient traffic)
+    seq_parallel: bool = False    # TP axis, torch path: activations row-sharded between the TP regions (parallel/tp_ops.py)
 
     def all_reduce(self, t: torch.Tensor, op=None) -> torch.Tensor:
         if self.size > 1:

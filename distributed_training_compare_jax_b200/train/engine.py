@@ -89,13 +89,15 @@ class StageEngineBase:
 class NativeStageEngine(StageEngineBase):
     backend = "native"
 
-    def __init__(self, *a, wgrad_splits: int = 0, overlap_wgrad: bool = True, **kw):
+    def __init__(self, *a, wgrad_splits: int = 0, overlap_wgrad: bool = True, wgrad_grouped: bool = False, **kw):
         super().__init__(*a, **kw)
         # Weight-gradient work (wgrad GEMMs + bias column sums) does not feed the backward chain: it runs on a side
         # stream concurrently with the dgrad / attention / LayerNorm chain.  Both streams then use the light GEMM
         # kernel (98 KB smem, 128 TMEM columns) so that two GEMM CTAs fit on one SM.
         self.overlap_wgrad = overlap_wgrad
         self.bwd_gemm_impl = int(__import__('os').environ.get('DTC_BWD_GEMM_IMPL', '0'))
+        # experimental (not yet measured on B200): one grouped wgrad launch + one grouped bias-grad launch per layer
+        self.wgrad_grouped = wgrad_grouped or __import__('os').environ.get('DTC_WGRAD_GROUPED', '0') == '1'
         self.side = None  # side stream of the workspace currently being processed (set in forward / backward)
         if self.device.type != "cuda":
             raise RuntimeError("the native engine needs a CUDA device (sm_100a)")
@@ -113,6 +115,16 @@ class NativeStageEngine(StageEngineBase):
             # global row index of local row 0: distinct dropout masks per DP rank / microbatch, identical across TP
             w.row_offset = (dp.rank * self.n_micro + i) * M
             w.side = torch.cuda.Stream(device=self.device) if self.overlap_wgrad else None
+            if self.wgrad_grouped:
+                # layer l's parameter gradients run while layer l-1's chain is already rewriting the scratch buffers:
+                # two scratch sets (by layer parity) and a third dL/dh buffer keep their operands alive
+                D, Dl, Fl = self.cfg.d_model, self.local.d_local, self.local.ff_local
+                w.dh_c = torch.empty(M, D, device=self.device, dtype=BF16)
+                w.scratch = [(w.df1, w.dqkv, w.dh_mid),
+                             (torch.empty(M, Fl, device=self.device, dtype=BF16),
+                              torch.empty(M, 3 * Dl, device=self.device, dtype=BF16),
+                              torch.empty(M, D, device=self.device, dtype=BF16))]
+                w.group_args = {}
             self.ws.append(w)
         self.tp_hooks = None  # set by parallel/tp.py when the fused GEMM+collective kernels are enabled
 
@@ -133,9 +145,12 @@ class NativeStageEngine(StageEngineBase):
             Fn.gemm(x, w, b_mn=True, out=out)
         tp.all_reduce(out)
 
-    def side_work(self, fn) -> None:
+    def side_work(self, fn, layer: int | None = None) -> None:
         """Run ``fn`` (kernel launches that only produce parameter gradients) on the side stream, after everything
-        issued so far on the main stream."""
+        issued so far on the main stream.  ``layer``: set for the per-layer weight / bias gradients, which the grouped
+        mode replaces by one launch per layer (``_stage_backward_grouped``)."""
+        if layer is not None and self.wgrad_grouped:
+            return
         if self.side is None:
             fn()
             return
@@ -196,7 +211,10 @@ class NativeStageEngine(StageEngineBase):
         self.side = ws.side
         top = ws.dh_top if self.local.has_head else ws.dh_b
         with self.backward_gemm_impl():
-            dh0 = self.model.native_stage_backward(self, ws, top)
+            if self.wgrad_grouped:
+                dh0 = self._stage_backward_grouped(ws, top)
+            else:
+                dh0 = self.model.native_stage_backward(self, ws, top)
         self.side_join()
         if self.local.has_embed:
             self.model.native_embed_backward(self, ws, dh0)
@@ -204,12 +222,76 @@ class NativeStageEngine(StageEngineBase):
         return dh0
 
 
+def _grouped_backward_impl(self, ws, top: torch.Tensor) -> torch.Tensor:
+    """Backward through the local layers with ONE grouped weight-gradient launch and ONE grouped bias-gradient launch per
+    layer on the side stream (instead of 4 split-K GEMMs + 4 column sums issued along the chain).  The launch of layer l
+    runs concurrently with the chain of layer l-1; its operands stay alive because the scratch buffers alternate by
+    layer parity and dL/dh rotates through three buffers; the chain of layer l-2 waits for it."""
+    L, g = self.local.L, self.g
+    main = torch.cuda.current_stream()
+    ring = [ws.dh_a, ws.dh_b, ws.dh_c]
+    i = next((k for k, b in enumerate(ring) if b.data_ptr() == top.data_ptr()), None)
+    if i is None:            # gradient arrived in a foreign buffer: start the rotation next to it
+        ring, i = [top, ws.dh_a, ws.dh_b], 0
+    cur = top
+    events: dict[int, torch.cuda.Event] = {}
+    tiles = 0
+
+    def release(layer: int) -> None:   # layer's parameter gradients are complete: buffers reusable, DP bucket reducible
+        main.wait_event(events[layer])
+        if self.has_grad_hooks:
+            self.on_layer_grads_ready(layer)
+
+    for l in reversed(range(L)):
+        if l + 2 < L:
+            release(l + 2)
+        ws.df1, ws.dqkv, ws.dh_mid = ws.scratch[l & 1]
+        i = (i + 1) % 3
+        nxt = ring[i]
+        self.model.block.native_backward(self, ws, l, cur, ws.dh_mid, nxt)
+        key = (l, cur.data_ptr())
+        if key not in ws.group_args:
+            xs = [ws.g[l], ws.ln2[l], ws.attn[l], ws.ln1[l]]
+            dys = [cur, ws.df1, ws.dh_mid, ws.dqkv]
+            ws.group_args[key] = (Fn.colsum_group_args(dys, [g["b2"][l], g["b1"][l], g["bo"][l], g["bqkv"][l]]),
+                                  Fn.wgrad_group_args(xs, dys, [g["w2"][l], g["w1"][l], g["wo"][l], g["wqkv"][l]]))
+            tiles = sum(-(-x.shape[1] // 128) * -(-d.shape[1] // 128) for x, d in zip(xs, dys))
+        cs_args, wg_args = ws.group_args[key]
+        splits = getattr(ws, "group_splits", None)
+        if splits is None:   # fill 2 CTAs per SM when the layer is small (tensor-parallel shards)
+            splits = ws.group_splits = max(1, min(8, 296 // max(tiles, 1)))
+        side = self.side if self.side is not None else main
+        if side is not main:
+            side.wait_stream(main)
+        with torch.cuda.stream(side):
+            Fn.colsum_grouped(cs_args)
+            Fn.wgrad_grouped(wg_args, splits=splits)
+            ev = torch.cuda.Event()
+            ev.record(side)
+        events[l] = ev
+        cur = nxt
+    for l in (1, 0):
+        if l < L:
+            release(l)
+    return cur
+
+
+NativeStageEngine._stage_backward_grouped = _grouped_backward_impl
+
+
 class TorchStageEngine(StageEngineBase):
     """fp32 autograd engine over the same ParamStore (CPU oracle / gloo path / cuBLAS stand-in baseline)."""
     backend = "torch"
 
-    def __init__(self, *a, **kw):
+    def __init__(self, *a, seq_parallel: bool = False, **kw):
         super().__init__(*a, **kw)
+        # sequence-parallel TP (the fp32 counterpart of parallel/tp_sp.py): same conditions as the native engine
+        tp = self.mesh.tp
+        self.seq_parallel = bool(seq_parallel and tp.size > 1 and self.local.has_embed and self.local.has_head
+                                 and self.n_micro == 1 and self.micro_batch % tp.size == 0)
+        tp.seq_parallel = self.seq_parallel
+        st = self.store
+        self._partial_grads = st.flat_grad[st.offsets["ln1_g"][0]:st.rep_numel] if self.seq_parallel else None
         self.params = {}
         for name in self.store.names():
             p = self.store.p[name]
@@ -271,6 +353,8 @@ class TorchStageEngine(StageEngineBase):
         else:
             self._out[mb].backward(self.grad_input_buffer(mb))
         self._loss[mb], self._out[mb] = None, None
+        if self.seq_parallel:   # LayerNorm / row-bias gradients come from the owned rows only: sum over the TP group
+            self.mesh.tp.all_reduce(self._partial_grads)
         if self.local.has_embed:
             return None
         g = self._in[mb].grad
@@ -279,6 +363,7 @@ class TorchStageEngine(StageEngineBase):
 
 def make_engine(backend: str, *args, **kw) -> StageEngineBase:
     if backend == "native":
+        kw.pop("seq_parallel", None)   # the native sequence-parallel engine is parallel/tp_sp.py (chosen in build_state)
         return NativeStageEngine(*args, **kw)
     if backend == "torch":
         kw.pop("wgrad_splits", None)

@@ -60,7 +60,7 @@ def build_state(train_config: TrainConfig, model_config: ModelConfig, opt_config
                 print(f"[dtc] sequence-parallel TP unavailable ({e}); using the replicated-activation TP path", flush=True)
     if engine is None:
         engine = make_engine(backend, model_config, local, mesh, store, micro_batch, model_config.max_seq_len, n_micro,
-                             global_tokens, train_config.seed)
+                             global_tokens, train_config.seed, seq_parallel=train_config.tp_seq_parallel)
     reducer = None
     if native_dp and not fused_dp:
         from ..parallel.dp import make_grad_reducer
@@ -122,7 +122,8 @@ def _run_loop(train_config: TrainConfig, model_config: ModelConfig, state: Train
     metrics = {"strategy": strategy, "world_size": mesh.world_size, "backend": state.engine.backend,
                "steps": train_config.steps, "device_ms_per_step_max_over_ranks": ms / steps,
                "tokens_per_step": tokens_per_step, "tokens_per_s": tokens_per_step * steps / (ms / 1e3) if ms else 0.0,
-               "final_loss": log.loss_history[-1] if log.loss_history else None}
+               "final_loss": log.loss_history[-1] if log.loss_history else None,
+               "tp_seq_parallel": bool(getattr(state.engine, "seq_parallel", False) or hasattr(state.engine, "sp"))}
     log.finish(metrics)
     if train_config.checkpoint_dir:
         if hasattr(state.optimizer, "sync_full_state"):

@@ -140,6 +140,16 @@ int dtc_sp_ln_fwd(const void* res, const void* bias, const void* part, int n_par
 int dtc_sp_ln_bwd(const void* part, int n_part, const void* x, const float* mean, const float* rstd, const void* gamma,
                   const void* dres, float* dgamma, float* dbeta, unsigned long long mc_out,
                   const unsigned long long* peer_out, int n_out, long long out_row0, int Ms, int D, cudaStream_t stream);
+
+/* ---- grouped parameter-gradient launches (experimental, `DTC_WGRAD_GROUPED=1`): the four weight gradients of a layer
+ *      (K16 of SURVEY.md section 2.5) as ONE persistent tcgen05 launch without split-K, and its four bias gradients as
+ *      one column-sum launch.  All arrays are HOST arrays of `count` (<= 4) entries. ----
+ * out[p][M_p, N_p] (fp32) += alpha * A[p]^T B[p],  A[p] = [K, M_p], B[p] = [K, N_p] bf16 row-major. */
+int dtc_gemm_wgrad_grouped(int count, const unsigned long long* A, const long long* lda, const unsigned long long* B,
+                           const long long* ldb, const int* Ms, const int* Ns, int K, const unsigned long long* out,
+                           const long long* ldo, float alpha, int splits, int stages, cudaStream_t stream);
+int dtc_colsum_grouped(int count, const unsigned long long* x, const long long* ld, const int* M, const int* N,
+                       const unsigned long long* out, cudaStream_t stream);
 int dtc_gemm_set_dual(int bits);   /* tuning: bit0 two-CTAs-per-SM GEMM, bit1 64-wide tiles for small grids, bit2 coop stores */
 
 #ifdef __cplusplus

@@ -54,9 +54,13 @@ def test_dp2_matches_single_device(single, tmp_path):
     np.testing.assert_allclose(loss, single, rtol=2e-5)
 
 
-def test_tp2_matches_single_device(single, tmp_path):
-    loss, _ = _run(tmp_path, "tp2", "tp", 2)
+@pytest.mark.parametrize("seq_parallel", [True, False])
+def test_tp2_matches_single_device(single, tmp_path, seq_parallel):
+    # seq_parallel: the residual stream is row-sharded between the TP regions (all-gather / reduce-scatter halves of the
+    # all-reduce, LayerNorm + row-bias gradients summed over the group afterwards) — the fp32 model of parallel/tp_sp.py
+    loss, _ = _run(tmp_path, "tp2", "tp", 2, tp_seq_parallel=seq_parallel)
     np.testing.assert_allclose(loss, single, rtol=2e-5)       # reference DP-vs-TP gap over 10 steps: 2e-5
+    assert json.load(open(tmp_path / "tp2" / "metrics.json"))["tp_seq_parallel"] is seq_parallel
 
 
 @pytest.mark.parametrize("schedule", ["gpipe", "1f1b"])
@@ -82,6 +86,7 @@ def test_pp3_uneven_layers_1f1b_matches_single_device(single, tmp_path):
 def test_dp2_x_tp2_hybrid_mesh_matches_single_device(single, tmp_path):
     loss, _ = _run(tmp_path, "dptp", "dp_tp", 4, dp_size=2, tp_size=2)
     np.testing.assert_allclose(loss, single, rtol=2e-5)
+    assert json.load(open(tmp_path / "dptp" / "metrics.json"))["tp_seq_parallel"] is True   # 2 sequences per TP group
 
 
 def test_metrics_json_and_plot_summary(single, tmp_path):
