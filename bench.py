@@ -75,7 +75,7 @@ def run(args) -> dict | None:
                      global_batch_is_per_device=True, sync_every_step=True, backend=args.backend,
                      pp_schedule=args.pp_schedule, fused_comm=not args.no_fused_comm, cuda_graph=not args.no_graph,
                      dp_overlap=not args.no_dp_overlap, tp_fused=args.tp_fused,
-                     tp_seq_parallel=not args.no_tp_seq_parallel)
+                     tp_seq_parallel=not args.no_tp_seq_parallel, pp_cuda_graph=args.pp_graph)
     mc = load_model_config(os.path.join(ROOT, args.model_config), vocab_size=VOCAB_SIZE, parallel=strategy)
     oc = load_optim_config(os.path.join(ROOT, "configs/optim_config.yaml"))
     dp, tp, pp = mesh_shape(tc, world)
@@ -89,7 +89,7 @@ def run(args) -> dict | None:
         M = tc.pp_microbatches
         state = build_state(tc, mc, oc, mesh, global_batch // M, M, global_batch * T, local, clip_scope=tc.pp_clip,
                             clip_scale=1.0 / pp, pp_stage_keys=True)
-        train_step = create_pp_train_step(M, pp, tc.pp_schedule)
+        train_step = create_pp_train_step(M, pp, tc.pp_schedule, cuda_graph=tc.pp_cuda_graph and tc.cuda_graph)
         it = get_batch_iterator(global_batch, T + 1, seed=0)
     else:
         global_batch = per_rank_batch * dp
@@ -202,6 +202,8 @@ def main() -> int:
                     "GEMM-epilogue reduce-scatter + LayerNorm all-gather")
     ap.add_argument("--no-tp-seq-parallel", action="store_true", help="TP: replicated activations, GEMM + NCCL all-reduce")
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--pp-graph", action="store_true",
+                    help="PP: one CUDA graph per (forward | backward, microbatch) of a stage (experimental)")
     ap.add_argument("--chains", type=int, default=1, help="concurrent chains the local batch is split into (DP)")
     args = ap.parse_args()
     if args.impl == "reference":

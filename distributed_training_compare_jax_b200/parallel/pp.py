@@ -114,15 +114,50 @@ class P2PBackend:
 class PipelineExecutor:
     """Walks a stage's action list, moving activations (forward) and activation gradients (backward)."""
 
-    def __init__(self, engine, axis, schedule: str, p2p=None):
+    def __init__(self, engine, axis, schedule: str, p2p=None, cuda_graph: bool = False, eager_steps: int = 2):
         self.engine, self.axis = engine, axis
         self.stage, self.n_stages = axis.rank, axis.size
         self.actions = build_schedule(schedule, self.n_stages, self.stage, engine.n_micro)
         self.p2p = p2p or P2PBackend(axis)
         self.trace: list[tuple[str, int]] = []  # (event, mb) — used by the schedule tests
+        # Optional (native engine): every (forward | backward, microbatch) of this stage becomes one CUDA graph, so a step
+        # costs 2·M graph launches + the NCCL send / recv calls instead of a few hundred kernel launches from Python
+        # (the host of the GPU box needs ~15 us per launch: an eager pipeline step is host-bound).  All graphs are
+        # captured in one pass BETWEEN two steps — capture records without executing and involves no communication, so
+        # every stage does it at the same step without any cross-stage ordering constraint.
+        self.cuda_graph = bool(cuda_graph and getattr(engine, "backend", "") == "native")
+        self.eager_steps = eager_steps
+        self.steps_run = 0
+        self.graphs: dict[tuple[str, int], tuple] = {}
+
+    def _capture_all(self) -> None:
+        from ..ops import native
+        eng = self.engine
+        torch.cuda.synchronize()
+        for kind, mb in sorted({(a.kind, a.mb) for a in self.actions}):
+            g = torch.cuda.CUDAGraph()
+            before = native.launches()
+            with torch.cuda.graph(g):
+                out = eng.forward(mb) if kind == "F" else eng.backward(mb)
+            n = native.launches() - before          # recorded, not executed
+            native.add_launches(-n)
+            self.graphs[(kind, mb)] = (g, out, n)
+
+    def _do(self, kind: str, mb: int):
+        hit = self.graphs.get((kind, mb))
+        if hit is None:
+            return self.engine.forward(mb) if kind == "F" else self.engine.backward(mb)
+        from ..ops import native
+        g, out, n = hit
+        g.replay()
+        native.add_launches(n)
+        return out
 
     def run(self) -> None:
         eng, first, last = self.engine, self.stage == 0, self.stage == self.n_stages - 1
+        if self.cuda_graph and not self.graphs and self.steps_run >= self.eager_steps:
+            self._capture_all()
+        self.steps_run += 1
         for a in self.actions:
             if a.kind == "F" and not first:
                 self.p2p.recv(eng.input_buffer(a.mb), self.stage - 1)
@@ -130,11 +165,11 @@ class PipelineExecutor:
                 self.p2p.recv(eng.grad_input_buffer(a.mb), self.stage + 1)
             self.trace.append((a.kind, a.mb))
             if a.kind == "F":
-                out = eng.forward(a.mb)
+                out = self._do("F", a.mb)
                 if not last:
                     self.p2p.send(out, self.stage + 1)
             else:
-                gin = eng.backward(a.mb)
+                gin = self._do("B", a.mb)
                 if not first:
                     self.p2p.send(gin.contiguous(), self.stage - 1)
         self.p2p.flush()

@@ -150,7 +150,7 @@ def create_train_step(parallel: str = "dp", cuda_graph: bool = True) -> Any:
     return train_step
 
 
-def create_pp_train_step(num_microbatches: int, num_stages: int, schedule: str = "gpipe") -> Any:
+def create_pp_train_step(num_microbatches: int, num_stages: int, schedule: str = "gpipe", cuda_graph: bool = False) -> Any:
     cache: dict = {}
     executors: dict = {}
 
@@ -165,7 +165,7 @@ def create_pp_train_step(num_microbatches: int, num_stages: int, schedule: str =
             eng.set_batch(m, x[m * mbs:(m + 1) * mbs], y[m * mbs:(m + 1) * mbs])
         _mark_copied(dev, cache)
         if id(eng) not in executors:
-            executors[id(eng)] = PipelineExecutor(eng, mesh.pp, schedule)
+            executors[id(eng)] = PipelineExecutor(eng, mesh.pp, schedule, cuda_graph=cuda_graph)
         eng.begin_step()
         executors[id(eng)].run()
         opt.step()

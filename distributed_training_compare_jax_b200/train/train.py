@@ -168,7 +168,8 @@ def train_pp(train_config: TrainConfig, model_config: ModelConfig, opt_config: O
     state = build_state(train_config, model_config, opt_config, mesh, train_config.batch // M, M,
                         train_config.batch * T, local, clip_scope=train_config.pp_clip, clip_scale=clip_scale,
                         pp_stage_keys=(train_config.pp_init == "reference"))
-    train_step = create_pp_train_step(num_microbatches=M, num_stages=S, schedule=train_config.pp_schedule)
+    train_step = create_pp_train_step(num_microbatches=M, num_stages=S, schedule=train_config.pp_schedule,
+                                      cuda_graph=train_config.pp_cuda_graph and train_config.cuda_graph)
     data_iterator = get_batch_iterator(batch_size=train_config.batch, seq_len=T + 1, seed=train_config.seed,
                                        synthetic=train_config.synthetic_data)
     return _run_loop(train_config, model_config, state, train_step, data_iterator, mesh, train_config.batch * T,

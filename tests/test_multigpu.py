@@ -81,3 +81,13 @@ def test_tp2_sequence_parallel_native(single, tmp_path):
 def test_dp2_tp2_sequence_parallel_native(single, tmp_path):
     loss = _run(tmp_path, "dptp_sp", "dp_tp", 4, dp_size=2, tp_size=2, tp_seq_parallel=True)
     np.testing.assert_allclose(loss, single, rtol=5e-3, atol=5e-3)
+
+
+@pytest.mark.skipif(NGPU < 2 or os.environ.get("DTC_EXPERIMENTAL") != "1",
+                    reason="needs >= 2 GPUs; unvalidated: set DTC_EXPERIMENTAL=1")
+@pytest.mark.parametrize("schedule", ["gpipe", "1f1b"])
+def test_pp2_cuda_graph_per_action(single, tmp_path, schedule):
+    """Every (forward | backward, microbatch) of a stage replayed as one CUDA graph (parallel/pp.py)."""
+    loss = _run(tmp_path, f"pp2_graph_{schedule}", "pp", 2, pp_microbatches=2, pp_init="shared", pp_clip="global",
+                pp_schedule=schedule, pp_cuda_graph=True)
+    np.testing.assert_allclose(loss, single, rtol=5e-3, atol=5e-3)
