@@ -123,6 +123,58 @@ if buf.mc_ptr:
     wire = M * D * 2  # bf16 tile data every rank must push into the switch once
     out["tp"] = {"fused_gemm_mcred_barrier_copy_zero_us": t_f, "gemm_plus_nccl_allreduce_us": t_u,
                  "wire_time_at_770GBps_us": wire / LINK * 1e6, "shape": [M, D, F]}
+# ---------------------------------------------------------------- TP, sequence-parallel form (parallel/tp_sp.py)
+# one sublayer boundary: row-parallel GEMM -> [sum over ranks + bias + residual] -> LayerNorm -> operand of the next GEMM
+#   plain : GEMM(+bias+residual epilogue) -> NCCL all-reduce of [M, D] -> LayerNorm over all M rows on every rank
+#   seqpar: GEMM with the scatter epilogue (P2P stores into the owner's slots) -> flag barrier -> reduce + bias + residual +
+#           LayerNorm on the M/n owned rows, output pushed to every rank (multimem.st) -> flag barrier
+if M % (world * 128) == 0:
+    import ctypes as C
+    Ms, row0 = M // world, rank * (M // world)
+    arena = SymmBuffer(2 * M * D, torch.bfloat16, dev, grp)          # [partial-sum slots | gathered LayerNorm output]
+    part, xg = arena.tensor[:M * D].view(world, Ms, D), arena.tensor[M * D:].view(M, D)
+    part_ptrs = (C.c_ulonglong * world)(*arena.ptrs)
+    xg_ptrs = (C.c_ulonglong * world)(*[q + M * D * 2 for q in arena.ptrs])
+    xg_mc = arena.mc_ptr + M * D * 2 if arena.mc_ptr else 0
+    res, bias = torch.randn(M, D, device=dev).to(torch.bfloat16), torch.randn(D, device=dev).to(torch.bfloat16)
+    gam, bet = torch.ones(D, device=dev, dtype=torch.bfloat16), torch.zeros(D, device=dev, dtype=torch.bfloat16)
+    hsum = torch.empty(Ms, D, device=dev, dtype=torch.bfloat16)
+    mean, rstd = torch.empty(M, device=dev), torch.empty(M, device=dev)
+    lnout = torch.empty(M, D, device=dev, dtype=torch.bfloat16)
+    sslot = [0]
+
+    def sp_bar():
+        bar(3 + sslot[0] % 12)
+        sslot[0] += 1
+
+    def seqpar():
+        Fn.gemm_scatter(x, w, part_ptrs, world, rank, D, b_mn=True)
+        sp_bar()
+        Fn.sp_ln_fwd(res[row0:row0 + Ms], bias, part, world, gam, bet, hsum, mean[:Ms], rstd[:Ms], xg_mc, xg_ptrs, world, row0)
+        sp_bar()
+
+    def plain():
+        Fn.gemm(x, w, b_mn=True, bias=bias, epi="bias_residual", aux=res, out=outb)
+        dist.all_reduce(outb)
+        Fn.layernorm_fwd(outb, gam, bet, out=lnout, mean=mean, rstd=rstd)
+
+    rs_, reps = graphed(seqpar)
+    t_sp = timed(rs_, iters=5) / reps
+    rp_, reps = graphed(plain)
+    t_pl = timed(rp_, iters=5) / reps
+    out["tp_seqpar"] = {"gemm_scatter_barrier_reduceLN_push_barrier_us": t_sp, "gemm_nccl_allreduce_layernorm_us": t_pl,
+                        "multicast": bool(xg_mc), "shape": [M, D, F],
+                        "wire_bytes_per_gpu": (world - 1) / world * M * D * 2 + Ms * D * 2,
+                        "wire_time_at_770GBps_us": ((world - 1) / world * M * D * 2 + Ms * D * 2) / LINK * 1e6}
+    del rs_, rp_
 if rank == 0:
-    print(json.dumps(out))
-dist.destroy_process_group()
+    print(json.dumps(out), flush=True)
+# CUDA graphs that captured NCCL work must be gone before the process group is destroyed (else destroy can hang)
+for name in ("rf", "ru"):
+    globals().pop(name, None)
+import gc  # noqa: E402
+
+gc.collect()
+torch.cuda.synchronize()
+dist.barrier()
+os._exit(0)
