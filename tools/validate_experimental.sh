@@ -31,6 +31,11 @@ if [ "$N" -ge 4 ]; then
     run dptp_medium_nccl python bench.py --gpus 8 --parallel dp_tp --steps 10 --warmup 3 --model-config configs/model_config_medium.yaml --no-tp-seq-parallel
   fi
 fi
+if [ "$N" -ge 2 ]; then
+  timeout 120 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29581 \
+    tools/comm_bench.py 2> gpurun_out/x_comm_bench_${N}gpu.err | tail -1 > gpurun_out/comm_bench_${N}gpu_r2.json
+  echo "comm_bench rc=$? $(cut -c1-600 gpurun_out/comm_bench_${N}gpu_r2.json)"
+fi
 python - <<'PY'
 import glob, json
 for f in sorted(glob.glob("gpurun_out/x_*.json")):
