@@ -49,8 +49,9 @@ def build_state(train_config: TrainConfig, model_config: ModelConfig, opt_config
                        symm_group=mesh.dp.group if fused_dp else None)
     init_params(store, train_config.seed, pp_stage_keys=pp_stage_keys, stage_index=mesh.pp.rank)
     engine = None
+    # (hybrid DP×TP keeps the replicated-activation TP path until the combination has run on hardware: DTC_SP_HYBRID=1)
     if (backend == "native" and train_config.tp_seq_parallel and mesh.tp.size > 1 and mesh.pp.size == 1 and n_micro == 1
-            and train_config.fused_comm):
+            and train_config.fused_comm and (mesh.dp.size == 1 or os.environ.get("DTC_SP_HYBRID") == "1")):
         from ..parallel.tp_sp import SeqParallelEngine
         try:   # the conditions checked inside are the same on every rank, so all ranks fall back together
             engine = SeqParallelEngine(model_config, local, mesh, store, micro_batch, model_config.max_seq_len, n_micro,

@@ -27,7 +27,7 @@ if [ "$N" -ge 4 ]; then
   run pp${N}_eager python bench.py --gpus $N --parallel pp --steps 30 --warmup 5
   run pp${N}_graph python bench.py --gpus $N --parallel pp --steps 30 --warmup 5 --pp-graph
   if [ "$N" = "8" ]; then
-    run dptp_medium_seqpar python bench.py --gpus 8 --parallel dp_tp --steps 10 --warmup 3 --model-config configs/model_config_medium.yaml
+    DTC_SP_HYBRID=1 run dptp_medium_seqpar python bench.py --gpus 8 --parallel dp_tp --steps 10 --warmup 3 --model-config configs/model_config_medium.yaml
     run dptp_medium_nccl python bench.py --gpus 8 --parallel dp_tp --steps 10 --warmup 3 --model-config configs/model_config_medium.yaml --no-tp-seq-parallel
   fi
 fi
