@@ -21,6 +21,7 @@
 #include <string.h>
 
 #include "common.cuh"
+#include "spsync.cuh"
 #include "tma_host.h"
 
 namespace dtc {
@@ -67,10 +68,20 @@ struct GemmEpiScatter : GemmEpi {
   bf16* peer_out[8];     // base of every rank's partial-sum buffer ([n_ranks * sp_rows, ldo] bf16)
   int sp_rank, sp_rows;  // this rank; rows owned per rank
 };
-template <bool SCATTER>
+// ... plus the folded-barrier signal block (experimental SIGNAL instantiations: the last CTA publishes the scattered tiles
+// to every rank itself instead of a barrier kernel after the GEMM)
+struct GemmEpiScatterSync : GemmEpiScatter {
+  SpSync sync;
+};
+template <bool SCATTER, bool SIGNAL = false>
 struct EpiArgT { using type = GemmEpi; };
 template <>
-struct EpiArgT<true> { using type = GemmEpiScatter; };
+struct EpiArgT<true, false> { using type = GemmEpiScatter; };
+template <>
+struct EpiArgT<true, true> { using type = GemmEpiScatterSync; };
+
+DTC_DEVICE void scatter_signal(const GemmEpi&, unsigned) {}
+DTC_DEVICE void scatter_signal(const GemmEpiScatterSync& epi, unsigned n_ctas) { sp_signal(epi.sync, n_ctas); }
 
 // destination of the output tile whose first row is m0: (base pointer, row shift)
 DTC_DEVICE void scatter_dest(const GemmEpi& epi, int, bf16*& base, long long& rshift) {
@@ -357,12 +368,12 @@ DTC_DEVICE void epi_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); 
 // or issuing warps, while two co-resident CTAs are each served at that rate.  The DUAL variant therefore keeps the
 // CTA under 113 KB of shared memory (2-3 stages, ONE staging tile: the residual / pre-activation tile is TMA-loaded
 // into the output staging tile by the epilogue leader and overwritten in place) and 256 TMEM columns.
-template <bool A_MN, bool B_MN, int BN, bool DUAL, bool SCATTER = false>
+template <bool A_MN, bool B_MN, int BN, bool DUAL, bool SCATTER = false, bool SIGNAL = false>
 __global__ void __launch_bounds__(PG_THREADS, DUAL ? 2 : 1)
 gemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                        const __grid_constant__ CUtensorMap tma_out, const __grid_constant__ CUtensorMap tma_out2,
                        const __grid_constant__ CUtensorMap tma_aux, int M, int N, int K, int m_blocks, int n_blocks,
-                       int splits, int kb_per_split, int num_stages, const typename EpiArgT<SCATTER>::type epi) {
+                       int splits, int kb_per_split, int num_stages, const typename EpiArgT<SCATTER, SIGNAL>::type epi) {
   using S = PgSmem<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -690,6 +701,11 @@ gemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
       }
     }
     if (bf16_out && store_leader) tma_store_wait_all();
+    if (SIGNAL) {  // every tile of this CTA has been stored to its owner: fence, then the last CTA of the grid signals all ranks
+      __threadfence_system();
+      epi_bar_sync();
+      if (store_leader) scatter_signal(epi, gridDim.x);
+    }
   }
 
   tc_fence_before();
@@ -711,9 +727,10 @@ static int num_sms() {
   return n;
 }
 
-template <bool A_MN, bool B_MN, int BN, bool DUAL, bool SCATTER = false>
+template <bool A_MN, bool B_MN, int BN, bool DUAL, bool SCATTER = false, bool SIGNAL = false>
 static int launch_gemm_persistent(const void* A, long long lda, const void* B, long long ldb, int M, int N, int K,
-                                  int splits, int stages, const typename EpiArgT<SCATTER>::type& epi, cudaStream_t stream) {
+                                  int splits, int stages, const typename EpiArgT<SCATTER, SIGNAL>::type& epi,
+                                  cudaStream_t stream) {
   using S = PgSmem<BN>;
   CUtensorMap ta, tb, tout, tout2, taux;
   int rc;
@@ -749,7 +766,7 @@ static int launch_gemm_persistent(const void* A, long long lda, const void* B, l
   const bool staging = epi.mode <= EPI_DGELU || SCATTER;
   while (stages > 2 && S::bytes(stages, DUAL, staging) > smem_cap) --stages;
   const int smem_bytes = S::bytes(stages, DUAL, staging);
-  auto kern = gemm_persistent_kernel<A_MN, B_MN, BN, DUAL, SCATTER>;
+  auto kern = gemm_persistent_kernel<A_MN, B_MN, BN, DUAL, SCATTER, SIGNAL>;
   static bool configured = false;
   if (!configured) {
     DTC_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, DUAL ? 113 * 1024 : 227 * 1024));
@@ -1419,15 +1436,16 @@ extern "C" int dtc_gemm_bf16(const void* A, long long lda, int a_mn_major, const
 //   peer_out[o][(rank*M/n + row - o*M/n) * ldo + col]                (bf16; P2P stores over NVLink, or local for o == rank)
 // `peer_out` is a HOST array of n_ranks device pointers (the symmetric buffer of every rank, each [M, ldo] bf16).
 // The caller separates this kernel from the owner's reduction with a cross-rank barrier (dtc_symm_barrier).
-extern "C" int dtc_gemm_bf16_scatter(const void* A, long long lda, const void* B, long long ldb, int b_mn_major, int M, int N,
-                                     int K, const unsigned long long* peer_out, int n_ranks, int rank, long long ldo,
-                                     int stages, int block_n, cudaStream_t stream) {
+template <bool SIGNAL>
+static int gemm_scatter_impl(const void* A, long long lda, const void* B, long long ldb, int b_mn_major, int M, int N, int K,
+                             const unsigned long long* peer_out, int n_ranks, int rank, long long ldo, int stages,
+                             int block_n, const unsigned long long* sig_ptrs, int* counters, cudaStream_t stream) {
   DTC_CHECK_ARG(M > 0 && N > 0 && K > 0, "gemm_scatter: empty problem M=%d N=%d K=%d", M, N, K);
   DTC_CHECK_ARG(n_ranks >= 1 && n_ranks <= 8 && rank >= 0 && rank < n_ranks, "gemm_scatter: bad rank %d of %d", rank, n_ranks);
   DTC_CHECK_ARG(M % (n_ranks * BM) == 0, "gemm_scatter: M=%d must be a multiple of n_ranks*128 (no tile may straddle owners)", M);
   DTC_CHECK_ARG(N % 64 == 0 && lda % 8 == 0 && ldb % 8 == 0 && ldo % 8 == 0, "gemm_scatter: N %% 64, ld %% 8 required");
   DTC_CHECK_ARG(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0, "gemm_scatter: operand pointers must be 16-byte aligned");
-  GemmEpiScatter epi;
+  typename EpiArgT<true, SIGNAL>::type epi;
   epi.mode = EPI_SCATTER_BF16;
   epi.alpha = 1.f;
   epi.bias = nullptr;
@@ -1445,6 +1463,13 @@ extern "C" int dtc_gemm_bf16_scatter(const void* A, long long lda, const void* B
   }
   epi.sp_rank = rank;
   epi.sp_rows = M / n_ranks;
+  if constexpr (SIGNAL) {
+    DTC_CHECK_ARG(sig_ptrs != nullptr && counters != nullptr, "gemm_scatter_signal: synchronisation block missing");
+    for (int i = 0; i < SP_MAX_RANKS; ++i) epi.sync.sig[i] = i < n_ranks ? reinterpret_cast<int*>(sig_ptrs[i]) : nullptr;
+    epi.sync.counters = counters;
+    epi.sync.rank = rank;
+    epi.sync.world = n_ranks;
+  }
   if (block_n == 0) {
     const long long t128 = (long long)(M / 128) * ((N + 127) / 128);
     block_n = (N <= 64 || t128 <= num_sms()) ? 64 : 128;
@@ -1452,11 +1477,31 @@ extern "C" int dtc_gemm_bf16_scatter(const void* A, long long lda, const void* B
   DTC_CHECK_ARG(block_n == 64 || block_n == 128, "gemm_scatter: block_n must be 64 or 128 (got %d)", block_n);
   if (stages == 0) stages = PG_STAGE_MAX;
   if (b_mn_major) {
-    if (block_n == 64) return launch_gemm_persistent<false, true, 64, true, true>(A, lda, B, ldb, M, N, K, 1, stages, epi, stream);
-    return launch_gemm_persistent<false, true, 128, true, true>(A, lda, B, ldb, M, N, K, 1, stages, epi, stream);
+    if (block_n == 64)
+      return launch_gemm_persistent<false, true, 64, true, true, SIGNAL>(A, lda, B, ldb, M, N, K, 1, stages, epi, stream);
+    return launch_gemm_persistent<false, true, 128, true, true, SIGNAL>(A, lda, B, ldb, M, N, K, 1, stages, epi, stream);
   }
-  if (block_n == 64) return launch_gemm_persistent<false, false, 64, true, true>(A, lda, B, ldb, M, N, K, 1, stages, epi, stream);
-  return launch_gemm_persistent<false, false, 128, true, true>(A, lda, B, ldb, M, N, K, 1, stages, epi, stream);
+  if (block_n == 64)
+    return launch_gemm_persistent<false, false, 64, true, true, SIGNAL>(A, lda, B, ldb, M, N, K, 1, stages, epi, stream);
+  return launch_gemm_persistent<false, false, 128, true, true, SIGNAL>(A, lda, B, ldb, M, N, K, 1, stages, epi, stream);
+}
+
+extern "C" int dtc_gemm_bf16_scatter(const void* A, long long lda, const void* B, long long ldb, int b_mn_major, int M, int N,
+                                     int K, const unsigned long long* peer_out, int n_ranks, int rank, long long ldo,
+                                     int stages, int block_n, cudaStream_t stream) {
+  return gemm_scatter_impl<false>(A, lda, B, ldb, b_mn_major, M, N, K, peer_out, n_ranks, rank, ldo, stages, block_n, nullptr,
+                                  nullptr, stream);
+}
+
+// Folded-barrier variant (experimental, `DTC_SP_FOLD=1`): the last CTA of the grid publishes the scattered tiles to every
+// rank (sequence number in sig[rank] on every peer) — no barrier kernel between this GEMM and dtc_sp_ln_*_sync(wait_in = 1).
+// sig_ptrs / counters: see dtc_sp_ln_fwd_sync.
+extern "C" int dtc_gemm_bf16_scatter_signal(const void* A, long long lda, const void* B, long long ldb, int b_mn_major, int M,
+                                            int N, int K, const unsigned long long* peer_out, int n_ranks, int rank,
+                                            long long ldo, int stages, int block_n, const unsigned long long* sig_ptrs,
+                                            int* counters, cudaStream_t stream) {
+  return gemm_scatter_impl<true>(A, lda, B, ldb, b_mn_major, M, N, K, peer_out, n_ranks, rank, ldo, stages, block_n, sig_ptrs,
+                                 counters, stream);
 }
 
 // Grouped weight gradients (see gemm_grouped_wgrad_kernel): for p < count

@@ -21,11 +21,11 @@
 // pass over the data: reduce-scatter = GEMM epilogue stores + the loads of this kernel, all-gather = its stores.
 // Without a multicast address (no NVLS, or the single-GPU unit test) the push is a loop of peer stores.
 #include "common.cuh"
+#include "spsync.cuh"
 
 namespace dtc {
 
 constexpr int SP_WARPS = 8;
-constexpr int SP_MAX_RANKS = 8;
 
 struct SpPeers {
   bf16* p[SP_MAX_RANKS];
@@ -53,7 +53,73 @@ DTC_DEVICE void add_bf16x8(float* acc, uint4 u) {
   }
 }
 
-// one warp per owned row; D = NCH * 256, the row lives in registers
+template <bool L2_COHERENT>
+DTC_DEVICE uint4 sp_load16(const bf16* p) {
+  // partial-sum slots written by peers while THIS kernel may already be resident must not come from a non-coherent path
+  if (L2_COHERENT) return __ldcg(reinterpret_cast<const uint4*>(p));
+  return *reinterpret_cast<const uint4*>(p);
+}
+
+// one warp per owned row; D = NCH * 256, the row lives in registers (body of the folded-barrier variant)
+template <int NCH, bool L2_COHERENT>
+DTC_DEVICE void sp_ln_fwd_row(const bf16* __restrict__ res, const bf16* __restrict__ bias, const bf16* __restrict__ part,
+                              int n_part, long long part_stride, const bf16* __restrict__ gamma,
+                              const bf16* __restrict__ beta, bf16* __restrict__ hsum, float* __restrict__ mean_out,
+                              float* __restrict__ rstd_out, bf16* mc_out, const SpPeers& peers, int n_out,
+                              long long out_row0, float eps, long long row, int lane) {
+  constexpr int D = NCH * 256;
+  float x[NCH * 8];
+  float s = 0.f, ss = 0.f;
+#pragma unroll
+  for (int k = 0; k < NCH; ++k) {
+    const int c = k * 256 + lane * 8;
+    const long long off = row * D + c;
+    float* xk = x + k * 8;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) xk[j] = 0.f;
+    add_bf16x8(xk, *reinterpret_cast<const uint4*>(res + off));
+    if (bias != nullptr) add_bf16x8(xk, *reinterpret_cast<const uint4*>(bias + c));
+    for (int p = 0; p < n_part; ++p) add_bf16x8(xk, sp_load16<L2_COHERENT>(part + p * part_stride + off));
+    // the residual stream is stored in bf16: normalise exactly what the backward pass will read back
+    const uint4 packed = make_uint4(pack_bf16x2(xk[0], xk[1]), pack_bf16x2(xk[2], xk[3]), pack_bf16x2(xk[4], xk[5]),
+                                    pack_bf16x2(xk[6], xk[7]));
+    if (hsum != nullptr) *reinterpret_cast<uint4*>(hsum + off) = packed;
+    const uint32_t w[4] = {packed.x, packed.y, packed.z, packed.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 f = unpack_bf16x2(w[j]);
+      xk[2 * j] = f.x;
+      xk[2 * j + 1] = f.y;
+      s += f.x + f.y;
+      ss += f.x * f.x + f.y * f.y;
+    }
+  }
+  s = warp_sum(s);
+  ss = warp_sum(ss);
+  const float mean = s / D;
+  const float var = fmaxf(ss / D - mean * mean, 0.f);
+  const float rstd = rsqrtf(var + eps);
+  if (lane == 0) {
+    mean_out[row] = mean;
+    rstd_out[row] = rstd;
+  }
+#pragma unroll
+  for (int k = 0; k < NCH; ++k) {
+    const int c = k * 256 + lane * 8;
+    const uint4 g = *reinterpret_cast<const uint4*>(gamma + c);
+    const uint4 b = *reinterpret_cast<const uint4*>(beta + c);
+    const uint32_t gw[4] = {g.x, g.y, g.z, g.w}, bw[4] = {b.x, b.y, b.z, b.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 gg = unpack_bf16x2(gw[j]), bb = unpack_bf16x2(bw[j]);
+      o[j] = pack_bf16x2((x[k * 8 + 2 * j] - mean) * rstd * gg.x + bb.x, (x[k * 8 + 2 * j + 1] - mean) * rstd * gg.y + bb.y);
+    }
+    sp_push16(mc_out, peers, n_out, (out_row0 + row) * D + c, make_uint4(o[0], o[1], o[2], o[3]));
+  }
+}
+
+// (validated kernel: kept verbatim, the folded-barrier variant below shares nothing with it but the math)
 template <int NCH>
 __global__ void __launch_bounds__(SP_WARPS * 32)
 sp_ln_fwd_kernel(const bf16* __restrict__ res, const bf16* __restrict__ bias, const bf16* __restrict__ part, int n_part,
@@ -114,6 +180,114 @@ sp_ln_fwd_kernel(const bf16* __restrict__ res, const bf16* __restrict__ bias, co
       o[j] = pack_bf16x2((x[k * 8 + 2 * j] - mean) * rstd * gg.x + bb.x, (x[k * 8 + 2 * j + 1] - mean) * rstd * gg.y + bb.y);
     }
     sp_push16(mc_out, peers, n_out, (out_row0 + row) * D + c, make_uint4(o[0], o[1], o[2], o[3]));
+  }
+}
+
+// Folded-barrier variant: optionally waits for the partial-sum slots of every rank in its prologue (wait_in) and
+// publishes its own pushes to every rank from its last CTA (signal_out) — no separate barrier kernels around it.
+template <int NCH>
+__global__ void __launch_bounds__(SP_WARPS * 32)
+sp_ln_fwd_sync_kernel(const bf16* __restrict__ res, const bf16* __restrict__ bias, const bf16* __restrict__ part, int n_part,
+                      long long part_stride, const bf16* __restrict__ gamma, const bf16* __restrict__ beta,
+                      bf16* __restrict__ hsum, float* __restrict__ mean_out, float* __restrict__ rstd_out, bf16* mc_out,
+                      SpPeers peers, int n_out, long long out_row0, int Ms, float eps, SpSync sync, int wait_in,
+                      int signal_out) {
+  pdl_launch_dependents();
+  pdl_wait();
+  if (wait_in) {
+    sp_wait_signals(sync, threadIdx.x);
+    __syncthreads();
+    if (threadIdx.x == 0) sp_wait_done(sync, gridDim.x);
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long row = (long long)blockIdx.x * SP_WARPS + warp;
+  if (row < Ms)
+    sp_ln_fwd_row<NCH, true>(res, bias, part, n_part, part_stride, gamma, beta, hsum, mean_out, rstd_out, mc_out, peers,
+                             n_out, out_row0, eps, row, lane);
+  if (signal_out) {
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) sp_signal(sync, gridDim.x);
+  }
+}
+
+template <int NCH, bool L2_COHERENT>
+DTC_DEVICE void sp_ln_bwd_body(const bf16* __restrict__ part, int n_part, long long part_stride, const bf16* __restrict__ x,
+                               const float* __restrict__ mean, const float* __restrict__ rstd,
+                               const bf16* __restrict__ gamma, const bf16* __restrict__ dres, float* __restrict__ dgamma,
+                               float* __restrict__ dbeta, bf16* mc_out, const SpPeers& peers, int n_out, long long out_row0,
+                               int Ms) {
+  constexpr int D = NCH * 256;
+  __shared__ float s_dg[D];
+  __shared__ float s_db[D];
+  for (int i = threadIdx.x; i < D; i += blockDim.x) {
+    s_dg[i] = 0.f;
+    s_db[i] = 0.f;
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float acc_dg[NCH * 8], acc_db[NCH * 8], gam[NCH * 8];
+#pragma unroll
+  for (int k = 0; k < NCH; ++k) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      acc_dg[k * 8 + j] = 0.f;
+      acc_db[k * 8 + j] = 0.f;
+      gam[k * 8 + j] = 0.f;
+    }
+    add_bf16x8(gam + k * 8, *reinterpret_cast<const uint4*>(gamma + k * 256 + lane * 8));
+  }
+  for (long long row = (long long)blockIdx.x * SP_WARPS + warp; row < Ms; row += (long long)gridDim.x * SP_WARPS) {
+    const float mu = mean[row], rs = rstd[row];
+    float xhat[NCH * 8], wdy[NCH * 8];
+    float c1 = 0.f, c2 = 0.f;
+#pragma unroll
+    for (int k = 0; k < NCH; ++k) {
+      const long long off = row * D + k * 256 + lane * 8;
+      float dy[8], xv[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        dy[j] = 0.f;
+        xv[j] = 0.f;
+      }
+      for (int p = 0; p < n_part; ++p) add_bf16x8(dy, sp_load16<L2_COHERENT>(part + p * part_stride + off));
+      add_bf16x8(xv, *reinterpret_cast<const uint4*>(x + off));
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int i = k * 8 + j;
+        xhat[i] = (xv[j] - mu) * rs;
+        acc_dg[i] += dy[j] * xhat[i];
+        acc_db[i] += dy[j];
+        wdy[i] = dy[j] * gam[i];
+        c1 += wdy[i];
+        c2 += wdy[i] * xhat[i];
+      }
+    }
+    c1 = warp_sum(c1) * (1.f / D);
+    c2 = warp_sum(c2) * (1.f / D);
+#pragma unroll
+    for (int k = 0; k < NCH; ++k) {
+      const long long off = row * D + k * 256 + lane * 8;
+      float r[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) r[j] = rs * (wdy[k * 8 + j] - c1 - xhat[k * 8 + j] * c2);
+      if (dres != nullptr) add_bf16x8(r, *reinterpret_cast<const uint4*>(dres + off));
+      sp_push16(mc_out, peers, n_out, (out_row0 + row) * D + k * 256 + lane * 8,
+                make_uint4(pack_bf16x2(r[0], r[1]), pack_bf16x2(r[2], r[3]), pack_bf16x2(r[4], r[5]), pack_bf16x2(r[6], r[7])));
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < NCH; ++k) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      atomicAdd(&s_dg[k * 256 + lane * 8 + j], acc_dg[k * 8 + j]);
+      atomicAdd(&s_db[k * 256 + lane * 8 + j], acc_db[k * 8 + j]);
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < D; i += blockDim.x) {
+    atomicAdd(&dgamma[i], s_dg[i]);
+    atomicAdd(&dbeta[i], s_db[i]);
   }
 }
 
@@ -197,6 +371,50 @@ sp_ln_bwd_kernel(const bf16* __restrict__ part, int n_part, long long part_strid
     atomicAdd(&dgamma[i], s_dg[i]);
     atomicAdd(&dbeta[i], s_db[i]);
   }
+}
+
+// Folded-barrier variant (see sp_ln_fwd_sync_kernel).
+template <int NCH>
+__global__ void __launch_bounds__(SP_WARPS * 32)
+sp_ln_bwd_sync_kernel(const bf16* __restrict__ part, int n_part, long long part_stride, const bf16* __restrict__ x,
+                      const float* __restrict__ mean, const float* __restrict__ rstd, const bf16* __restrict__ gamma,
+                      const bf16* __restrict__ dres, float* __restrict__ dgamma, float* __restrict__ dbeta, bf16* mc_out,
+                      SpPeers peers, int n_out, long long out_row0, int Ms, SpSync sync, int wait_in, int signal_out) {
+  pdl_launch_dependents();
+  pdl_wait();
+  if (wait_in) {
+    sp_wait_signals(sync, threadIdx.x);
+    __syncthreads();
+    if (threadIdx.x == 0) sp_wait_done(sync, gridDim.x);
+  }
+  sp_ln_bwd_body<NCH, true>(part, n_part, part_stride, x, mean, rstd, gamma, dres, dgamma, dbeta, mc_out, peers, n_out,
+                            out_row0, Ms);
+  if (signal_out) {
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) sp_signal(sync, gridDim.x);
+  }
+}
+
+// tiny consumer-side wait for kernels that cannot wait themselves (the stock GEMMs that read a gathered operand)
+__global__ void sp_wait_kernel(SpSync sync) {
+  pdl_launch_dependents();
+  pdl_wait();
+  sp_wait_signals(sync, threadIdx.x);
+  __syncthreads();
+  if (threadIdx.x == 0) sp_wait_done(sync, 1);
+}
+
+static int sp_fill_sync(SpSync* s, const unsigned long long* sig_ptrs, int* counters, int rank, int world, const char* who) {
+  if (sig_ptrs == nullptr || counters == nullptr || world < 1 || world > SP_MAX_RANKS || rank < 0 || rank >= world) {
+    dtc_set_error("%s: bad synchronisation block (world %d, rank %d)", who, world, rank);
+    return -1;
+  }
+  for (int i = 0; i < SP_MAX_RANKS; ++i) s->sig[i] = i < world ? reinterpret_cast<int*>(sig_ptrs[i]) : nullptr;
+  s->counters = counters;
+  s->rank = rank;
+  s->world = world;
+  return 0;
 }
 
 static int sp_fill_peers(SpPeers* peers, unsigned long long mc_out, const unsigned long long* peer_out, int n_out,
@@ -284,6 +502,83 @@ extern "C" int dtc_sp_ln_bwd(const void* part, int n_part, const void* x, const 
     default: dtc_set_error("sp_ln_bwd: unsupported D=%d", D); return -1;
   }
 #undef DTC_SP_BWD
+  DTC_CHECK_LAUNCH();
+  return 0;
+}
+
+// ---- folded-barrier variants (experimental; `DTC_SP_FOLD=1`) --------------------------------------------------------------
+// Same operations as dtc_sp_ln_fwd / dtc_sp_ln_bwd with the cross-rank synchronisation inside the kernel:
+//   wait_in    the prologue waits until every rank has issued the signal that publishes its partial-sum slots
+//   signal_out the last CTA publishes this kernel's pushes to every rank
+// sig_ptrs: HOST array of `world` device addresses (every rank's int[world] flag array, symmetric memory, zero-initialised);
+// counters: LOCAL int[4] device array, zero-initialised (signals issued, waits completed, two CTA ticket counters).
+extern "C" int dtc_sp_ln_fwd_sync(const void* res, const void* bias, const void* part, int n_part, const void* gamma,
+                                  const void* beta, void* hsum, float* mean, float* rstd, unsigned long long mc_out,
+                                  const unsigned long long* peer_out, int n_out, long long out_row0, int Ms, int D,
+                                  float eps, const unsigned long long* sig_ptrs, int* counters, int rank, int world,
+                                  int wait_in, int signal_out, cudaStream_t stream) {
+  DTC_CHECK_ARG(Ms > 0 && D % 256 == 0 && D >= 256 && D <= 2048, "sp_ln_fwd_sync: D=%d must be a multiple of 256, <= 2048", D);
+  DTC_CHECK_ARG(n_part >= 0 && n_part <= SP_MAX_RANKS && (n_part == 0 || part != nullptr), "sp_ln_fwd_sync: bad n_part %d", n_part);
+  DTC_CHECK_ARG(res != nullptr && out_row0 >= 0, "sp_ln_fwd_sync: residual rows missing");
+  SpPeers peers;
+  SpSync sync;
+  if (sp_fill_peers(&peers, mc_out, peer_out, n_out, "sp_ln_fwd_sync")) return -1;
+  if (sp_fill_sync(&sync, sig_ptrs, counters, rank, world, "sp_ln_fwd_sync")) return -1;
+  const int blocks = (Ms + SP_WARPS - 1) / SP_WARPS;
+  const long long stride = (long long)Ms * D;
+#define DTC_SP_FWD(NCH)                                                                                              \
+  case NCH:                                                                                                          \
+    DTC_CHECK_CUDA(dtc::launch(sp_ln_fwd_sync_kernel<NCH>, blocks, SP_WARPS * 32, 0, stream,                         \
+        reinterpret_cast<const bf16*>(res), reinterpret_cast<const bf16*>(bias), reinterpret_cast<const bf16*>(part), \
+        n_part, stride, reinterpret_cast<const bf16*>(gamma), reinterpret_cast<const bf16*>(beta),                   \
+        reinterpret_cast<bf16*>(hsum), mean, rstd, reinterpret_cast<bf16*>(mc_out), peers, n_out, out_row0, Ms, eps,  \
+        sync, wait_in, signal_out));                                                                                  \
+    break;
+  switch (D / 256) {
+    DTC_SP_FWD(1) DTC_SP_FWD(2) DTC_SP_FWD(3) DTC_SP_FWD(4) DTC_SP_FWD(5) DTC_SP_FWD(6) DTC_SP_FWD(7) DTC_SP_FWD(8)
+    default: dtc_set_error("sp_ln_fwd_sync: unsupported D=%d", D); return -1;
+  }
+#undef DTC_SP_FWD
+  DTC_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int dtc_sp_ln_bwd_sync(const void* part, int n_part, const void* x, const float* mean, const float* rstd,
+                                  const void* gamma, const void* dres, float* dgamma, float* dbeta,
+                                  unsigned long long mc_out, const unsigned long long* peer_out, int n_out,
+                                  long long out_row0, int Ms, int D, const unsigned long long* sig_ptrs, int* counters,
+                                  int rank, int world, int wait_in, int signal_out, cudaStream_t stream) {
+  DTC_CHECK_ARG(Ms > 0 && D % 256 == 0 && D >= 256 && D <= 2048, "sp_ln_bwd_sync: D=%d must be a multiple of 256, <= 2048", D);
+  DTC_CHECK_ARG(n_part >= 1 && n_part <= SP_MAX_RANKS && part != nullptr, "sp_ln_bwd_sync: bad n_part %d", n_part);
+  SpPeers peers;
+  SpSync sync;
+  if (sp_fill_peers(&peers, mc_out, peer_out, n_out, "sp_ln_bwd_sync")) return -1;
+  if (sp_fill_sync(&sync, sig_ptrs, counters, rank, world, "sp_ln_bwd_sync")) return -1;
+  int blocks = (Ms + SP_WARPS - 1) / SP_WARPS;
+  if (blocks > 148 * 2) blocks = 148 * 2;
+  const long long stride = (long long)Ms * D;
+#define DTC_SP_BWD(NCH)                                                                                             \
+  case NCH:                                                                                                         \
+    DTC_CHECK_CUDA(dtc::launch(sp_ln_bwd_sync_kernel<NCH>, blocks, SP_WARPS * 32, 0, stream,                        \
+        reinterpret_cast<const bf16*>(part), n_part, stride, reinterpret_cast<const bf16*>(x), mean, rstd,          \
+        reinterpret_cast<const bf16*>(gamma), reinterpret_cast<const bf16*>(dres), dgamma, dbeta,                   \
+        reinterpret_cast<bf16*>(mc_out), peers, n_out, out_row0, Ms, sync, wait_in, signal_out));                   \
+    break;
+  switch (D / 256) {
+    DTC_SP_BWD(1) DTC_SP_BWD(2) DTC_SP_BWD(3) DTC_SP_BWD(4) DTC_SP_BWD(5) DTC_SP_BWD(6) DTC_SP_BWD(7) DTC_SP_BWD(8)
+    default: dtc_set_error("sp_ln_bwd_sync: unsupported D=%d", D); return -1;
+  }
+#undef DTC_SP_BWD
+  DTC_CHECK_LAUNCH();
+  return 0;
+}
+
+// Waits (one tiny CTA, local polling only) until every rank has issued its next signal: in front of a stock GEMM that
+// reads an operand gathered by dtc_sp_ln_*_sync(signal_out = 1).
+extern "C" int dtc_sp_wait(const unsigned long long* sig_ptrs, int* counters, int rank, int world, cudaStream_t stream) {
+  SpSync sync;
+  if (sp_fill_sync(&sync, sig_ptrs, counters, rank, world, "sp_wait")) return -1;
+  DTC_CHECK_CUDA(dtc::launch(sp_wait_kernel, 1, 32, 0, stream, sync));
   DTC_CHECK_LAUNCH();
   return 0;
 }

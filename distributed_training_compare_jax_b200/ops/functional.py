@@ -86,6 +86,40 @@ def gemm_scatter(a: torch.Tensor, b: torch.Tensor, peer_ptrs, n_ranks: int, rank
                 stages, block_n)
 
 
+def gemm_scatter_signal(a: torch.Tensor, b: torch.Tensor, peer_ptrs, n_ranks: int, rank: int, ldo: int, sig_ptrs, counters,
+                        *, b_mn: bool = False, stages: int = 0, block_n: int = 0) -> None:
+    """:func:`gemm_scatter` whose last CTA also publishes the tiles to every rank (folded barrier, experimental)."""
+    _check_rowmajor(a, "a")
+    _check_rowmajor(b, "b")
+    M, K = a.shape
+    Kb, N = (b.shape[0], b.shape[1]) if b_mn else (b.shape[1], b.shape[0])
+    if K != Kb:
+        raise ValueError(f"gemm_scatter: reduction dims differ ({K} vs {Kb})")
+    native.call("dtc_gemm_bf16_scatter_signal", a, a.stride(0), b, b.stride(0), int(b_mn), M, N, K, peer_ptrs, n_ranks, rank,
+                ldo, stages, block_n, sig_ptrs, counters)
+
+
+def sp_ln_fwd_sync(res, bias, part, n_part: int, gamma, beta, hsum, mean, rstd, mc_out: int, peer_ptrs, n_out: int,
+                   out_row0: int, eps: float, sig_ptrs, counters, rank: int, world: int, wait_in: bool,
+                   signal_out: bool) -> None:
+    """:func:`sp_ln_fwd` with the cross-rank waits / signals inside the kernel (folded barrier, experimental)."""
+    Ms, D = res.shape
+    native.call("dtc_sp_ln_fwd_sync", res, bias, part, n_part, gamma, beta, hsum, mean, rstd, mc_out, peer_ptrs, n_out,
+                out_row0, Ms, D, float(eps), sig_ptrs, counters, rank, world, int(wait_in), int(signal_out))
+
+
+def sp_ln_bwd_sync(part, n_part: int, x, mean, rstd, gamma, dres, dgamma, dbeta, mc_out: int, peer_ptrs, n_out: int,
+                   out_row0: int, sig_ptrs, counters, rank: int, world: int, wait_in: bool, signal_out: bool) -> None:
+    Ms, D = x.shape
+    native.call("dtc_sp_ln_bwd_sync", part, n_part, x, mean, rstd, gamma, dres, dgamma, dbeta, mc_out, peer_ptrs, n_out,
+                out_row0, Ms, D, sig_ptrs, counters, rank, world, int(wait_in), int(signal_out))
+
+
+def sp_wait(sig_ptrs, counters, rank: int, world: int) -> None:
+    """One tiny CTA that waits for the next signal of every rank (in front of a stock GEMM reading a gathered operand)."""
+    native.call("dtc_sp_wait", sig_ptrs, counters, rank, world)
+
+
 def sp_ln_fwd(res, bias, part, n_part: int, gamma, beta, hsum, mean, rstd, mc_out: int, peer_ptrs, n_out: int,
               out_row0: int, eps: float = 1e-6) -> None:
     """Owned rows: hsum = res + bias + Σ part[p]; LayerNorm(hsum) pushed to rows [out_row0, out_row0+Ms) of every rank's

@@ -47,6 +47,10 @@ _PROTOS: dict[str, list[Any]] = {
     "dtc_colsum_grouped": [I, P, P, P, P, P],
     "dtc_sp_ln_fwd": [P, P, P, I, P, P, P, P, P, U64, P, I, L, I, I, F],
     "dtc_sp_ln_bwd": [P, I, P, P, P, P, P, P, P, U64, P, I, L, I, I],
+    "dtc_gemm_bf16_scatter_signal": [P, L, P, L, I, I, I, I, P, I, I, L, I, I, P, P],
+    "dtc_sp_ln_fwd_sync": [P, P, P, I, P, P, P, P, P, U64, P, I, L, I, I, F, P, P, I, I, I, I],
+    "dtc_sp_ln_bwd_sync": [P, I, P, P, P, P, P, P, P, U64, P, I, L, I, I, P, P, I, I, I, I],
+    "dtc_sp_wait": [P, P, I, I],
     "dtc_dp_reduce_scatter": [P, U64, P, I, I, L, L, P],
     "dtc_dp_norm_exchange": [P, I, P, P, I, I, I, F, P, P],
     "dtc_dp_adamw_allgather": [P, P, P, P, U64, P, I, L, L, L, P, P, F, F, F, F, F],

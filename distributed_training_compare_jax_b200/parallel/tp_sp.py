@@ -51,7 +51,7 @@ class _LocalArena:
 class SeqParallelState:
     """Buffers and cross-rank plumbing of the sequence-parallel path for one microbatch of M = B·T rows."""
 
-    def __init__(self, engine, mesh, use_multicast: bool = True):
+    def __init__(self, engine, mesh, use_multicast: bool = True, fold_barriers: bool = False):
         tp = mesh.tp
         cfg, local = engine.cfg, engine.local
         self.n, self.rank = tp.size, tp.rank
@@ -89,6 +89,18 @@ class SeqParallelState:
         self.mean2, self.rstd2 = e(L, Ms, dtype=F32), e(L, Ms, dtype=F32)
         self.meanf, self.rstdf = e(Ms, dtype=F32), e(Ms, dtype=F32)
         self.part_ptrs = self._peer_array(self.part)
+        # Experimental (DTC_SP_FOLD=1, not yet run on hardware): no barrier kernels between producers and consumers — the
+        # last CTA of a scatter GEMM / LayerNorm kernel publishes a sequence number to every rank, the LayerNorm kernels wait
+        # in their prologue and a one-CTA wait kernel sits in front of the stock GEMMs that read a gathered operand.
+        self.fold = bool(fold_barriers)
+        if self.fold:
+            if n > 1:
+                self.sig = SymmBuffer(16, torch.int32, dev, tp.group)
+                self.sig_ptrs = self.sig.ptr_array
+            else:
+                self.sig = torch.zeros(16, device=dev, dtype=torch.int32)
+                self.sig_ptrs = (C.c_ulonglong * 1)(self.sig.data_ptr())
+            self.counters = torch.zeros(4, device=dev, dtype=torch.int32)
 
     # ---- addressing ----
     def _offset_bytes(self, view: torch.Tensor) -> int:
@@ -114,17 +126,40 @@ class SeqParallelState:
             self.barrier_flags(self._slot)
             self._slot = (self._slot + 1) % FlagBarrier.N_SLOTS
 
+    def scattered(self) -> None:
+        """After a scatter GEMM, before the kernel that reduces the partial-sum slots."""
+        if not self.fold:
+            self.barrier()          # folded mode: the GEMM signals, the LayerNorm kernel waits in its prologue
+
+    def pushed(self) -> None:
+        """After a LayerNorm kernel pushed its rows to every rank, before the GEMMs that read the gathered buffer."""
+        if self.fold:
+            Fn.sp_wait(self.sig_ptrs, self.counters, self.rank, self.n)
+        else:
+            self.barrier()
+
     def gemm_scatter(self, a: torch.Tensor, w: torch.Tensor, b_mn: bool) -> None:
-        Fn.gemm_scatter(a, w, self.part_ptrs, self.n, self.rank, self.D, b_mn=b_mn)
+        if self.fold:
+            Fn.gemm_scatter_signal(a, w, self.part_ptrs, self.n, self.rank, self.D, self.sig_ptrs, self.counters, b_mn=b_mn)
+        else:
+            Fn.gemm_scatter(a, w, self.part_ptrs, self.n, self.rank, self.D, b_mn=b_mn)
 
     def ln_fwd(self, res, bias, reduce: bool, gamma, beta, hsum, mean, rstd, out, eps: float) -> None:
         mc, peers, n = self.dest(out)
-        Fn.sp_ln_fwd(res, bias, self.part if reduce else None, self.n if reduce else 0, gamma, beta, hsum, mean, rstd, mc,
-                     peers, n, self.row0, eps)
+        part, n_part = (self.part, self.n) if reduce else (None, 0)
+        if self.fold:
+            Fn.sp_ln_fwd_sync(res, bias, part, n_part, gamma, beta, hsum, mean, rstd, mc, peers, n, self.row0, eps,
+                              self.sig_ptrs, self.counters, self.rank, self.n, wait_in=reduce, signal_out=True)
+        else:
+            Fn.sp_ln_fwd(res, bias, part, n_part, gamma, beta, hsum, mean, rstd, mc, peers, n, self.row0, eps)
 
     def ln_bwd(self, x, mean, rstd, gamma, dres, dgamma, dbeta, out) -> None:
         mc, peers, n = self.dest(out)
-        Fn.sp_ln_bwd(self.part, self.n, x, mean, rstd, gamma, dres, dgamma, dbeta, mc, peers, n, self.row0)
+        if self.fold:
+            Fn.sp_ln_bwd_sync(self.part, self.n, x, mean, rstd, gamma, dres, dgamma, dbeta, mc, peers, n, self.row0,
+                              self.sig_ptrs, self.counters, self.rank, self.n, wait_in=True, signal_out=True)
+        else:
+            Fn.sp_ln_bwd(self.part, self.n, x, mean, rstd, gamma, dres, dgamma, dbeta, mc, peers, n, self.row0)
 
     def own(self, full: torch.Tensor) -> torch.Tensor:
         return full[self.row0:self.row0 + self.Ms]
@@ -137,8 +172,10 @@ class SeqParallelEngine(NativeStageEngine):
 
     defer_grad_reduction = True   # parallel/dp.py: all-reduce the DP gradient after backward, not bucket by bucket
 
-    def __init__(self, *a, use_multicast: bool = True, **kw):
+    def __init__(self, *a, use_multicast: bool = True, fold_barriers: bool | None = None, **kw):
         super().__init__(*a, **kw)
+        if fold_barriers is None:
+            fold_barriers = __import__("os").environ.get("DTC_SP_FOLD") == "1"
         if not (self.local.has_embed and self.local.has_head) or self.n_micro != 1 or self.local.L < 1:
             raise ValueError("sequence-parallel TP runs the whole model on one stage with one microbatch")
         ws = self.ws[0]
@@ -146,7 +183,7 @@ class SeqParallelEngine(NativeStageEngine):
                      "meanf", "rstdf"):
             if hasattr(ws, name):
                 delattr(ws, name)   # replaced by the row-sharded / gathered buffers of SeqParallelState
-        self.sp = SeqParallelState(self, self.mesh, use_multicast)
+        self.sp = SeqParallelState(self, self.mesh, use_multicast, fold_barriers)
         st = self.store
         self._partial_grads = st.flat_grad[st.offsets["ln1_g"][0]:st.rep_numel]   # ln1_g ln1_b bo ln2_g ln2_b b2 lnf_g lnf_b
 
@@ -169,21 +206,21 @@ class SeqParallelEngine(NativeStageEngine):
             else:   # h[l] = hmid[l-1] + b2 + Σ fc2 partials
                 sp.ln_fwd(sp.hmids[l - 1], c["b2"][l - 1], True, c["ln1_g"][l], c["ln1_b"][l], sp.hs[l], sp.mean1[l],
                           sp.rstd1[l], sp.xg1[l], eps)
-            sp.barrier()
+            sp.pushed()
             Fn.gemm(sp.xg1[l], c["wqkv"][l], b_mn=True, bias=c["bqkv"][l], out=ws.qkv[l])
             Fn.flash_attn_fwd(ws.qkv[l], ws.B, Hl, ws.T, hd, out=ws.attn[l], lse2=ws.lse2[l])
             sp.gemm_scatter(ws.attn[l], c["wo"][l], b_mn=True)
-            sp.barrier()
+            sp.scattered()
             # hmid[l] = h[l] + bo + Σ out_proj partials
             sp.ln_fwd(sp.hs[l], c["bo"][l], True, c["ln2_g"][l], c["ln2_b"][l], sp.hmids[l], sp.mean2[l], sp.rstd2[l],
                       sp.xg2[l], eps)
-            sp.barrier()
+            sp.pushed()
             Fn.gemm(sp.xg2[l], c["w1"][l], b_mn=True, bias=c["b1"][l], epi="bias_gelu", out=ws.f1[l], out2=ws.g[l])
             sp.gemm_scatter(ws.g[l], c["w2"][l], b_mn=True)
-            sp.barrier()
+            sp.scattered()
         # ---- head: final LayerNorm (gathered) → vocab-parallel lm_head → softmax-CE and its gradient
         sp.ln_fwd(sp.hmids[L - 1], c["b2"][L - 1], True, c["lnf_g"], c["lnf_b"], sp.hs[L], sp.meanf, sp.rstdf, sp.xgf, eps)
-        sp.barrier()
+        sp.pushed()
         nv, gscale = lo.vocab_valid, 1.0 / self.global_tokens
         Fn.gemm(sp.xgf, c["wlm"], b_mn=True, bias=c["blm"], out=ws.logits)
         if n == 1:
@@ -200,9 +237,9 @@ class SeqParallelEngine(NativeStageEngine):
 
         self.side_work(head_param_grads)
         sp.gemm_scatter(ws.logits, c["wlm"], b_mn=False)
-        sp.barrier()
+        sp.scattered()
         sp.ln_bwd(sp.hs[L], sp.meanf, sp.rstdf, c["lnf_g"], None, g["lnf_g"], g["lnf_b"], sp.dA)
-        sp.barrier()
+        sp.pushed()
         Fn.reduce_sum(ws.loss_rows, gscale, self.loss_sum, accumulate=True)
         self.side_join()
         return None
@@ -235,9 +272,9 @@ class SeqParallelEngine(NativeStageEngine):
                 Fn.gemm(cur, c["w2"][l], epi="dgelu", aux=ws.f1[l], out=ws.df1)
                 self.side_work(fc1_param_grads)
                 sp.gemm_scatter(ws.df1, c["w1"][l], b_mn=False)
-                sp.barrier()
+                sp.scattered()
                 sp.ln_bwd(sp.hmids[l], sp.mean2[l], sp.rstd2[l], c["ln2_g"][l], cur_own, g["ln2_g"][l], g["ln2_b"][l], sp.dMID)
-                sp.barrier()
+                sp.pushed()
 
                 # ---- attention
                 mid_own = sp.own(sp.dMID)
@@ -256,9 +293,9 @@ class SeqParallelEngine(NativeStageEngine):
                                   dq_accum=ws.dq_accum, delta=ws.delta)
                 self.side_work(qkv_param_grads)
                 sp.gemm_scatter(ws.dqkv, c["wqkv"][l], b_mn=False)
-                sp.barrier()
+                sp.scattered()
                 sp.ln_bwd(sp.hs[l], sp.mean1[l], sp.rstd1[l], c["ln1_g"][l], mid_own, g["ln1_g"][l], g["ln1_b"][l], other)
-                sp.barrier()
+                sp.pushed()
                 cur, other = other, cur
         self.side_join()
         # dL/dh[0] is complete on every rank: the embedding tables are replicated, every rank scatters all rows

@@ -150,6 +150,24 @@ int dtc_gemm_wgrad_grouped(int count, const unsigned long long* A, const long lo
                            const long long* ldo, float alpha, int splits, int stages, cudaStream_t stream);
 int dtc_colsum_grouped(int count, const unsigned long long* x, const long long* ld, const int* M, const int* N,
                        const unsigned long long* out, cudaStream_t stream);
+/* folded-barrier variants (experimental, `DTC_SP_FOLD=1`): same operations with the cross-rank synchronisation inside the
+ * kernels.  sig_ptrs: HOST array of `world` device addresses of every rank's int[world] flag array (symmetric memory, zeroed);
+ * counters: LOCAL zeroed int[4].  wait_in: wait in the prologue for the signal that publishes the partial-sum slots;
+ * signal_out: the last CTA publishes this kernel's remote stores; dtc_sp_wait: one-CTA wait in front of a stock GEMM. */
+int dtc_gemm_bf16_scatter_signal(const void* A, long long lda, const void* B, long long ldb, int b_mn_major, int M, int N,
+                                 int K, const unsigned long long* peer_out, int n_ranks, int rank, long long ldo,
+                                 int stages, int block_n, const unsigned long long* sig_ptrs, int* counters,
+                                 cudaStream_t stream);
+int dtc_sp_ln_fwd_sync(const void* res, const void* bias, const void* part, int n_part, const void* gamma, const void* beta,
+                       void* hsum, float* mean, float* rstd, unsigned long long mc_out, const unsigned long long* peer_out,
+                       int n_out, long long out_row0, int Ms, int D, float eps, const unsigned long long* sig_ptrs,
+                       int* counters, int rank, int world, int wait_in, int signal_out, cudaStream_t stream);
+int dtc_sp_ln_bwd_sync(const void* part, int n_part, const void* x, const float* mean, const float* rstd, const void* gamma,
+                       const void* dres, float* dgamma, float* dbeta, unsigned long long mc_out,
+                       const unsigned long long* peer_out, int n_out, long long out_row0, int Ms, int D,
+                       const unsigned long long* sig_ptrs, int* counters, int rank, int world, int wait_in, int signal_out,
+                       cudaStream_t stream);
+int dtc_sp_wait(const unsigned long long* sig_ptrs, int* counters, int rank, int world, cudaStream_t stream);
 int dtc_gemm_set_dual(int bits);   /* tuning: bit0 two-CTAs-per-SM GEMM, bit1 64-wide tiles for small grids, bit2 coop stores */
 
 #ifdef __cplusplus

@@ -94,3 +94,12 @@ def test_pp2_cuda_graph_per_action(single, tmp_path, schedule):
     loss = _run(tmp_path, f"pp2_graph_{schedule}", "pp", 2, pp_microbatches=2, pp_init="shared", pp_clip="global",
                 pp_schedule=schedule, pp_cuda_graph=True)
     np.testing.assert_allclose(loss, single, rtol=5e-3, atol=5e-3)
+
+
+@pytest.mark.skipif(NGPU < 2 or os.environ.get("DTC_EXPERIMENTAL") != "1",
+                    reason="needs >= 2 GPUs; unvalidated: set DTC_EXPERIMENTAL=1")
+def test_tp2_sequence_parallel_folded_barriers(single, tmp_path, monkeypatch):
+    """DTC_SP_FOLD=1: signals from the last CTA of the producers, waits inside the LayerNorm kernels (parallel/tp_sp.py)."""
+    monkeypatch.setenv("DTC_SP_FOLD", "1")
+    loss = _run(tmp_path, "tp2_sp_fold", "tp", 2, tp_seq_parallel=True)
+    np.testing.assert_allclose(loss, single, rtol=5e-3, atol=5e-3)

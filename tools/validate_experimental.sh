@@ -14,16 +14,18 @@ if [ "$N" = "1" ]; then
   DTC_WGRAD_GROUPED=1 run dp1_wgrad_grouped python bench.py --steps 30 --warmup 5
 fi
 if [ "$N" = "2" ]; then
-  DTC_EXPERIMENTAL=1 timeout 300 python -m pytest tests/test_multigpu.py -q -x -k "sequence_parallel or cuda_graph_per_action or tp2" 2>&1 | tail -15 | tee gpurun_out/x_multigpu_tests.log
+  DTC_EXPERIMENTAL=1 timeout 300 python -m pytest tests/test_multigpu.py -q -x -k "sequence_parallel or cuda_graph_per_action or tp2 or folded" 2>&1 | tail -15 | tee gpurun_out/x_multigpu_tests.log
   run pp2_eager python bench.py --gpus 2 --parallel pp --steps 30 --warmup 5
   run pp2_graph python bench.py --gpus 2 --parallel pp --steps 30 --warmup 5 --pp-graph
   run tp2_seqpar python bench.py --gpus 2 --parallel tp --steps 30 --warmup 5
   run tp2_nccl python bench.py --gpus 2 --parallel tp --steps 30 --warmup 5 --no-tp-seq-parallel
+  DTC_SP_FOLD=1 run tp2_seqpar_fold python bench.py --gpus 2 --parallel tp --steps 30 --warmup 5
   DTC_WGRAD_GROUPED=1 run dp2_wgrad_grouped python bench.py --gpus 2 --steps 30 --warmup 5
 fi
 if [ "$N" -ge 4 ]; then
   run tp${N}_seqpar python bench.py --gpus $N --parallel tp --steps 30 --warmup 5
   run tp${N}_nccl python bench.py --gpus $N --parallel tp --steps 30 --warmup 5 --no-tp-seq-parallel
+  DTC_SP_FOLD=1 run tp${N}_seqpar_fold python bench.py --gpus $N --parallel tp --steps 30 --warmup 5
   run pp${N}_eager python bench.py --gpus $N --parallel pp --steps 30 --warmup 5
   run pp${N}_graph python bench.py --gpus $N --parallel pp --steps 30 --warmup 5 --pp-graph
   if [ "$N" = "8" ]; then
