@@ -92,8 +92,8 @@ class NativeStageEngine(StageEngineBase):
     def __init__(self, *a, wgrad_splits: int = 0, overlap_wgrad: bool = True, wgrad_grouped: bool = False, **kw):
         super().__init__(*a, **kw)
         # Weight-gradient work (wgrad GEMMs + bias column sums) does not feed the backward chain: it runs on a side
-        # stream concurrently with the dgrad / attention / LayerNorm chain.  Both streams then use the light GEMM
-        # kernel (98 KB smem, 128 TMEM columns) so that two GEMM CTAs fit on one SM.
+        # stream concurrently with the dgrad / attention / LayerNorm chain.  Both streams use the light (two CTAs per SM)
+        # configuration of the persistent GEMM, so a CTA of each stream fits on one SM.
         self.overlap_wgrad = overlap_wgrad
         self.bwd_gemm_impl = int(__import__('os').environ.get('DTC_BWD_GEMM_IMPL', '0'))
         # experimental (not yet measured on B200): one grouped wgrad launch + one grouped bias-grad launch per layer
