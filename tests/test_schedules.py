@@ -129,3 +129,18 @@ def test_executor_moves_data_without_deadlock(kind, S, M):
         assert torch.all(engines[0].final[mb] == 10 * S)          # and S backwards
     for e in execs:
         assert len(e.trace) == 2 * M
+
+
+def test_per_action_cuda_graphs_are_only_used_with_the_native_engine():
+    # the option is a no-op for the torch / fake engines: the executor keeps calling forward / backward directly
+    net = _FakeNet()
+    engines = [_FakeEngine(s, 2, 2) for s in range(2)]
+    execs = [PipelineExecutor(engines[s], Axis("pp", 2, s, None, [0, 1]), "gpipe", p2p=_FakeP2P(net, s), cuda_graph=True)
+             for s in range(2)]
+    assert not any(e.cuda_graph for e in execs)
+    for _ in range(4):      # past the eager warm-up steps: still no capture
+        ts = [threading.Thread(target=e.run) for e in execs]
+        [t.start() for t in ts]
+        [t.join(30) for t in ts]
+    assert all(not e.graphs and e.steps_run == 4 for e in execs)
+    assert torch.equal(engines[1].final[0], torch.full((2,), 2.0))
