@@ -142,11 +142,15 @@ def single_device_mesh(device: torch.device | str | None = None) -> DeviceMesh:
     return DeviceMesh(1, 0, torch.device(device), Axis("dp"), Axis("tp"), Axis("pp"))
 
 
-def shutdown(hard_exit_after_s: float | None = None) -> None:
+def shutdown(hard_exit_after_s: float | None = None, abort: bool = False) -> None:
     """Tear the process groups down.  CUDA graphs that captured NCCL work must be released first (drop the
     train-step / engine objects before calling this); with ``hard_exit_after_s`` a teardown that does not finish
-    in time ends the process with ``os._exit(0)`` instead of hanging the job."""
+    in time ends the process with ``os._exit(0)`` instead of hanging the job.  ``abort``: this rank is leaving because
+    of an error — no barrier, no collective teardown (the peers are not going to join it): the launcher sees the
+    failing process exit and tears the other ranks down."""
     if not (dist.is_available() and dist.is_initialized()):
+        return
+    if abort:
         return
 
     def _destroy():

@@ -23,6 +23,8 @@ from dataclasses import dataclass
 import torch
 import torch.distributed as dist
 
+from ..utils.timing import nvtx_range
+
 
 @dataclass(frozen=True)
 class Action:
@@ -165,11 +167,13 @@ class PipelineExecutor:
                 self.p2p.recv(eng.grad_input_buffer(a.mb), self.stage + 1)
             self.trace.append((a.kind, a.mb))
             if a.kind == "F":
-                out = self._do("F", a.mb)
+                with nvtx_range(f"F{a.mb}"):
+                    out = self._do("F", a.mb)
                 if not last:
                     self.p2p.send(out, self.stage + 1)
             else:
-                gin = self._do("B", a.mb)
+                with nvtx_range(f"B{a.mb}"):
+                    gin = self._do("B", a.mb)
                 if not first:
                     self.p2p.send(gin.contiguous(), self.stage - 1)
         self.p2p.flush()

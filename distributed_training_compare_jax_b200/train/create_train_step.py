@@ -21,6 +21,7 @@ import torch
 
 from ..ops import native
 from ..parallel.pp import PipelineExecutor
+from ..utils.timing import nvtx_range
 
 
 @dataclass(frozen=True)
@@ -125,8 +126,10 @@ def create_train_step(parallel: str = "dp", cuda_graph: bool = True) -> Any:
         def body():
             eng.begin_step()
             if n == 1:
-                eng.forward(0)
-                eng.backward(0)
+                with nvtx_range("forward"):
+                    eng.forward(0)
+                with nvtx_range("backward"):
+                    eng.backward(0)
             else:
                 main = torch.cuda.current_stream()
                 if "chains" not in cache:
@@ -138,7 +141,8 @@ def create_train_step(parallel: str = "dp", cuda_graph: bool = True) -> Any:
                         eng.backward(m)
                 for st in cache["chains"]:
                     main.wait_stream(st)
-            opt.step()
+            with nvtx_range("optimizer"):
+                opt.step()
             mesh.dp.all_reduce(eng.loss_sum)  # mean over the GLOBAL batch (reference: loss.mean() over P("data"))
 
         if id(eng) not in graphed:

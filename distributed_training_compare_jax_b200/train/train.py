@@ -103,7 +103,11 @@ def _run_loop(train_config: TrainConfig, model_config: ModelConfig, state: Train
     timer.start()
     log.start_timing()
     pending: list[tuple[int, torch.Tensor]] = []
+    fault = os.environ.get("DTC_FAULT", "")     # fault injection for the failure-handling tests: "<rank>:<step>"
+    fault_rank, fault_step = (int(v) for v in fault.split(":")) if fault else (-1, -1)
     for step in range(1, train_config.steps + 1):
+        if step == fault_step and mesh.rank == fault_rank:
+            raise RuntimeError(f"injected fault on rank {mesh.rank} at step {step} (DTC_FAULT)")
         state, loss = train_step(state, next_batch(), None)
         if train_config.sync_every_step:
             log.record(step, float(loss))          # blocking D2H like the reference (train/train.py:82-83)

@@ -5,6 +5,7 @@
 throttle reasons, as required for every reported number; ``l2_flush`` writes a buffer larger than the 126 MB L2."""
 from __future__ import annotations
 
+import os
 import statistics
 import subprocess
 import threading
@@ -100,3 +101,23 @@ class ClockSampler:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
         return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons),
                 "samples": len(sm)}
+
+
+class nvtx_range:
+    """``with nvtx_range("forward"):`` — NVTX range around a phase of the step when ``DTC_NVTX=1`` (visible in ncu / nsys
+    timelines; the reference has no tracing at all).  A no-op otherwise and on CPU."""
+    enabled = os.environ.get("DTC_NVTX") == "1"
+
+    def __init__(self, name: str):
+        self.name = name
+        self.on = nvtx_range.enabled and torch.cuda.is_available()
+
+    def __enter__(self):
+        if self.on:
+            torch.cuda.nvtx.range_push(self.name)
+        return self
+
+    def __exit__(self, *exc):
+        if self.on:
+            torch.cuda.nvtx.range_pop()
+        return False

@@ -49,6 +49,7 @@ def run(train_config_path: str, model_config_path: str, optim_config_path: str, 
     num_devices = int(os.environ.get("WORLD_SIZE", "1"))
     if int(os.environ.get("RANK", "0")) == 0:
         print(f"Running `{parallel_strategy}` on {num_devices} devices.", flush=True)
+    failed = False
     try:
         if parallel_strategy == "pp":
             return train_pp(train_config=train_config, model_config=model_config, opt_config=opt_config,
@@ -58,8 +59,11 @@ def run(train_config_path: str, model_config_path: str, optim_config_path: str, 
                                parallel_strategy=parallel_strategy, num_devices=num_devices)
         else:
             raise ValueError(f"Unsupported strategy `{parallel_strategy}`")
+    except BaseException:
+        failed = True      # leave without the collective teardown: the other ranks are not going to take part in it
+        raise
     finally:
-        shutdown()
+        shutdown(abort=failed)
 
 
 def _worker(rank: int, world: int, port: int, args: tuple) -> None:

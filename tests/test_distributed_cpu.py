@@ -101,3 +101,24 @@ def test_metrics_json_and_plot_summary(single, tmp_path):
     for png in ("loss.png", "average_elapsed_time.png"):          # the reference's two figures (plot.py:25,38)
         data = open(tmp_path / png, "rb").read()
         assert data[:8] == b"\x89PNG\r\n\x1a\n" and len(data) > 500
+
+
+def test_a_failing_rank_takes_the_job_down_quickly(tmp_path):
+    """Failure handling: one rank raises in the middle of training; the launcher must tear the other rank
+    down and exit non-zero well before any collective timeout instead of hanging."""
+    import time
+    import yaml
+    (tmp_path / "m.yaml").write_text(yaml.safe_dump(MODEL))
+    train = {"batch": 4, "log_every": 4, "output_dir": str(tmp_path / "out"), "parallel": "dp", "seed": 0, "steps": 8,
+             "warmup_steps": 1, "backend": "torch"}
+    (tmp_path / "t.yaml").write_text(yaml.safe_dump(train))
+    env = dict(os.environ, OMP_NUM_THREADS="1", MASTER_PORT=str(_free_port()), CUDA_VISIBLE_DEVICES="", DTC_FAULT="1:3",
+               DTC_DIST_TIMEOUT="300")
+    cmd = [sys.executable, os.path.join(ROOT, "main.py"), "--train_config_path", str(tmp_path / "t.yaml"),
+           "--model_config_path", str(tmp_path / "m.yaml"), "--optim_config_path",
+           os.path.join(ROOT, "configs", "optim_config.yaml"), "--num_devices", "2"]
+    t0 = time.time()
+    r = subprocess.run(cmd, cwd=ROOT, env=env, capture_output=True, text=True, timeout=280)
+    assert r.returncode != 0
+    assert "injected fault on rank 1 at step 3" in r.stderr
+    assert time.time() - t0 < 200, "the surviving rank was not torn down: the job waited for the collective timeout"
