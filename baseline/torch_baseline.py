@@ -4,7 +4,10 @@ torch.optim.AdamW, clip_grad_norm_, NCCL all-reduce through DistributedDataParal
 master weights.  It shares NO code with the product path (none of this repo's kernels, engine or models) and
 exists only to be measured on the same box, because the reference's own JAX build cannot be installed offline.
 
-    python baseline/torch_baseline.py [--steps 50] [--warmup 5] [--compile-off]
+    python baseline/torch_baseline.py [--steps 50] [--warmup 5] [--graph]
+``--graph`` (single GPU): the whole step — forward, backward, clip, fused AdamW — is captured into one CUDA graph and
+replayed, which removes the host launch overhead that bounds the eager variant on this box; it is the fairer bar for the
+kernels (same library kernels, no launch gaps), the eager number is the fairer bar for an out-of-the-box framework.
     torchrun --nproc-per-node N baseline/torch_baseline.py     (data parallel, batch 8 per rank)
 Prints one JSON line with device-timed (CUDA events, max over ranks) tokens/s.
 """
@@ -54,6 +57,7 @@ def main():
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--batch", type=int, default=8)
+    ap.add_argument("--graph", action="store_true", help="capture the whole training step into one CUDA graph (1 GPU)")
     args = ap.parse_args()
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     local_rank = int(os.environ.get("LOCAL_RANK", 0))
@@ -64,11 +68,26 @@ def main():
     torch.manual_seed(0)
     model = GPT().to(dev)
     net = nn.parallel.DistributedDataParallel(model, device_ids=[dev.index]) if world > 1 else model
-    opt = torch.optim.AdamW(model.parameters(), lr=3e-4, weight_decay=0.1, eps=1e-8, fused=True)
+    use_graph = args.graph and world == 1
+    opt = torch.optim.AdamW(model.parameters(), lr=3e-4, weight_decay=0.1, eps=1e-8, fused=True, capturable=use_graph)
     T = 512
     g = torch.Generator(device=dev).manual_seed(rank)
+    static_tok = torch.zeros(args.batch, T + 1, device=dev, dtype=torch.int64)
+    graph, static_loss = None, None
+
+    def body():
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            loss = net(static_tok[:, :-1], static_tok[:, 1:])
+        loss.backward()
+        torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)
+        opt.step()
+        return loss
 
     def step():
+        if graph is not None:
+            static_tok.copy_(torch.randint(0, 50257, (args.batch, T + 1), device=dev, generator=g))
+            graph.replay()
+            return static_loss
         tok = torch.randint(0, 50257, (args.batch, T + 1), device=dev, generator=g)
         with torch.autocast("cuda", dtype=torch.bfloat16):
             loss = net(tok[:, :-1], tok[:, 1:])
@@ -81,6 +100,22 @@ def main():
     for _ in range(max(args.warmup, 3)):
         step()
     torch.cuda.synchronize()
+    if use_graph:   # whole-step capture (PyTorch "whole network capture" recipe): warm up on a side stream, then capture
+        static_tok.copy_(torch.randint(0, 50257, (args.batch, T + 1), device=dev, generator=g))
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                opt.zero_grad(set_to_none=True)
+                body()
+        torch.cuda.current_stream().wait_stream(side)
+        opt.zero_grad(set_to_none=True)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            static_loss = body()
+        for _ in range(3):
+            step()
+        torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -94,7 +129,8 @@ def main():
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms = ms.item()
     if rank == 0:
-        print(json.dumps({"impl": "torch-eager stand-in baseline (cuBLAS + SDPA + fused AdamW + NCCL DDP)",
+        print(json.dumps({"impl": ("torch CUDA-graph" if graph is not None else "torch-eager")
+                          + " stand-in baseline (cuBLAS + SDPA + fused AdamW + NCCL DDP)",
                           "metric": "training throughput, tokens/s (whole job), DP", "n_gpus": world,
                           "value": args.batch * world * T * args.steps / (ms / 1e3), "unit": "tokens/s",
                           "ms_per_step": ms / args.steps, "steps": args.steps, "dtype": "bf16 autocast",

@@ -12,6 +12,9 @@ if [ "$N" = "1" ]; then
   DTC_EXPERIMENTAL=1 timeout 200 python -m pytest tests/test_experimental_gpu.py -q -x 2>&1 | tail -15 | tee gpurun_out/x_experimental_tests.log
   run dp1_default python bench.py --steps 30 --warmup 5
   DTC_WGRAD_GROUPED=1 run dp1_wgrad_grouped python bench.py --steps 30 --warmup 5
+  # the fairer bar for the kernels: the same cuBLAS / SDPA / fused-AdamW step without host launch gaps
+  timeout 100 python baseline/torch_baseline.py --steps 30 --graph 2> gpurun_out/x_torch_graph.err | tail -1 > gpurun_out/baseline_torch_graph_1gpu.json
+  echo "torch graph baseline rc=$? $(cut -c1-300 gpurun_out/baseline_torch_graph_1gpu.json)"
 fi
 if [ "$N" = "2" ]; then
   DTC_EXPERIMENTAL=1 timeout 300 python -m pytest tests/test_multigpu.py -q -x -k "sequence_parallel or cuda_graph_per_action or tp2 or folded" 2>&1 | tail -15 | tee gpurun_out/x_multigpu_tests.log
