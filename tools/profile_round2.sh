@@ -7,15 +7,15 @@
 #   wgrad      ncu --set full on the grouped wgrad kernel                     -> gpurun_out/prof_wgrad.ncu-rep
 # Read here with:  ncu -i gpurun_out/<name>.ncu-rep --page raw --csv | grep -E 'gpu__time_duration.sum|sm__pipe_tensor|lts__t_bytes|dram__bytes|sm__warps_active|launch__registers'
 #                  ncu -i gpurun_out/<name>.ncu-rep --page source --csv      (stall reasons per line; the library is built with -lineinfo)
-#                  python tools/ncu_launch_table.py gpurun_out/launches_r2.csv --steps 2 --md profiles/r2/step_budget_ncu.md
+#                  python tools/ncu_launch_table.py gpurun_out/launches_r2.csv --steps 2.1 --md profiles/r2/step_budget_ncu.md   (steps = launches / ~300)
 mkdir -p gpurun_out
 what=${1:-launches}
 case "$what" in
   launches)
     cmd="python bench.py --steps 2 --warmup 3 --no-graph"
     $cmd > gpurun_out/plain.log 2>&1 || { tail -20 gpurun_out/plain.log; exit 1; }
-    # skip the launches of the 3 + 3 warm-up / eager steps (~330 kernels each), keep two steps
-    ncu --metrics gpu__time_duration.sum --clock-control none -s 2400 -c 700 --csv --log-file gpurun_out/launches_r2.csv $cmd \
+    # ~300 launches per step without the graph: skip the 3 warm-up steps, keep about two steps
+    ncu --metrics gpu__time_duration.sum --clock-control none -s 900 -c 650 --csv --log-file gpurun_out/launches_r2.csv $cmd \
       > gpurun_out/ncu.log 2>&1; echo "ncu rc=$?"; grep -c gpu__time_duration gpurun_out/launches_r2.csv ;;
   attn_bwd|attn_fwd|gemm)
     case "$what" in attn_bwd) pat="flash_attn_bwd"; tgt=attn;; attn_fwd) pat="flash_attn_fwd"; tgt=attn;; gemm) pat="gemm_persistent"; tgt=gemm;; esac
