@@ -869,22 +869,16 @@ static int launch_fwd(const void* q, const void* k, const void* v, long long ld,
     if ((rc = make_tmap_2d_bf16(&tv64, v, M, (uint64_t)H * HD, ld, 64, HD, swz))) return rc;
     const int smem64 = C::TILE_BYTES + ATT_BLK * 128 + 4 * 64 * C::ROW_BYTES + 1024 + 128;
     auto kern64 = flash_attn_fwd_kv64_kernel<HD>;
-    static bool configured64 = false;
-    if (!configured64) {
-      DTC_CHECK_CUDA(cudaFuncSetAttribute(kern64, cudaFuncAttributeMaxDynamicSharedMemorySize, smem64));
-      configured64 = true;
-    }
+    static dtc::SmemOptIn configured64;  // per device
+    DTC_CHECK_CUDA(dtc::ensure_dyn_smem(kern64, smem64, configured64));
     DTC_CHECK_CUDA(dtc::launch(kern64, grid, 128, smem64, stream, tq, tk64, tv64, reinterpret_cast<bf16*>(out), ldo, lse2, T, H,
                                scale * LOG2E));
     return 0;
   }
   const int smem = 5 * C::TILE_BYTES + C::P_BYTES + 1024 + 128;
   auto kern = flash_attn_fwd_kernel<HD>;
-  static bool configured = false;
-  if (!configured) {
-    DTC_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    configured = true;
-  }
+  static dtc::SmemOptIn configured;  // per device
+  DTC_CHECK_CUDA(dtc::ensure_dyn_smem(kern, smem, configured));
   DTC_CHECK_CUDA(dtc::launch(kern, grid, 128, smem, stream, tq, tk, tv, reinterpret_cast<bf16*>(out), ldo, lse2, T, H, scale * LOG2E));
   DTC_CHECK_LAUNCH();
   return 0;
@@ -914,11 +908,8 @@ static int launch_bwd(const void* q, const void* k, const void* v, long long ld,
     if (!use_v1) {
       const int smem2 = 5 * C::TILE_BYTES + 2 * C::P_BYTES + 2 * ATT_BLK * 4 + 1024 + 128;
       auto kern2 = flash_attn_bwd_regacc_kernel<HD>;
-      static bool configured2 = false;
-      if (!configured2) {
-        DTC_CHECK_CUDA(cudaFuncSetAttribute(kern2, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
-        configured2 = true;
-      }
+      static dtc::SmemOptIn configured2;  // per device
+      DTC_CHECK_CUDA(dtc::ensure_dyn_smem(kern2, smem2, configured2));
       dim3 grid2(T / ATT_BLK, H, B);
       DTC_CHECK_CUDA(dtc::launch(kern2, grid2, 128, smem2, stream, tq, tk, tv, tdo, lse2, delta, dq_accum, lddq,
                                  reinterpret_cast<bf16*>(dk), reinterpret_cast<bf16*>(dv), lddkv, T, H, scale_,
@@ -928,11 +919,8 @@ static int launch_bwd(const void* q, const void* k, const void* v, long long ld,
   }
   const int smem = 6 * C::TILE_BYTES + 2 * C::P_BYTES + 4 * ATT_BLK * 4 + 1024 + 128;
   auto kern = flash_attn_bwd_kernel<HD>;
-  static bool configured = false;
-  if (!configured) {
-    DTC_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    configured = true;
-  }
+  static dtc::SmemOptIn configured;  // per device
+  DTC_CHECK_CUDA(dtc::ensure_dyn_smem(kern, smem, configured));
   const float scale = 1.f / sqrtf((float)HD);
   dim3 grid(T / ATT_BLK, H, B);
   DTC_CHECK_CUDA(dtc::launch(kern, grid, 128, smem, stream, tq, tk, tv, tdo, lse2, delta, dq_accum, lddq, reinterpret_cast<bf16*>(dk),

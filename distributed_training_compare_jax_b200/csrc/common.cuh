@@ -57,6 +57,26 @@ inline cudaError_t launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is a per-device (per-context) setting, not a per-process one: a process
+// that drives several GPUs must opt in on each of them.  `done` is the call site's table (one static per kernel
+// instantiation), indexed by the current device.  Setting the attribute twice is harmless, so a race between two host
+// threads on the same device is benign.
+constexpr int MAX_DEVICES = 64;
+struct SmemOptIn {
+  bool done[MAX_DEVICES] = {};
+};
+template <typename K>
+inline cudaError_t ensure_dyn_smem(K kernel, int bytes, SmemOptIn& table) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  const bool tracked = dev >= 0 && dev < MAX_DEVICES;
+  if (tracked && table.done[dev]) return cudaSuccess;
+  e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e == cudaSuccess && tracked) table.done[dev] = true;
+  return e;
+}
+
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 

@@ -323,11 +323,8 @@ static int launch_gemm(const void* A, long long lda, const void* B, long long ld
   while (S::bytes(stages) > 227 * 1024) --stages;
   const int smem_bytes = S::bytes(stages);
   auto kern = gemm_tcgen05_kernel<A_MN, B_MN, BN>;
-  static int configured_smem = 0;  // per instantiation
-  if (smem_bytes > configured_smem) {
-    DTC_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    configured_smem = 227 * 1024;
-  }
+  static dtc::SmemOptIn configured;  // per instantiation, per device
+  DTC_CHECK_CUDA(dtc::ensure_dyn_smem(kern, 227 * 1024, configured));
   const int m_blocks = (M + BM - 1) / BM, n_blocks = (N + BN - 1) / BN;
   dim3 grid(m_blocks * n_blocks, splits, 1);
   DTC_CHECK_CUDA(dtc::launch(kern, grid, GEMM_THREADS, smem_bytes, stream, ta, tb, M, N, K, m_blocks, kb_per_split, stages, epi));
@@ -767,11 +764,8 @@ static int launch_gemm_persistent(const void* A, long long lda, const void* B, l
   while (stages > 2 && S::bytes(stages, DUAL, staging) > smem_cap) --stages;
   const int smem_bytes = S::bytes(stages, DUAL, staging);
   auto kern = gemm_persistent_kernel<A_MN, B_MN, BN, DUAL, SCATTER, SIGNAL>;
-  static bool configured = false;
-  if (!configured) {
-    DTC_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, DUAL ? 113 * 1024 : 227 * 1024));
-    configured = true;
-  }
+  static dtc::SmemOptIn configured;  // per device
+  DTC_CHECK_CUDA(dtc::ensure_dyn_smem(kern, DUAL ? 113 * 1024 : 227 * 1024, configured));
   const int m_blocks = (M + BM - 1) / BM, n_blocks = (N + BN - 1) / BN;
   const int total_tiles = m_blocks * n_blocks * splits;
   const int max_ctas = (DUAL ? 2 : 1) * num_sms();
@@ -1286,11 +1280,8 @@ static int launch_gemm_2cta(const void* A, long long lda, const void* B, long lo
   while (S::bytes(stages) > 227 * 1024) --stages;
   const int smem_bytes = S::bytes(stages);
   auto kern = gemm_2cta_kernel<A_MN, B_MN, BN>;
-  static bool configured = false;
-  if (!configured) {
-    DTC_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    configured = true;
-  }
+  static dtc::SmemOptIn configured;  // per device
+  DTC_CHECK_CUDA(dtc::ensure_dyn_smem(kern, 227 * 1024, configured));
   const int m_blocks = (M + 255) / 256, n_blocks = (N + BN - 1) / BN;
   const int total_tiles = m_blocks * n_blocks * splits;
   const int max_pairs = num_sms() / 2;
@@ -1551,11 +1542,8 @@ extern "C" int dtc_gemm_wgrad_grouped(int count, const unsigned long long* A, co
   auto smem_of = [](int st) { return st * S::STAGE_BYTES + 1024 + 256; };
   while (stages > 2 && smem_of(stages) > smem_cap) --stages;
   auto kern = gemm_grouped_wgrad_kernel<BN>;
-  static bool configured = false;
-  if (!configured) {
-    DTC_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 113 * 1024));
-    configured = true;
-  }
+  static dtc::SmemOptIn configured;  // per device
+  DTC_CHECK_CUDA(dtc::ensure_dyn_smem(kern, 113 * 1024, configured));
   const int total_tiles = tiles * splits;
   const int max_ctas = 2 * num_sms();
   const int grid = total_tiles < max_ctas ? total_tiles : max_ctas;

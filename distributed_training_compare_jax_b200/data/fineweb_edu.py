@@ -135,12 +135,22 @@ class _Prefetcher:
         return item
 
 
+def _skip(gen: Iterator[np.ndarray], n: int) -> Iterator[np.ndarray]:
+    for _ in range(n):
+        next(gen)
+    yield from gen
+
+
 def get_batch_iterator(batch_size: int, seq_len: int, *, seed: int = 0, rank: int = 0, world: int = 1,
-                       synthetic: bool = True, prefetch: int = 4) -> Any:
+                       synthetic: bool = True, prefetch: int = 4, skip_batches: int = 0) -> Any:
     """Infinite iterator of ``np.int32 [batch_size // world, seq_len]`` batches (``[batch_size, seq_len]`` when
-    ``world == 1``).  All ranks walk the same global stream, so DP/TP/PP see identical global batches."""
+    ``world == 1``).  All ranks walk the same global stream, so DP/TP/PP see identical global batches.
+    ``skip_batches``: global batches already consumed by the run being resumed (the stream is deterministic, so the
+    resumed run continues with the batch the interrupted one would have seen next)."""
     if world > 1 and batch_size % world:
         raise ValueError(f"batch {batch_size} not divisible by {world} data-parallel ranks")
     gen = _synthetic_batches(batch_size, seq_len, seed, rank, world) if synthetic \
         else _hf_batches(batch_size, seq_len, rank, world)
+    if skip_batches > 0:
+        gen = _skip(gen, skip_batches)
     return _Prefetcher(gen, prefetch) if prefetch > 0 else gen

@@ -366,3 +366,70 @@ def import_flax_tree(tree: dict[str, np.ndarray], local: LocalShape, views: dict
         if nv > 0:
             views["wlm"][:, :nv].copy_(t("lm_head/kernel")[:, v0:v0 + nv])
             views["blm"][:nv].copy_(t("lm_head/bias")[v0:v0 + nv])
+
+
+# ----------------------------------------------------------------------------------------------------------
+# The reference's PIPELINE state layout (train/train.py:141-167)
+# ----------------------------------------------------------------------------------------------------------
+def export_pp_tree(tree: dict[str, np.ndarray], n_stages: int, layer_ranges: list[range] | None = None,
+                   dead_copy_scale: float = 1.0) -> dict[str, np.ndarray] | list[dict[str, np.ndarray]]:
+    """Re-arrange a merged DP/TP-layout tree (``export_flax_tree``) into the state the reference's ``train_pp`` holds.
+
+    The reference builds, for every stage ``i``, ``{"embed": {wte, wpe}, "stage": {ScanScanBlock_0/… with a leading axis of
+    layers_per_stage}, "head": {LayerNorm_0, lm_head}}`` (train/train.py:155-161) and stacks the S per-stage trees on a
+    new leading axis with ``jax.device_put_sharded`` (train/train.py:166-167).  Keys here are the ``/``-joined paths of
+    that tree (``embed/wte/embedding``, ``stage/ScanScanBlock_0/…``, ``head/lm_head/kernel``).
+
+    ``layer_ranges``: layers owned by each stage; default = the reference's ``n_layers // n_stages`` contiguous layers per
+    stage (remainder dropped, quirk Q2).  When every stage owns the same number of layers the result is ONE dict whose
+    leaves carry the leading ``S`` axis (the reference's layout); otherwise — this framework's uneven split — a list of
+    per-stage dicts, which cannot be stacked.
+
+    ``dead_copy_scale``: the reference keeps a copy of embed / head on EVERY stage although only the first / last stage
+    uses them; the unused copies receive zero gradients and merely shrink by weight decay, ``p·(1 − lr·wd)`` per step
+    (SURVEY.md §2.7 "PP dead copies").  This framework stores embed / head on their owner stage only; pass
+    ``(1 − lr·wd) ** steps`` to reproduce the dead copies' values analytically relative to the INITIAL weights — or keep
+    1.0 to fill every copy with the owner's current value."""
+    n_layers = next(v.shape[0] for k, v in tree.items() if k.startswith(BLOCK + "/"))
+    if layer_ranges is None:
+        per = n_layers // n_stages
+        layer_ranges = [range(s * per, (s + 1) * per) for s in range(n_stages)]
+    if len(layer_ranges) != n_stages:
+        raise ValueError(f"{len(layer_ranges)} layer ranges for {n_stages} stages")
+    embed_keys = ("wte/embedding", "wpe/embedding")
+    head_keys = ("LayerNorm_0/scale", "LayerNorm_0/bias", "lm_head/kernel", "lm_head/bias")
+    per_stage: list[dict[str, np.ndarray]] = []
+    for s, rng in enumerate(layer_ranges):
+        d: dict[str, np.ndarray] = {}
+        for k in embed_keys:
+            d[f"embed/{k}"] = tree[k] if s == 0 else tree[k] * np.float32(dead_copy_scale)
+        for k, v in tree.items():
+            if k.startswith(BLOCK + "/"):
+                d[f"stage/{k}"] = v[rng.start:rng.stop]
+        for k in head_keys:
+            d[f"head/{k}"] = tree[k] if s == n_stages - 1 else tree[k] * np.float32(dead_copy_scale)
+        per_stage.append(d)
+    if len({len(r) for r in layer_ranges}) == 1:
+        return {k: np.stack([d[k] for d in per_stage], 0) for k in per_stage[0]}
+    return per_stage
+
+
+def import_pp_tree(pp_tree: dict[str, np.ndarray] | list[dict[str, np.ndarray]]) -> dict[str, np.ndarray]:
+    """Inverse of :func:`export_pp_tree`: merge a reference-layout pipeline state back into the DP/TP-layout tree
+    (embed from stage 0, head from the last stage, layers concatenated in stage order)."""
+    if isinstance(pp_tree, dict):
+        S = next(iter(pp_tree.values())).shape[0]
+        stages = [{k: v[s] for k, v in pp_tree.items()} for s in range(S)]
+    else:
+        stages = list(pp_tree)
+    out: dict[str, np.ndarray] = {}
+    for k, v in stages[0].items():
+        if k.startswith("embed/"):
+            out[k[len("embed/"):]] = v
+    for k, v in stages[-1].items():
+        if k.startswith("head/"):
+            out[k[len("head/"):]] = v
+    for k in stages[0]:
+        if k.startswith("stage/"):
+            out[k[len("stage/"):]] = np.concatenate([d[k] for d in stages], 0)
+    return out

@@ -50,7 +50,9 @@ def _digest() -> str:
                     + [REPO_DIR / "include" / "dtc_b200.h"]):
         h.update(p.name.encode())
         h.update(p.read_bytes())
-    h.update(" ".join(NVCC_FLAGS).encode())
+    # flags without the absolute include paths: the same tree must digest identically wherever it is checked out
+    # (the GPU box runs a copy of the repo under a scratch path)
+    h.update(" ".join(f for f in NVCC_FLAGS if not os.path.isabs(f)).encode())
     return h.hexdigest()
 
 
@@ -65,6 +67,20 @@ def build(force: bool = False, verbose: bool = True) -> Path:
     nvcc = find_nvcc()
     OBJ_DIR.mkdir(parents=True, exist_ok=True)
     LIB_DIR.mkdir(parents=True, exist_ok=True)
+    # several ranks may get here at once: one builds, the others wait for the lock and find a fresh library
+    import fcntl
+    lock = open(LIB_DIR / ".build.lock", "w")
+    fcntl.flock(lock, fcntl.LOCK_EX)
+    try:
+        if not force and is_fresh():
+            return LIB_PATH
+        return _build_locked(nvcc, verbose)
+    finally:
+        fcntl.flock(lock, fcntl.LOCK_UN)
+        lock.close()
+
+
+def _build_locked(nvcc: str, verbose: bool) -> Path:
 
     def compile_one(src: Path) -> Path:
         obj = OBJ_DIR / (src.stem + ".o")

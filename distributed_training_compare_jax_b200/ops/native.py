@@ -74,10 +74,20 @@ def load(build_if_missing: bool = True) -> C.CDLL:
     if _LIB is not None:
         return _LIB
     path = lib_path()
-    if not path.exists() or (os.environ.get("DTC_REBUILD") == "1"):
-        if not build_if_missing:
-            raise RuntimeError(f"{path} is missing: run `python -m distributed_training_compare_jax_b200.ops.build`")
-        _build.build(force=True)
+    force = os.environ.get("DTC_REBUILD") == "1"
+    if force or not _build.is_fresh():
+        # missing OR stale (csrc / header digest differs from the one the .so was built from): never run an old binary
+        # against newer sources.  The digest check is cheap (hash of ~10 files); the rebuild needs nvcc.
+        have_nvcc = True
+        try:
+            _build.find_nvcc()
+        except RuntimeError:
+            have_nvcc = False
+        if not build_if_missing or not have_nvcc:
+            what = "missing" if not path.exists() else "stale (csrc/ or include/ changed since it was built)"
+            raise RuntimeError(f"{path} is {what}: run `python -m distributed_training_compare_jax_b200.ops.build`"
+                               + ("" if have_nvcc else " on a machine with nvcc"))
+        _build.build(force=force)
     lib = C.CDLL(str(path))
     lib.dtc_last_error.restype = C.c_char_p
     lib.dtc_version.restype = I

@@ -38,6 +38,8 @@ class TrainState:
     optimizer: Any
     mesh: Any
     step: int = 0
+    batches_consumed: int = 0   # global batches drawn from the token stream so far (saved in checkpoints)
+    resumed: bool = False       # state came from a checkpoint: no warm-up steps, the stream continues
 
     @property
     def params(self):

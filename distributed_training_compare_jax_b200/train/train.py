@@ -80,7 +80,15 @@ def build_state(train_config: TrainConfig, model_config: ModelConfig, opt_config
     if train_config.resume:
         meta = load_checkpoint(train_config.resume, store)
         state.step = int(meta.get("step", 0))
+        # a resumed run continues the token stream where the interrupted one stopped and does not repeat the warm-up
+        state.batches_consumed = int(meta.get("batches_consumed", state.step))
+        state.resumed = True
     return state
+
+
+def _checkpoint_meta(state: TrainState, mesh: DeviceMesh, strategy: str) -> dict:
+    return {"strategy": strategy, "batches_consumed": state.batches_consumed,
+            "mesh_shape": [mesh.dp.size, mesh.tp.size, mesh.pp.size]}
 
 
 def _run_loop(train_config: TrainConfig, model_config: ModelConfig, state: TrainState, train_step, data_iterator,
@@ -92,8 +100,10 @@ def _run_loop(train_config: TrainConfig, model_config: ModelConfig, state: Train
         return Batch(x=np.ascontiguousarray(x_np[:, :-1]), y=np.ascontiguousarray(x_np[:, 1:]))
 
     log.say("Warmup")
-    for _ in range(train_config.warmup_steps):
+    # the reference's warm-up steps TRAIN and consume data (train/train.py:63-70); a resumed run already did them
+    for _ in range(0 if state.resumed else train_config.warmup_steps):
         state, loss = train_step(state, next_batch(), None)
+        state.batches_consumed += 1
     if mesh.device.type == "cuda":
         torch.cuda.synchronize()
     mesh.barrier()
@@ -109,6 +119,7 @@ def _run_loop(train_config: TrainConfig, model_config: ModelConfig, state: Train
         if step == fault_step and mesh.rank == fault_rank:
             raise RuntimeError(f"injected fault on rank {mesh.rank} at step {step} (DTC_FAULT)")
         state, loss = train_step(state, next_batch(), None)
+        state.batches_consumed += 1
         if train_config.sync_every_step:
             log.record(step, float(loss))          # blocking D2H like the reference (train/train.py:82-83)
         else:
@@ -121,7 +132,7 @@ def _run_loop(train_config: TrainConfig, model_config: ModelConfig, state: Train
             if hasattr(state.optimizer, "sync_full_state"):
                 state.optimizer.sync_full_state()
             save_checkpoint(os.path.join(train_config.checkpoint_dir, f"step_{state.step}.npz"), state.engine.store,
-                            mesh, state.step, {"strategy": strategy})
+                            mesh, state.step, _checkpoint_meta(state, mesh, strategy))
     ms = mesh.max_over_ranks(timer.stop())
     steps = max(train_config.steps, 1)
     metrics = {"strategy": strategy, "world_size": mesh.world_size, "backend": state.engine.backend,
@@ -134,7 +145,7 @@ def _run_loop(train_config: TrainConfig, model_config: ModelConfig, state: Train
         if hasattr(state.optimizer, "sync_full_state"):
             state.optimizer.sync_full_state()
         save_checkpoint(os.path.join(train_config.checkpoint_dir, "final.npz"), state.engine.store, mesh, state.step,
-                        {"strategy": strategy})
+                        _checkpoint_meta(state, mesh, strategy))
     return metrics
 
 
@@ -153,7 +164,8 @@ def train_dp_tp(train_config: TrainConfig, model_config: ModelConfig, opt_config
                         local)
     train_step = create_train_step(parallel=parallel_strategy, cuda_graph=train_config.cuda_graph)
     data_iterator = get_batch_iterator(batch_size=global_batch, seq_len=T + 1, seed=train_config.seed, rank=mesh.dp.rank,
-                                       world=dp, synthetic=train_config.synthetic_data)
+                                       world=dp, synthetic=train_config.synthetic_data,
+                                       skip_batches=state.batches_consumed)
     return _run_loop(train_config, model_config, state, train_step, data_iterator, mesh, global_batch * T,
                      parallel_strategy)
 
@@ -176,6 +188,6 @@ def train_pp(train_config: TrainConfig, model_config: ModelConfig, opt_config: O
     train_step = create_pp_train_step(num_microbatches=M, num_stages=S, schedule=train_config.pp_schedule,
                                       cuda_graph=train_config.pp_cuda_graph and train_config.cuda_graph)
     data_iterator = get_batch_iterator(batch_size=train_config.batch, seq_len=T + 1, seed=train_config.seed,
-                                       synthetic=train_config.synthetic_data)
+                                       synthetic=train_config.synthetic_data, skip_batches=state.batches_consumed)
     return _run_loop(train_config, model_config, state, train_step, data_iterator, mesh, train_config.batch * T,
                      parallel_strategy)

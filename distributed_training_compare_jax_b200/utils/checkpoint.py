@@ -7,7 +7,7 @@ its Flax/optax state.  A checkpoint is one ``.npz`` whose keys are ``/``-joined 
     opt_state/mu/<path>      Adam first moment  (optax ScaleByAdamState.mu)   — same tree as params
     opt_state/nu/<path>      Adam second moment (optax ScaleByAdamState.nu)
     opt_state/count, step    optimizer step count / TrainState.step
-    meta/*                   strategy, mesh shape, data position
+    meta/*                   strategy, mesh_shape (dp, tp, pp), batches_consumed (position in the token stream)
 
 Saving gathers every rank's physical tensors to rank 0 (``gather_object``) and merges them with
 ``export_flax_tree``; loading slices the full tree for the local rank (``import_flax_tree``), so a checkpoint
@@ -64,10 +64,11 @@ def load_checkpoint(path: str, store: ParamStore) -> dict:
         n = len(prefix) + 1
         return {k[n:]: z[k] for k in z.files if k.startswith(prefix + "/")}
 
-    import_flax_tree(sub("params"), store.local, store.p)
-    if store.flat_m is not None and any(k.startswith("opt_state/mu/") for k in z.files):
-        import_flax_tree(sub("opt_state/mu"), store.local, store.views_of(store.flat_m))
-        import_flax_tree(sub("opt_state/nu"), store.local, store.views_of(store.flat_v))
+    with torch.no_grad():   # the torch engine has already marked the parameter views as autograd leaves
+        import_flax_tree(sub("params"), store.local, store.p)
+        if store.flat_m is not None and any(k.startswith("opt_state/mu/") for k in z.files):
+            import_flax_tree(sub("opt_state/mu"), store.local, store.views_of(store.flat_m))
+            import_flax_tree(sub("opt_state/nu"), store.local, store.views_of(store.flat_v))
     if "opt_state/count" in z.files:
         store.step.fill_(int(z["opt_state/count"]))
     store.sync_compute_copy()

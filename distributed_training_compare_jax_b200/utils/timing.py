@@ -56,21 +56,61 @@ _QUERY = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
 
 
 class ClockSampler:
-    """Samples SM clock / throttle reasons of one GPU every ``period`` s while the context is active."""
+    """Samples SM clock / throttle reasons of one GPU every ``period`` s while the context is active.
 
-    def __init__(self, gpu_index: int = 0, period: float = 0.2):
+    NVML (``pynvml``, in-process, ≈ 0.1 ms per sample) is used when available so that even a 0.1 s timed region gets
+    several samples at the default 10 ms period; otherwise ``nvidia-smi`` is polled (≈ 50 ms per sample)."""
+
+    _REASONS = (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20), ("sw_power_cap", 0x4))
+
+    def __init__(self, gpu_index: int = 0, period: float = 0.01):
         self.gpu_index, self.period = gpu_index, period
         self.samples: list[list[str]] = []
         self._stop = threading.Event()
         self._t: threading.Thread | None = None
+        self.source = "nvidia-smi"
+        self._nvml = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            # NVML enumerates physical devices: honour CUDA_VISIBLE_DEVICES when it is a plain index list
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+            phys = gpu_index
+            if vis and all(v.strip().isdigit() for v in vis.split(",")):
+                ids = [int(v) for v in vis.split(",")]
+                if gpu_index < len(ids):
+                    phys = ids[gpu_index]
+            self._handle = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self._max = pynvml.nvmlDeviceGetMaxClockInfo(self._handle, pynvml.NVML_CLOCK_SM)
+            self._nvml = pynvml
+            self.source = "nvml"
+        except Exception:
+            self._nvml = None
+
+    def _sample_nvml(self) -> None:
+        nv = self._nvml
+        sm = nv.nvmlDeviceGetClockInfo(self._handle, nv.NVML_CLOCK_SM)
+        try:
+            mask = nv.nvmlDeviceGetCurrentClocksEventReasons(self._handle)
+        except Exception:
+            mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self._handle)
+        try:
+            watts = nv.nvmlDeviceGetPowerUsage(self._handle) / 1e3
+        except Exception:
+            watts = 0.0
+        self.samples.append([str(sm), str(self._max), f"{watts:.1f}"]
+                            + ["Active" if mask & bit else "Not Active" for _, bit in self._REASONS])
 
     def _poll(self) -> None:
         while not self._stop.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", f"--id={self.gpu_index}", f"--query-gpu={_QUERY}",
-                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5)
-                if out.returncode == 0 and out.stdout.strip():
-                    self.samples.append([c.strip() for c in out.stdout.strip().splitlines()[0].split(",")])
+                if self._nvml is not None:
+                    self._sample_nvml()
+                else:
+                    out = subprocess.run(["nvidia-smi", f"--id={self.gpu_index}", f"--query-gpu={_QUERY}",
+                                          "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5)
+                    if out.returncode == 0 and out.stdout.strip():
+                        self.samples.append([c.strip() for c in out.stdout.strip().splitlines()[0].split(",")])
             except Exception:
                 pass
             self._stop.wait(self.period)
@@ -86,21 +126,23 @@ class ClockSampler:
             self._t.join(timeout=6)
 
     def summary(self) -> dict:
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        sm, mx, watts, reasons = [], [], [], set()
+        names = [n for n, _ in self._REASONS]
         for s in self.samples:
             try:
                 sm.append(float(s[0]))
                 mx.append(float(s[1]))
+                watts.append(float(s[2]))
             except (ValueError, IndexError):
                 continue
             for name, val in zip(names, s[3:7]):
                 if val.lower().startswith("active"):
                     reasons.add(name)
         if not sm:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0, "source": self.source}
         return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons),
-                "samples": len(sm)}
+                "samples": len(sm), "power_w_max": max(watts) if watts else None, "source": self.source,
+                "period_s": self.period}
 
 
 class nvtx_range:

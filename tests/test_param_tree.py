@@ -139,3 +139,39 @@ def test_checkpoint_is_flax_layout_and_resumes(tmp_path):
     Fl = SMALL.d_ff // 2
     assert torch.equal(st2.p["w1"], st.p["w1"][:, :, Fl:])
     assert torch.equal(st2.views_of(st2.flat_v)["w2"], st.views_of(st.flat_v)["w2"][:, Fl:, :])
+
+
+def _small_flax_tree():
+    st = pt.ParamStore(pt.LocalShape(SMALL), "cpu", with_compute_copy=False)
+    pt.init_params(st, seed=3)
+    return pt.export_flax_tree([(st.local, st.p)])
+
+
+def test_pp_state_layout_matches_the_reference_and_round_trips():
+    """reference train/train.py:155-167: {"embed","stage","head"} per stage, stacked on a leading S axis."""
+    tree = _small_flax_tree()
+    blk = "ScanScanBlock_0/TransformerBlock_0"
+    pp = pt.export_pp_tree(tree, n_stages=2)
+    assert isinstance(pp, dict)
+    assert pp["embed/wte/embedding"].shape == (2, 1003, 64) and pp["head/lm_head/kernel"].shape == (2, 64, 1003)
+    assert pp[f"stage/{blk}/MLP_0/fc1/kernel"].shape == (2, 2, 64, 128)          # (S, layers_per_stage, D, F)
+    assert {k.split("/")[0] for k in pp} == {"embed", "stage", "head"}
+    assert np.array_equal(pp[f"stage/{blk}/MLP_0/fc1/kernel"][1, 0], tree[f"{blk}/MLP_0/fc1/kernel"][2])
+    assert np.array_equal(pp["embed/wte/embedding"][0], pp["embed/wte/embedding"][1])   # replicated copies
+    back = pt.import_pp_tree(pp)
+    assert set(back) == set(tree) and all(np.array_equal(back[k], tree[k]) for k in tree)
+    # the reference's floor split drops the remainder (12 layers on 8 stages -> 8 layers): 4 layers on 3 stages -> 3
+    pp3 = pt.export_pp_tree(tree, n_stages=3)
+    assert pp3[f"stage/{blk}/LayerNorm_0/scale"].shape == (3, 1, 64)
+    # the framework's uneven split keeps every layer and cannot be stacked: a list of per-stage trees
+    from distributed_training_compare_jax_b200.parallel.pp import stage_layers
+    uneven = pt.export_pp_tree(tree, 3, layer_ranges=stage_layers(4, 3))
+    assert isinstance(uneven, list) and [d[f"stage/{blk}/LayerNorm_0/scale"].shape[0] for d in uneven] == [2, 1, 1]
+    back = pt.import_pp_tree(uneven)
+    assert all(np.array_equal(back[k], tree[k]) for k in tree)
+    # dead copies: unused embed / head replicas shrink by weight decay only
+    dead = pt.export_pp_tree(tree, 2, dead_copy_scale=0.5)
+    assert np.allclose(dead["embed/wte/embedding"][1], 0.5 * tree["wte/embedding"])
+    assert np.array_equal(dead["embed/wte/embedding"][0], tree["wte/embedding"])
+    assert np.allclose(dead["head/lm_head/kernel"][0], 0.5 * tree["lm_head/kernel"])
+    assert np.array_equal(dead["head/lm_head/kernel"][1], tree["lm_head/kernel"])

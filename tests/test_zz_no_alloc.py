@@ -67,9 +67,11 @@ def _run_pair(lib, B, H, T, hd, seed):
     def rel(a, b):
         return ((a.float() - b.float()).norm() / b.float().norm().clamp_min(1e-12)).item()
 
-    # same kernels, same inputs: only the fp32 reduce-add order of dQ may differ between the two runs
-    assert rel(dq_b, dq_a) < 1e-2
-    assert rel(dkv_b[:, Dl:], dkv_a[:, Dl:]) < 1e-2
+    # Same kernels, same inputs, same launch order.  dK / dV are produced by one CTA per key block in a fixed order, so
+    # the two entry points must agree bit for bit; dQ is accumulated with fp32 reduce-adds whose arrival order may
+    # differ from run to run, which moves it by rounding noise only.
+    assert torch.equal(dkv_b[:, Dl:], dkv_a[:, Dl:])
+    assert rel(dq_b, dq_a) < 1e-5
     assert torch.isfinite(dq_b).all() and torch.isfinite(dkv_b[:, Dl:].float()).all()
 
 
