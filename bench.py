@@ -1,19 +1,29 @@
 """Headline benchmark: training throughput (tokens/s, whole job) of the reference GPT on N B200s.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--parallel dp|tp|pp] [--impl native|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--arms dp,dp_weak,tp,pp] [--impl native|reference]
 
 Metric / config (BASELINE.json): GPT 12L / d512 / 16 heads / ff2048 / seq 512 / vocab 50258
-(configs/model_config.yaml), train_config_{dp,tp,pp}.yaml shapes (batch 8 per data-parallel rank — weak scaling:
-global batch = 8·N for DP; TP / PP keep batch 8), clip 1.0 + AdamW lr 3e-4 wd 0.1, bf16 compute with fp32 master
-weights / optimizer state, synthetic FineWeb-edu-shaped tokens and random-init weights (no network on the box).
+(configs/model_config.yaml), train_config_{dp,tp,pp}.yaml shapes, clip 1.0 + AdamW lr 3e-4 wd 0.1, bf16 compute
+with fp32 master weights / optimizer state, synthetic FineWeb-edu-shaped tokens and random-init weights (no network).
 
-Two numbers per run, both over EXACTLY K full training steps (forward, backward, gradient reduction, clip,
-AdamW — nothing skipped), bracketed by barrier + synchronize, CUDA events, max over ranks:
+One invocation at N GPUs times, in this order, the reference's three strategies on the reference's shapes:
+  dp       HEADLINE.  Data parallel at the reference's batch semantics: ``batch: 8`` is the GLOBAL batch, sharded over
+           the data axis (reference train/create_train_step.py:36-40) -> strong scaling, 8/N sequences per rank.
+  dp_weak  data parallel with batch 8 PER RANK (global batch 8·N)                      -> ``extra.dp_weak``
+  tp       tensor parallel over all N GPUs, global batch 8 (train_config_tp.yaml)       -> ``extra.tp``
+  pp       pipeline parallel, N stages, 2 microbatches (train_config_pp.yaml)           -> ``extra.pp``
+At N = 1 the four coincide (one GPU, batch 8) and only the headline arm runs.  ``--parallel X`` runs a single arm
+(tools / A-B scripts).  An arm that fails or exceeds its time limit is reported as ``{"error": ...}`` under ``extra``
+and does not take the headline number down with it.
+
+Two numbers per arm, both over EXACTLY K full training steps (forward, backward, gradient reduction, clip, AdamW —
+nothing skipped), bracketed by barrier + synchronize, CUDA events, max over ranks:
   value : the captured step graph replayed back to back with device-resident batches (kernel time)
   e2e   : the public API ``train_step(state, Batch(x, y))`` fed from pinned host memory every step (H2D of x and
           y) with a blocking device→host read of the loss every step — what a user of main.py gets.
 L2 is not flushed explicitly: one step touches ≈1.8 GB of parameters / optimizer state and ≈1.2 GB of
 activations per rank, far more than the 126 MB L2, so nothing survives between iterations (stated in config).
+SM clock / throttle reasons are sampled through NVML every 10 ms during both timed regions.
 """
 from __future__ import annotations
 
@@ -21,12 +31,16 @@ import argparse
 import json
 import os
 import sys
+import threading
+import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-BASELINE_TOKENS_PER_S = {"dp": 27887.0, "tp": 27919.0, "pp": 19978.0}  # BASELINE.md §1 (published logs, n=2, fp32)
+# the reference's published logs (n = 2 GPUs inferred, fp32, hardware unstated, host/data-bound)
+BASELINE_TOKENS_PER_S = {"dp": 27887.0, "dp_weak": 27887.0, "tp": 27919.0, "pp": 19978.0}
+ARM_STRATEGY = {"dp": "dp", "dp_weak": "dp", "tp": "tp", "pp": "pp", "dp_tp": "dp_tp"}
 
 
 def reference_arm(args) -> int:
@@ -48,7 +62,11 @@ def reference_arm(args) -> int:
     return 0
 
 
-def run(args) -> dict | None:
+def run_arm(args, arm: str) -> dict:
+    """Build one strategy on the current world, warm it up, time K steps twice (device-resident and end to end).
+    Every rank returns the same dict (times are max over ranks; losses come from rank 0's view of the global loss)."""
+    import gc
+
     import numpy as np
     import torch
 
@@ -57,45 +75,45 @@ def run(args) -> dict | None:
     from distributed_training_compare_jax_b200.data.fineweb_edu import VOCAB_SIZE, get_batch_iterator
     from distributed_training_compare_jax_b200.models.param_tree import LocalShape
     from distributed_training_compare_jax_b200.ops import native
-    from distributed_training_compare_jax_b200.parallel.mesh import build_mesh, shutdown
-    from distributed_training_compare_jax_b200.parallel.pp import stage_layers
+    from distributed_training_compare_jax_b200.parallel.mesh import build_mesh
+    from distributed_training_compare_jax_b200.parallel.pp import bubble_fraction, stage_layers
     from distributed_training_compare_jax_b200.train.create_train_step import (Batch, create_pp_train_step,
                                                                             create_train_step)
     from distributed_training_compare_jax_b200.train.train import build_state
     from distributed_training_compare_jax_b200.utils.timing import ClockSampler, DeviceTimer
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    if world != args.gpus:
-        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run "
-                         f"--nproc-per-node {args.gpus}")
-    strategy = args.parallel
-    per_rank_batch = args.batch
-    tc = TrainConfig(seed=0, parallel=strategy, batch=per_rank_batch, steps=args.steps, log_every=10 ** 9,
+    strategy = ARM_STRATEGY[arm]
+    weak = arm == "dp_weak" or (arm == "dp_tp")          # batch is per data-parallel rank
+    tc = TrainConfig(seed=0, parallel=strategy, batch=args.batch, steps=args.steps, log_every=10 ** 9,
                      output_dir="outputs/bench", pp_microbatches=args.pp_microbatches, warmup_steps=args.warmup,
-                     global_batch_is_per_device=True, sync_every_step=True, backend=args.backend,
+                     global_batch_is_per_device=weak, sync_every_step=True, backend=args.backend,
                      pp_schedule=args.pp_schedule, fused_comm=not args.no_fused_comm, cuda_graph=not args.no_graph,
                      dp_overlap=not args.no_dp_overlap, tp_fused=args.tp_fused,
-                     tp_seq_parallel=not args.no_tp_seq_parallel, pp_cuda_graph=args.pp_graph)
+                     tp_seq_parallel=not args.no_tp_seq_parallel, pp_cuda_graph=not args.no_pp_graph)
     mc = load_model_config(os.path.join(ROOT, args.model_config), vocab_size=VOCAB_SIZE, parallel=strategy)
     oc = load_optim_config(os.path.join(ROOT, "configs/optim_config.yaml"))
     dp, tp, pp = mesh_shape(tc, world)
-    mesh = build_mesh(dp, tp, pp)
     T = mc.max_seq_len
+    global_batch = args.batch * (dp if weak else 1)
+    if strategy != "pp" and global_batch % dp:
+        raise ValueError(f"global batch {global_batch} is not divisible by {dp} data-parallel ranks")
+    mesh = build_mesh(dp, tp, pp)
     if strategy == "pp":
         layers = stage_layers(mc.n_layers, pp, False)[mesh.pp.rank]
         local = LocalShape(mc, layer_start=layers.start, layer_end=layers.stop, has_embed=mesh.pp.rank == 0,
                            has_head=mesh.pp.rank == pp - 1)
-        global_batch = per_rank_batch
         M = tc.pp_microbatches
         state = build_state(tc, mc, oc, mesh, global_batch // M, M, global_batch * T, local, clip_scope=tc.pp_clip,
                             clip_scale=1.0 / pp, pp_stage_keys=True)
         train_step = create_pp_train_step(M, pp, tc.pp_schedule, cuda_graph=tc.pp_cuda_graph and tc.cuda_graph)
         it = get_batch_iterator(global_batch, T + 1, seed=0)
+        local_batch = global_batch
     else:
-        global_batch = per_rank_batch * dp
+        local_batch = global_batch // dp
         local = LocalShape(mc, tp_rank=mesh.tp.rank, tp_size=tp)
-        chains = args.chains if tp == 1 else 1
-        state = build_state(tc, mc, oc, mesh, per_rank_batch // chains, chains, global_batch * T, local)
+        chains = args.chains if (tp == 1 and local_batch % max(args.chains, 1) == 0) else 1
+        state = build_state(tc, mc, oc, mesh, local_batch // chains, chains, global_batch * T, local)
         train_step = create_train_step(strategy, cuda_graph=tc.cuda_graph)
         it = get_batch_iterator(global_batch, T + 1, seed=0, rank=mesh.dp.rank, world=dp)
     tokens_per_step = global_batch * T
@@ -106,8 +124,9 @@ def run(args) -> dict | None:
         return Batch(x=np.ascontiguousarray(a[:, :-1]), y=np.ascontiguousarray(a[:, 1:]))
 
     # ---- warm-up: W real training steps through the public API (also triggers graph capture) ----
+    warm = max(args.warmup, 4)   # eager, eager, capture + replay, replay
     loss = None
-    for _ in range(max(args.warmup, 3)):
+    for _ in range(warm):
         state, loss = train_step(state, host_batch(), None)
     first_loss = float(loss)
     if dev.type == "cuda":
@@ -148,39 +167,87 @@ def run(args) -> dict | None:
     gpu_launches = native.launches() - launches_before
 
     opt = state.optimizer
+    eng = state.engine
     comm_path = {"dp": ("symmetric-memory reduce-scatter + sharded AdamW + all-gather ("
                         + ("multimem/NVLS" if getattr(opt, "uses_multicast", False) else "peer loads/stores") + ")")
                  if type(opt).__name__ == "FusedShardedStep" else ("NCCL bucketed all-reduce" if dp > 1 else "none"),
                  "tp": ("sequence-parallel: GEMM-epilogue reduce-scatter (P2P stores) + LayerNorm all-gather ("
-                        + ("multimem.st" if state.engine.sp.use_mc else "peer stores") + ")"
-                        if hasattr(state.engine, "sp") else
-                        "GEMM epilogue multimem.red all-reduce" if getattr(state.engine, "tp_hooks", None) is not None
+                        + ("multimem.st" if eng.sp.use_mc else "peer stores") + ")"
+                        if hasattr(eng, "sp") else
+                        "GEMM epilogue multimem.red all-reduce" if getattr(eng, "tp_hooks", None) is not None
                         else ("GEMM + NCCL all-reduce" if tp > 1 else "none")),
-                 "pp": "NCCL send/recv, one communicator per direction" if pp > 1 else "none"}
+                 "pp": ("NCCL send/recv, one communicator per direction"
+                        + (", one CUDA graph per (F|B, microbatch)" if tc.pp_cuda_graph and tc.cuda_graph else ", eager launches")
+                        ) if pp > 1 else "none"}
     tps = tokens_per_step * args.steps / (ms_dev / 1e3)
     tps_e2e = tokens_per_step * args.steps / (ms_e2e / 1e3)
-    # bytes actually copied host->device per step over the whole job: every DP/TP rank stages its own x and y;
-    # in PP only the first stage copies x and only the last stage copies y
-    h2d = 2 * per_rank_batch * T * 4 * (1 if strategy == "pp" else world)
-    result = {
-        "metric": "training throughput, tokens/s (whole job), " + strategy.upper(),
-        "value": tps, "unit": "tokens/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-        "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak" if strategy == "dp" else "strong",
-        "vs_baseline": tps / BASELINE_TOKENS_PER_S[strategy] if strategy in BASELINE_TOKENS_PER_S else None,
+    # bytes actually copied host->device per step over the whole job: every DP/TP rank stages its own x and y
+    # (DP: its slice of the global batch; TP: the replicated batch); in PP every stage stages x and y of the whole batch
+    # into pinned memory but only the first stage copies x and only the last stage copies y
+    h2d = 2 * local_batch * T * 4 * (1 if strategy == "pp" else world)
+    res = {
+        "metric": "training throughput, tokens/s (whole job), " + arm.upper(),
+        "value": tps, "unit": "tokens/s", "n_gpus": world, "steps": args.steps, "warmup": warm,
+        "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak" if weak else "strong",
+        "vs_baseline": tps / BASELINE_TOKENS_PER_S[arm] if arm in BASELINE_TOKENS_PER_S else None,
+        "vs_baseline_note": "published reference log: n = 2 GPUs (inferred), fp32, global batch 8, host/data-bound, "
+                            "hardware unstated (BASELINE.md §1) — context, not a like-for-like ratio",
         "dtype": "bf16", "data": "synthetic FineWeb-edu-shaped tokens (Zipf + bigram), random-init weights",
         "impl": "native",
         "config": {"model": f"GPT {mc.n_layers}L/d{mc.d_model}/h{mc.n_heads}/ff{mc.d_ff}/seq{T}/vocab{mc.vocab_size} "
                             f"({args.model_config})", "global_batch": global_batch, "seq_len": T,
-                   "parallelism": f"{strategy}{world}", "optimizer": "clip_by_global_norm(1.0)+AdamW(3e-4, wd 0.1)",
+                   "parallelism": f"{strategy}{world}" if strategy != "dp_tp" else f"dp{dp}xtp{tp}",
+                   "batch_semantics": "batch 8 per data-parallel rank" if weak else "global batch 8 (reference semantics)",
+                   "optimizer": "clip_by_global_norm(1.0)+AdamW(3e-4, wd 0.1)",
                    "l2": "no explicit flush: per-step working set (~3 GB/rank) >> 126 MB L2",
-                   "backend": state.engine.backend, "cuda_graph": bool(tc.cuda_graph and state.engine.backend == "native"),
-                   "fused_comm": tc.fused_comm, "comm_path": comm_path},
+                   "backend": eng.backend, "cuda_graph": bool(tc.cuda_graph and eng.backend == "native"),
+                   "fused_comm": tc.fused_comm, "comm_path": comm_path,
+                   "wgrad_grouped": bool(getattr(eng, "wgrad_grouped", False))},
         "e2e": {"value": tps_e2e, "unit": "tokens/s", "ms_per_step": ms_e2e / args.steps,
                 "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4 * world},
         "gpu_launches": int(gpu_launches),  # rank 0, both timed regions (2K steps)
         "clocks": clocks.summary(), "loss_first": first_loss, "loss_last": last,
     }
-    return result if mesh.is_main else None
+    if strategy == "pp":
+        res["config"]["pp_microbatches"] = tc.pp_microbatches
+        res["config"]["pp_schedule"] = tc.pp_schedule
+        res["config"]["bubble_fraction"] = bubble_fraction(pp, tc.pp_microbatches)
+    # release the arm: graphs first (they reference NCCL work), then the engine / symmetric buffers
+    del train_step, state, opt, eng, dev_batches, pinned
+    gc.collect()
+    if dev.type == "cuda":
+        torch.cuda.synchronize()
+        torch.cuda.empty_cache()
+    mesh.barrier()
+    return res
+
+
+class _Watchdog:
+    """Per-arm time limit.  A hung collective (a rank that never arrives) would otherwise hang the whole benchmark and
+    lose the arms that already finished: on expiry rank 0 prints the line assembled so far and every rank exits."""
+
+    def __init__(self, emit, fail_marker: str):
+        self.emit, self.deadline, self.arm, self.fail_marker = emit, None, "", fail_marker
+        self.t = threading.Thread(target=self._run, daemon=True)
+        self.t.start()
+
+    def arm_start(self, arm: str, limit_s: float) -> None:
+        self.arm, self.deadline = arm, time.time() + limit_s
+
+    def arm_done(self) -> None:
+        self.deadline = None
+
+    def _run(self) -> None:
+        while True:
+            time.sleep(0.5)
+            d = self.deadline
+            peer_failed = d is not None and os.path.exists(self.fail_marker)
+            if peer_failed or (d is not None and time.time() > d):
+                why = "a peer rank failed (see stderr)" if peer_failed else "exceeded its time limit (hung collective?)"
+                self.emit(f"arm `{self.arm}`: {why}", self.arm)
+                sys.stdout.flush()
+                sys.stderr.flush()
+                os._exit(0)
 
 
 def main() -> int:
@@ -189,8 +256,12 @@ def main() -> int:
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
-    ap.add_argument("--parallel", default="dp", choices=["dp", "tp", "pp", "dp_tp"])
-    ap.add_argument("--batch", type=int, default=8, help="batch per data-parallel rank (train_config_*.yaml: 8)")
+    ap.add_argument("--arms", default="", help="comma list of dp,dp_weak,tp,pp,dp_tp (default: all four reference "
+                    "arms when N > 1, dp when N = 1); the first one is the headline")
+    ap.add_argument("--parallel", default="", choices=["", "dp", "dp_weak", "tp", "pp", "dp_tp"],
+                    help="run ONE arm only (tools); `dp` = global batch 8, `dp_weak` = batch 8 per rank")
+    ap.add_argument("--batch", type=int, default=8, help="train_config_*.yaml: batch 8")
+    ap.add_argument("--arm-timeout", type=float, default=240.0, help="seconds per arm before the watchdog gives up")
     ap.add_argument("--pp-microbatches", type=int, default=2)
     ap.add_argument("--pp-schedule", default="gpipe")
     ap.add_argument("--model-config", default="configs/model_config.yaml")
@@ -202,8 +273,8 @@ def main() -> int:
                     "GEMM-epilogue reduce-scatter + LayerNorm all-gather")
     ap.add_argument("--no-tp-seq-parallel", action="store_true", help="TP: replicated activations, GEMM + NCCL all-reduce")
     ap.add_argument("--no-graph", action="store_true")
-    ap.add_argument("--pp-graph", action="store_true",
-                    help="PP: one CUDA graph per (forward | backward, microbatch) of a stage (experimental)")
+    ap.add_argument("--pp-graph", action="store_true", help="(default) PP: one CUDA graph per (F | B, microbatch) of a stage")
+    ap.add_argument("--no-pp-graph", action="store_true", help="PP: eager kernel launches from Python")
     ap.add_argument("--chains", type=int, default=1, help="concurrent chains the local batch is split into (DP)")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -220,9 +291,84 @@ def main() -> int:
     os.environ.setdefault("RANK", "0")
     os.environ.setdefault("WORLD_SIZE", "1")
     os.environ.setdefault("LOCAL_RANK", "0")
-    res = run(args)  # engine, CUDA graph and communicator users are released when run() returns
-    if res is not None:
-        print(json.dumps(res), flush=True)
+    world = int(os.environ["WORLD_SIZE"])
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run "
+                         f"--nproc-per-node {args.gpus}")
+    rank0 = int(os.environ["RANK"]) == 0
+    if args.parallel:
+        arms = [args.parallel]
+    elif args.arms:
+        arms = [a.strip() for a in args.arms.split(",") if a.strip()]
+    else:
+        arms = ["dp"] if world == 1 else ["dp", "dp_weak", "tp", "pp"]
+    for a in arms:
+        if a not in ARM_STRATEGY:
+            raise SystemExit(f"unknown arm `{a}`")
+
+    headline: dict = {}
+    extra: dict = {}
+    printed = threading.Event()
+
+    def emit(error: str | None = None, failed_arm: str = "") -> None:
+        if printed.is_set():
+            return
+        printed.set()
+        if error and failed_arm:
+            extra.setdefault(failed_arm, {"error": error})
+        if rank0:
+            line = dict(headline) if headline else {"metric": "training throughput, tokens/s (whole job), " + arms[0].upper(),
+                                                    "value": None, "error": error or "headline arm did not finish"}
+            if extra:
+                line["extra"] = extra
+            line["arms"] = arms
+            print(json.dumps(line), flush=True)
+
+    # a rank that fails drops this marker; the watchdogs of its peers (stuck in a collective waiting for it) see it,
+    # rank 0 prints what has been measured so far, and everybody leaves
+    fail_marker = f"/tmp/dtc_bench_failed_{os.getppid()}_{os.environ.get('MASTER_PORT', '0')}"
+    dog = _Watchdog(emit, fail_marker)
+    poisoned = ""
+    for i, arm in enumerate(arms):
+        if poisoned:
+            extra[arm] = {"error": "skipped: " + poisoned}
+            continue
+        dog.arm_start(arm, args.arm_timeout)
+        try:
+            res = run_arm(args, arm)
+            if i == 0:
+                headline.update(res)
+            else:
+                extra[arm] = {k: res[k] for k in ("value", "unit", "ms_per_step", "scaling", "vs_baseline", "e2e",
+                                                  "gpu_launches", "loss_first", "loss_last", "clocks")}
+                extra[arm]["config"] = {k: res["config"][k] for k in res["config"]
+                                        if k in ("global_batch", "parallelism", "batch_semantics", "comm_path",
+                                                 "pp_microbatches", "pp_schedule", "bubble_fraction", "cuda_graph")}
+        except BaseException as e:  # noqa: BLE001 — a failed arm must not lose the arms that finished
+            if isinstance(e, (KeyboardInterrupt, SystemExit)):
+                raise
+            import traceback
+            traceback.print_exc()
+            msg = f"{type(e).__name__}: {str(e).splitlines()[0] if str(e) else ''}"[:300]
+            if i == 0:
+                headline.update({"metric": "training throughput, tokens/s (whole job), " + arm.upper(), "value": None,
+                                 "error": msg})
+            else:
+                extra[arm] = {"error": msg}
+            # a failed rank leaves its peers inside a collective and (for CUDA faults) a dead context: stop here
+            poisoned = f"arm `{arm}` failed ({msg})"
+            try:
+                open(fail_marker, "w").write(msg)
+            except OSError:
+                pass
+            emit()
+            sys.stdout.flush()
+            sys.stderr.flush()
+            time.sleep(3.0)   # let the peers' watchdogs notice the marker and rank 0 print before the launcher reacts
+            os._exit(0 if (headline.get("value") or not rank0) else 1)
+        finally:
+            dog.arm_done()
+    emit()
     import gc
     gc.collect()
     from distributed_training_compare_jax_b200.parallel.mesh import shutdown
