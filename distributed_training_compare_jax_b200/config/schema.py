@@ -77,6 +77,7 @@ class TrainConfig:
     dp_overlap: bool = True           # fused DP: reduce-scatter each layer's gradient bucket during the backward pass
     tp_seq_parallel: bool = True      # TP: row-sharded residual stream, GEMM-epilogue reduce-scatter + LayerNorm all-gather (parallel/tp_sp.py; +22 % at TP2 vs GEMM + NCCL all-reduce, falls back when batch % tp != 0)
     pp_cuda_graph: bool = True        # PP: one CUDA graph per (forward | backward, microbatch) of a stage (2 GPUs: 7.49 -> 5.59 ms/step)
+    tp_resync_every: int = 128        # TP: every N steps re-broadcast the REPLICATED leaves (embeddings, LayerNorm, row biases) and their Adam moments from tp-rank 0: their gradients are accumulated with fp32 atomics whose order differs per rank, so the copies would otherwise drift apart bit by bit (the reference's GSPMD keeps them identical); 0 = never
     micro_chains: int = 1             # DP/TP: split the local batch into this many concurrently executed chains
     fused_comm: bool = True           # fused compute+collective kernels over symmetric memory (vs plain NCCL)
     global_batch_is_per_device: bool = False  # weak scaling: `batch` is per data-parallel rank

@@ -383,6 +383,231 @@ flash_attn_fwd_kv64_kernel(const __grid_constant__ CUtensorMap tm_q, const __gri
   }
 }
 
+// Forward, software-pipelined (default).  Same math as the kernels above; what changes is who waits for whom:
+//   * warp 4 is a dedicated issue warp (one elected lane): TMA loads of Q / K_j / V_j and every tcgen05.mma;
+//   * warps 0..3 are the softmax warps (thread r owns query row r);
+//   * S is double-buffered in tensor memory and Q K_{j+1}^T is issued BEFORE the softmax of block j starts, so the
+//     tensor-core latency of the next block hides behind the exp2 work of this one;
+//   * P is double-buffered in shared memory and the P V product of block j is folded into the register accumulator one
+//     block late — O = (O + PV_{j-1}) * alpha_j — so no thread ever waits for the MMA it has just triggered.
+// The only per-block synchronisation left is mbarrier traffic between the softmax threads and the issue lane (no
+// __syncthreads in the loop).  Softmax inner loop: FMNMX, FFMA, MUFU.EX2, FADD and half a CVT per element; the causal
+// predicate is evaluated on the (at most two) diagonal blocks only.
+// TMEM: S 2 x 64 columns, PV 2 x HD columns -> 256 allocated -> two CTAs per SM.
+DTC_DEVICE float ex2_ftz(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+template <int HD>
+__global__ void __launch_bounds__(160, HD == 32 ? 2 : 1)
+flash_attn_fwd_pipe_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
+                           const __grid_constant__ CUtensorMap tm_v, bf16* __restrict__ out, long long ldo,
+                           float* __restrict__ lse2_out, int T, int H, float scale_log2) {
+  using C = AttnCfg<HD>;
+  constexpr int KVB = 64;
+  constexpr int KV_BYTES = KVB * C::ROW_BYTES;
+  constexpr int P64_BYTES = ATT_BLK * 128;  // [128 x 64] bf16, one K-major 128B-swizzled block
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* sQ = smem;
+  uint8_t* sP = sQ + C::TILE_BYTES;      // 2 buffers
+  uint8_t* sK = sP + 2 * P64_BYTES;      // 2 stages
+  uint8_t* sV = sK + 2 * KV_BYTES;       // 2 stages
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sV + 2 * KV_BYTES);
+  uint64_t* bar_q = bars;
+  uint64_t* bar_k = bars + 1;  // [2] K_j landed
+  uint64_t* bar_v = bars + 3;  // [2] V_j landed
+  uint64_t* bar_s = bars + 5;  // [2] S_j complete in tensor memory
+  uint64_t* bar_p = bars + 7;  // [2] P_j written by the 4 softmax warps (and S_j / PV_{j-1} consumed)
+  uint64_t* bar_o = bars + 9;  // [2] PV_j complete in tensor memory
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 11);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int qblk = gridDim.x - 1 - blockIdx.x, h = blockIdx.y, b = blockIdx.z;  // heaviest query blocks first
+  const int row0 = b * T + qblk * ATT_BLK;
+  const int nkv = 2 * (qblk + 1);  // causal: 64-key blocks 0 .. 2*qblk+1
+
+  if (tid == 0) {
+    tma_prefetch_desc(&tm_q);
+    tma_prefetch_desc(&tm_k);
+    tma_prefetch_desc(&tm_v);
+    mbar_init(bar_q, 1);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&bar_k[s], 1);
+      mbar_init(&bar_v[s], 1);
+      mbar_init(&bar_s[s], 1);
+      mbar_init(&bar_p[s], 4);  // one arrival per softmax warp
+      mbar_init(&bar_o[s], 1);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 4) {
+    tmem_alloc(tmem_ptr_smem, 256);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+  pdl_launch_dependents();
+  pdl_wait();
+  // columns: S0 [0,64) S1 [64,128) PV0 [128,128+HD) PV1 [128+HD,128+2HD)
+  constexpr uint32_t idesc_s = make_idesc_bf16(128, KVB, 0, 0);
+  constexpr uint32_t idesc_pv = make_idesc_bf16(128, HD, 0, 1);
+
+  if (warp == 4) {
+    // ------------------------------ issue warp ------------------------------
+    if (elect_one()) {
+      auto load_k = [&](int j) {
+        mbar_expect_tx(&bar_k[j & 1], KV_BYTES);
+        tma_load_2d(sK + (j & 1) * KV_BYTES, &tm_k, &bar_k[j & 1], h * HD, b * T + j * KVB);
+      };
+      auto load_v = [&](int j) {
+        mbar_expect_tx(&bar_v[j & 1], KV_BYTES);
+        tma_load_2d(sV + (j & 1) * KV_BYTES, &tm_v, &bar_v[j & 1], h * HD, b * T + j * KVB);
+      };
+      auto issue_qk = [&](int j) {  // S[j&1] = Q K_j^T
+        mbar_wait(&bar_k[j & 1], (j >> 1) & 1);
+        tc_fence_after();
+        const uint32_t aq = smem_u32(sQ), ak = smem_u32(sK + (j & 1) * KV_BYTES);
+#pragma unroll
+        for (int k = 0; k < HD / 16; ++k)
+          umma_bf16(tmem_base + (j & 1) * KVB, make_smem_desc(aq + k * 32, 16, C::SBO, C::SWZ),
+                    make_smem_desc(ak + k * 32, 16, C::SBO, C::SWZ), idesc_s, k > 0);
+        umma_commit(&bar_s[j & 1]);
+      };
+      mbar_expect_tx(bar_q, C::TILE_BYTES);
+      tma_load_2d(sQ, &tm_q, bar_q, h * HD, row0);
+      load_k(0);
+      load_v(0);
+      load_k(1);  // nkv >= 2 always
+      load_v(1);
+      mbar_wait(bar_q, 0);
+      issue_qk(0);
+      for (int j = 0; j < nkv; ++j) {
+        const int st = j & 1;
+        const uint32_t ph = (j >> 1) & 1;
+        if (j + 1 < nkv) issue_qk(j + 1);  // S[(j+1)&1] was consumed before bar_p of block j-1 completed (waited below)
+        // K stage `st` is free once Q K_j^T has completed: fetch K_{j+2} into it
+        if (j + 2 < nkv) {
+          mbar_wait(&bar_s[st], ph);
+          load_k(j + 2);
+        }
+        mbar_wait(&bar_p[st], ph);  // P_j is in shared memory; the softmax warps have also read S_j and PV_{j-1}
+        mbar_wait(&bar_v[st], ph);
+        tc_fence_after();
+        const uint32_t ap = smem_u32(sP + st * P64_BYTES), av = smem_u32(sV + st * KV_BYTES);
+#pragma unroll
+        for (int k = 0; k < KVB / 16; ++k)
+          umma_bf16(tmem_base + 2 * KVB + st * HD, make_smem_desc(ap + k * 32, 16, 1024, SWZ_128B),
+                    make_smem_desc(av + k * 16 * C::ROW_BYTES, 16, C::SBO, C::SWZ), idesc_pv, k > 0);
+        umma_commit(&bar_o[st]);
+        // V stage of block j-1 is free once P V_{j-1} has completed: fetch V_{j+1} into it
+        if (j >= 1 && j + 1 < nkv) {
+          mbar_wait(&bar_o[st ^ 1], ((j - 1) >> 1) & 1);
+          load_v(j + 1);
+        }
+      }
+    }
+  } else {
+    // ------------------------------ softmax warps (thread = query row) ------------------------------
+    const int qrow = qblk * ATT_BLK + tid;  // position of this thread's query inside the sequence
+    const uint32_t lane_sel = (uint32_t)(warp * 32) << 16;
+    float o_acc[HD];
+#pragma unroll
+    for (int e = 0; e < HD; ++e) o_acc[e] = 0.f;
+    float m_run = -INFINITY, l_run = 0.f;
+
+    for (int j = 0; j < nkv; ++j) {
+      const int st = j & 1;
+      const uint32_t ph = (j >> 1) & 1;
+      mbar_wait(&bar_s[st], ph);
+      tc_fence_after();
+      uint32_t r[64];
+      tmem_ld_32x32b_x32(tmem_base + st * KVB + lane_sel, r);
+      tmem_ld_32x32b_x32(tmem_base + st * KVB + lane_sel + 32, r + 32);
+      tmem_ld_wait();
+      const int lim = qrow - j * KVB;  // key column c of this block is visible iff c <= lim
+      if (lim < KVB - 1) {             // diagonal block: mask (uniform per warp except inside the two diagonal warps)
+#pragma unroll
+        for (int i = 0; i < 64; ++i)
+          if (i > lim) r[i] = 0xff800000u;  // -inf
+      }
+      float mx = __uint_as_float(r[0]);
+#pragma unroll
+      for (int i = 1; i < 64; ++i) mx = fmaxf(mx, __uint_as_float(r[i]));
+      // m_run is finite from block 0 on (key 0 is visible to every query); a fully masked block leaves it unchanged
+      const float m_new = fmaxf(m_run, mx * scale_log2);
+      const float alpha = ex2_ftz(m_run - m_new);
+      float l_blk = 0.f;
+      uint8_t* prow = sP + st * P64_BYTES;
+#pragma unroll
+      for (int g = 0; g < 8; ++g) {
+        float p[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          p[i] = ex2_ftz(fmaf(__uint_as_float(r[g * 8 + i]), scale_log2, -m_new));
+          l_blk += p[i];
+        }
+        *reinterpret_cast<uint4*>(prow + swizzle_offset<3>(tid * 128 + g * 16)) =
+            make_uint4(pack_bf16x2(p[0], p[1]), pack_bf16x2(p[2], p[3]), pack_bf16x2(p[4], p[5]), pack_bf16x2(p[6], p[7]));
+      }
+      l_run = l_run * alpha + l_blk;
+      m_run = m_new;
+      // fold the product of the PREVIOUS block (its MMA was issued a whole softmax ago) before P_j is published:
+      // bar_p also tells the issue warp that PV[(j-1)&1] may be overwritten by block j+1
+      if (j >= 1) {
+        mbar_wait(&bar_o[st ^ 1], ((j - 1) >> 1) & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int c = 0; c < HD / 32; ++c) {
+          uint32_t pv[32];
+          tmem_ld_32x32b_x32(tmem_base + 2 * KVB + (st ^ 1) * HD + lane_sel + c * 32, pv);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) o_acc[c * 32 + i] = (o_acc[c * 32 + i] + __uint_as_float(pv[i])) * alpha;
+        }
+      }
+      fence_proxy_async_smem();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bar_p[st]);
+    }
+    {  // last block's product
+      const int jl = nkv - 1;
+      mbar_wait(&bar_o[jl & 1], (jl >> 1) & 1);
+      tc_fence_after();
+      const float inv_l = 1.f / l_run;
+      bf16* orow = out + (long long)(row0 + tid) * ldo + h * HD;
+#pragma unroll
+      for (int c = 0; c < HD / 32; ++c) {
+        uint32_t pv[32];
+        tmem_ld_32x32b_x32(tmem_base + 2 * KVB + (jl & 1) * HD + lane_sel + c * 32, pv);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) o_acc[c * 32 + i] = (o_acc[c * 32 + i] + __uint_as_float(pv[i])) * inv_l;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          const int e = c * 32 + g * 8;
+          *reinterpret_cast<uint4*>(orow + e) =
+              make_uint4(pack_bf16x2(o_acc[e], o_acc[e + 1]), pack_bf16x2(o_acc[e + 2], o_acc[e + 3]),
+                         pack_bf16x2(o_acc[e + 4], o_acc[e + 5]), pack_bf16x2(o_acc[e + 6], o_acc[e + 7]));
+        }
+      }
+      lse2_out[((long long)b * H + h) * T + qblk * ATT_BLK + tid] = m_run + log2f(l_run);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 256);
+  }
+}
+
 // delta[b,h,t] = sum_d dO[b,t,h,d] * O[b,t,h,d]   (one thread per 8 columns, HD/8 threads per (row, head))
 template <int HD>
 __global__ void attn_bwd_prep_kernel(const bf16* __restrict__ o, long long ldo, const bf16* __restrict__ d_o,
@@ -843,6 +1068,256 @@ flash_attn_bwd_regacc_kernel(const __grid_constant__ CUtensorMap tm_q, const __g
   }
 }
 
+DTC_DEVICE void red_add_v4_f32_attn(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+// Backward, software-pipelined (head_dim 32, default).  CTA = one (batch, head, 128-key block j), looping over the query
+// blocks i >= j as before, but
+//   * scores are kept in the S = Q_i K_j^T orientation (thread r owns QUERY row r), so lse2 / delta are two per-thread
+//     scalars instead of two shared-memory loads per element;
+//   * 8 softmax warps: warps 0..3 take key columns [0,64), warps 4..7 take [64,128) of the same rows — twice the warps
+//     per scheduler for the exp2 / FMA work that bounds this kernel;
+//   * warp 8 is the issue warp (one elected lane): all TMA loads and tcgen05.mma.  S_{i+1} / dP_{i+1} are issued as soon as
+//     every softmax warp has pulled S_i / dP_i into registers, i.e. they run UNDER the element-wise work of block i;
+//   * P / dS tiles are double-buffered in shared memory, so the three product GEMMs of block i (dV += P^T dO_i,
+//     dK += dS^T Q_i, dQ_i = dS K_j) overlap the element-wise work of block i+1;
+//   * dK / dV accumulate in tensor memory across i (no per-iteration read-back); dQ_i is double-buffered in tensor
+//     memory and pushed to global (fp32 red.add) one block late, when its MMAs are certainly complete.
+// TMEM columns: S [0,128) dP [128,256) dV [256,288) dK [288,320) dQ0 [320,352) dQ1 [352,384) -> 512 allocated, 1 CTA / SM.
+template <int HD>
+__global__ void __launch_bounds__(288, 1)
+flash_attn_bwd_pipe_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
+                           const __grid_constant__ CUtensorMap tm_v, const __grid_constant__ CUtensorMap tm_do,
+                           const float* __restrict__ lse2, const float* __restrict__ delta, float* __restrict__ dq_accum,
+                           long long lddq, bf16* __restrict__ dk, bf16* __restrict__ dv, long long lddkv, int T, int H,
+                           float scale, float scale_log2) {
+  using C = AttnCfg<HD>;
+  static_assert(HD == 32, "the pipelined backward is laid out for head_dim 32");
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* sP = smem;                      // 2 buffers of [128 q x 128 k] bf16
+  uint8_t* sDS = sP + 2 * C::P_BYTES;      // 2 buffers
+  uint8_t* sK = sDS + 2 * C::P_BYTES;
+  uint8_t* sV = sK + C::TILE_BYTES;
+  uint8_t* sQ = sV + C::TILE_BYTES;        // 2 stages
+  uint8_t* sDO = sQ + 2 * C::TILE_BYTES;   // 2 stages
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sDO + 2 * C::TILE_BYTES);
+  uint64_t* bar_kv = bars;
+  uint64_t* bar_ld = bars + 1;  // [2] Q_i and dO_i landed
+  uint64_t* bar_s = bars + 3;   //     S_i / dP_i complete
+  uint64_t* bar_c = bars + 4;   //     S_i / dP_i pulled into registers by all 8 softmax warps
+  uint64_t* bar_p = bars + 5;   // [2] P_i / dS_i written (and dQ_{i-1} read out)
+  uint64_t* bar_d = bars + 7;   // [2] products of block i complete
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 9);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int jblk = blockIdx.x, h = blockIdx.y, b = blockIdx.z;  // key block 0 has the most query blocks: heaviest first
+  const int nblk = T / ATT_BLK;
+  const int n_it = nblk - jblk;
+  const int kv_row0 = b * T + jblk * ATT_BLK;
+  const long long stat_base = ((long long)b * H + h) * T;
+
+  if (tid == 0) {
+    tma_prefetch_desc(&tm_q);
+    tma_prefetch_desc(&tm_k);
+    tma_prefetch_desc(&tm_v);
+    tma_prefetch_desc(&tm_do);
+    mbar_init(bar_kv, 1);
+    mbar_init(bar_s, 1);
+    mbar_init(bar_c, 8);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&bar_ld[s], 1);
+      mbar_init(&bar_p[s], 8);
+      mbar_init(&bar_d[s], 1);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 8) {
+    tmem_alloc(tmem_ptr_smem, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+  pdl_launch_dependents();
+  pdl_wait();
+  const uint32_t tm_s = tmem_base, tm_dp = tmem_base + 128, tm_dv = tmem_base + 256, tm_dk = tmem_base + 256 + HD,
+                 tm_dq = tmem_base + 256 + 2 * HD;  // two buffers of HD columns
+
+  if (warp == 8) {
+    // ------------------------------ issue warp ------------------------------
+    if (elect_one()) {
+      constexpr uint32_t idesc_kk = make_idesc_bf16(128, 128, 0, 0);
+      constexpr uint32_t idesc_kn = make_idesc_bf16(128, HD, 0, 1);
+      constexpr uint32_t idesc_nn = make_idesc_bf16(128, HD, 1, 1);
+      auto load_qdo = [&](int it) {
+        const int st = it & 1;
+        mbar_expect_tx(&bar_ld[st], 2 * C::TILE_BYTES);
+        tma_load_2d(sQ + st * C::TILE_BYTES, &tm_q, &bar_ld[st], h * HD, b * T + (jblk + it) * ATT_BLK);
+        tma_load_2d(sDO + st * C::TILE_BYTES, &tm_do, &bar_ld[st], h * HD, b * T + (jblk + it) * ATT_BLK);
+      };
+      auto issue_scores = [&](int it) {  // S = Q_i K_j^T, dP = dO_i V_j^T
+        const int st = it & 1;
+        mbar_wait(&bar_ld[st], (it >> 1) & 1);
+        tc_fence_after();
+        const uint32_t ak = smem_u32(sK), av = smem_u32(sV), aq = smem_u32(sQ + st * C::TILE_BYTES),
+                       ado = smem_u32(sDO + st * C::TILE_BYTES);
+#pragma unroll
+        for (int k = 0; k < HD / 16; ++k)
+          umma_bf16(tm_s, make_smem_desc(aq + k * 32, 16, C::SBO, C::SWZ), make_smem_desc(ak + k * 32, 16, C::SBO, C::SWZ),
+                    idesc_kk, k > 0);
+#pragma unroll
+        for (int k = 0; k < HD / 16; ++k)
+          umma_bf16(tm_dp, make_smem_desc(ado + k * 32, 16, C::SBO, C::SWZ), make_smem_desc(av + k * 32, 16, C::SBO, C::SWZ),
+                    idesc_kk, k > 0);
+        umma_commit(bar_s);
+      };
+      mbar_expect_tx(bar_kv, 2 * C::TILE_BYTES);
+      tma_load_2d(sK, &tm_k, bar_kv, h * HD, kv_row0);
+      tma_load_2d(sV, &tm_v, bar_kv, h * HD, kv_row0);
+      load_qdo(0);
+      if (n_it > 1) load_qdo(1);
+      mbar_wait(bar_kv, 0);
+      issue_scores(0);
+      for (int it = 0; it < n_it; ++it) {
+        const int st = it & 1;
+        const uint32_t ph = (it >> 1) & 1;
+        // S_it / dP_it are in registers everywhere: the tensor cores may start on block it+1 under the exp2 work
+        mbar_wait(bar_c, it & 1);
+        if (it + 1 < n_it) issue_scores(it + 1);
+        // P_it / dS_it are in shared memory (and dQ buffer st was read out two blocks ago)
+        mbar_wait(&bar_p[st], ph);
+        tc_fence_after();
+        const uint32_t apt = smem_u32(sP + st * C::P_BYTES), adst = smem_u32(sDS + st * C::P_BYTES),
+                       aq = smem_u32(sQ + st * C::TILE_BYTES), ado = smem_u32(sDO + st * C::TILE_BYTES), ak = smem_u32(sK);
+        // dV += P^T dO_i ; dK += dS^T Q_i : A = the [q x k] tile read MN-major (M = keys contiguous, 16 query rows per step)
+#pragma unroll
+        for (int k = 0; k < ATT_BLK / 16; ++k)
+          umma_bf16(tm_dv, make_smem_desc(apt + k * 2048, ATT_BLK * 128, 1024, SWZ_128B),
+                    make_smem_desc(ado + k * 16 * C::ROW_BYTES, 16, C::SBO, C::SWZ), idesc_nn, (it > 0 || k > 0) ? 1u : 0u);
+#pragma unroll
+        for (int k = 0; k < ATT_BLK / 16; ++k)
+          umma_bf16(tm_dk, make_smem_desc(adst + k * 2048, ATT_BLK * 128, 1024, SWZ_128B),
+                    make_smem_desc(aq + k * 16 * C::ROW_BYTES, 16, C::SBO, C::SWZ), idesc_nn, (it > 0 || k > 0) ? 1u : 0u);
+        // dQ_i = dS K_j : A = the same tile K-major (two 64-key blocks), B = K_j MN-major
+#pragma unroll
+        for (int k = 0; k < ATT_BLK / 16; ++k) {
+          const uint32_t a_off = (k >> 2) * (ATT_BLK * 128) + (k & 3) * 32;
+          umma_bf16(tm_dq + st * HD, make_smem_desc(adst + a_off, 16, 1024, SWZ_128B),
+                    make_smem_desc(ak + k * 16 * C::ROW_BYTES, 16, C::SBO, C::SWZ), idesc_kn, k > 0);
+        }
+        umma_commit(&bar_d[st]);
+        // Q_it / dO_it were operands of these products: their stage is free once they complete
+        if (it + 2 < n_it) {
+          mbar_wait(&bar_d[st], ph);
+          load_qdo(it + 2);
+        }
+      }
+    }
+  } else {
+    // ------------------------------ softmax warps ------------------------------
+    const int row = (warp & 3) * 32 + lane;  // query row inside the block (TMEM lane)
+    const int gq = warp >> 2;                // key-column half handled by this warp
+    const uint32_t lane_sel = (uint32_t)((warp & 3) * 32) << 16;
+    for (int it = 0; it < n_it; ++it) {
+      const int st = it & 1;
+      const int i = jblk + it;
+      const float lse_r = lse2[stat_base + i * ATT_BLK + row];
+      const float delta_r = delta[stat_base + i * ATT_BLK + row];
+      mbar_wait(bar_s, it & 1);
+      tc_fence_after();
+      uint32_t rs[64], rp[64];
+      tmem_ld_32x32b_x32(tm_s + lane_sel + gq * 64, rs);
+      tmem_ld_32x32b_x32(tm_s + lane_sel + gq * 64 + 32, rs + 32);
+      tmem_ld_32x32b_x32(tm_dp + lane_sel + gq * 64, rp);
+      tmem_ld_32x32b_x32(tm_dp + lane_sel + gq * 64 + 32, rp + 32);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_c);
+      if (it == 0) {  // diagonal block (i == j): key column c is visible to query row r iff c <= r
+        const int lim = row - gq * 64;
+#pragma unroll
+        for (int e = 0; e < 64; ++e)
+          if (e > lim) rs[e] = 0xff800000u;  // -inf -> P = 0
+      }
+      uint8_t* pbuf = sP + st * C::P_BYTES;
+      uint8_t* dsbuf = sDS + st * C::P_BYTES;
+#pragma unroll
+      for (int g = 0; g < 8; ++g) {
+        float p[8], ds[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          p[e] = ex2_ftz(fmaf(__uint_as_float(rs[g * 8 + e]), scale_log2, -lse_r));
+          ds[e] = p[e] * (__uint_as_float(rp[g * 8 + e]) - delta_r);
+        }
+        const uint32_t off = p_tile_offset(row, gq * 8 + g);
+        *reinterpret_cast<uint4*>(pbuf + off) =
+            make_uint4(pack_bf16x2(p[0], p[1]), pack_bf16x2(p[2], p[3]), pack_bf16x2(p[4], p[5]), pack_bf16x2(p[6], p[7]));
+        *reinterpret_cast<uint4*>(dsbuf + off) = make_uint4(pack_bf16x2(ds[0], ds[1]), pack_bf16x2(ds[2], ds[3]),
+                                                            pack_bf16x2(ds[4], ds[5]), pack_bf16x2(ds[6], ds[7]));
+      }
+      // dQ of the previous block: its MMAs were issued a whole element-wise pass ago
+      if (it >= 1) {
+        mbar_wait(&bar_d[st ^ 1], ((it - 1) >> 1) & 1);
+        tc_fence_after();
+        uint32_t rq[16];
+        tmem_ld_32x32b_x16(tm_dq + (st ^ 1) * HD + lane_sel + gq * 16, rq);
+        tmem_ld_wait();
+        float* dq_row = dq_accum + (long long)(b * T + (i - 1) * ATT_BLK + row) * lddq + h * HD + gq * 16;
+#pragma unroll
+        for (int e = 0; e < 16; e += 4)
+          red_add_v4_f32_attn(dq_row + e, __uint_as_float(rq[e]) * scale, __uint_as_float(rq[e + 1]) * scale,
+                              __uint_as_float(rq[e + 2]) * scale, __uint_as_float(rq[e + 3]) * scale);
+      }
+      fence_proxy_async_smem();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bar_p[st]);
+    }
+    {  // tail: dQ of the last block, then the dK / dV accumulators of this key block
+      const int itl = n_it - 1, stl = itl & 1;
+      mbar_wait(&bar_d[stl], (itl >> 1) & 1);
+      tc_fence_after();
+      uint32_t rq[16], rk[16], rv[16];
+      tmem_ld_32x32b_x16(tm_dq + stl * HD + lane_sel + gq * 16, rq);
+      tmem_ld_32x32b_x16(tm_dk + lane_sel + gq * 16, rk);
+      tmem_ld_32x32b_x16(tm_dv + lane_sel + gq * 16, rv);
+      tmem_ld_wait();
+      float* dq_row = dq_accum + (long long)(b * T + (jblk + itl) * ATT_BLK + row) * lddq + h * HD + gq * 16;
+#pragma unroll
+      for (int e = 0; e < 16; e += 4)
+        red_add_v4_f32_attn(dq_row + e, __uint_as_float(rq[e]) * scale, __uint_as_float(rq[e + 1]) * scale,
+                            __uint_as_float(rq[e + 2]) * scale, __uint_as_float(rq[e + 3]) * scale);
+      bf16* dk_row = dk + (long long)(kv_row0 + row) * lddkv + h * HD + gq * 16;
+      bf16* dv_row = dv + (long long)(kv_row0 + row) * lddkv + h * HD + gq * 16;
+#pragma unroll
+      for (int g = 0; g < 2; ++g) {
+        const int e = g * 8;
+        float fk[8], fv[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          fk[u] = __uint_as_float(rk[e + u]) * scale;
+          fv[u] = __uint_as_float(rv[e + u]);
+        }
+        *reinterpret_cast<uint4*>(dk_row + e) =
+            make_uint4(pack_bf16x2(fk[0], fk[1]), pack_bf16x2(fk[2], fk[3]), pack_bf16x2(fk[4], fk[5]), pack_bf16x2(fk[6], fk[7]));
+        *reinterpret_cast<uint4*>(dv_row + e) =
+            make_uint4(pack_bf16x2(fv[0], fv[1]), pack_bf16x2(fv[2], fv[3]), pack_bf16x2(fv[4], fv[5]), pack_bf16x2(fv[6], fv[7]));
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 8) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
 template <int HD>
 static int attn_tmap(CUtensorMap* m, const void* p, long long rows, int H, long long ld) {
   return make_tmap_2d_bf16(m, p, rows, (uint64_t)H * HD, ld, ATT_BLK, HD,
@@ -862,11 +1337,21 @@ static int launch_fwd(const void* q, const void* k, const void* v, long long ld,
   const float scale = 1.f / sqrtf((float)HD);
   dim3 grid(T / ATT_BLK, H, B);
   static const bool use_kv128 = getenv("DTC_ATTN_FWD_KV128") != nullptr;  // A/B switch: the 128-key-block kernel
+  static const bool use_serial = getenv("DTC_ATTN_FWD_SERIAL") != nullptr;  // A/B switch: the un-pipelined 64-key kernel
   if (!use_kv128) {
     CUtensorMap tk64, tv64;
     const CUtensorMapSwizzle swz = HD == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
     if ((rc = make_tmap_2d_bf16(&tk64, k, M, (uint64_t)H * HD, ld, 64, HD, swz))) return rc;
     if ((rc = make_tmap_2d_bf16(&tv64, v, M, (uint64_t)H * HD, ld, 64, HD, swz))) return rc;
+    if (!use_serial) {
+      const int smem_p = C::TILE_BYTES + 2 * ATT_BLK * 128 + 4 * 64 * C::ROW_BYTES + 1024 + 256;
+      auto kern_p = flash_attn_fwd_pipe_kernel<HD>;
+      static dtc::SmemOptIn configured_p;  // per device
+      DTC_CHECK_CUDA(dtc::ensure_dyn_smem(kern_p, smem_p, configured_p));
+      DTC_CHECK_CUDA(dtc::launch(kern_p, grid, 160, smem_p, stream, tq, tk64, tv64, reinterpret_cast<bf16*>(out), ldo, lse2, T,
+                                 H, scale * LOG2E));
+      return 0;
+    }
     const int smem64 = C::TILE_BYTES + ATT_BLK * 128 + 4 * 64 * C::ROW_BYTES + 1024 + 128;
     auto kern64 = flash_attn_fwd_kv64_kernel<HD>;
     static dtc::SmemOptIn configured64;  // per device
@@ -904,7 +1389,19 @@ static int launch_bwd(const void* q, const void* k, const void* v, long long ld,
   }
   const float scale_ = 1.f / sqrtf((float)HD);
   static const bool use_v1 = getenv("DTC_ATTN_BWD_V1") != nullptr;  // A/B switch: TMEM-accumulator kernel
+  static const bool use_regacc = getenv("DTC_ATTN_BWD_REGACC") != nullptr;  // A/B switch: the un-pipelined register-accumulator kernel
   if constexpr (HD == 32) {
+    if (!use_v1 && !use_regacc) {
+      const int smem3 = 4 * C::P_BYTES + 6 * C::TILE_BYTES + 1024 + 256;
+      auto kern3 = flash_attn_bwd_pipe_kernel<HD>;
+      static dtc::SmemOptIn configured3;  // per device
+      DTC_CHECK_CUDA(dtc::ensure_dyn_smem(kern3, smem3, configured3));
+      dim3 grid3(T / ATT_BLK, H, B);
+      DTC_CHECK_CUDA(dtc::launch(kern3, grid3, 288, smem3, stream, tq, tk, tv, tdo, lse2, delta, dq_accum, lddq,
+                                 reinterpret_cast<bf16*>(dk), reinterpret_cast<bf16*>(dv), lddkv, T, H, scale_,
+                                 scale_ * LOG2E));
+      return 0;
+    }
     if (!use_v1) {
       const int smem2 = 5 * C::TILE_BYTES + 2 * C::P_BYTES + 2 * ATT_BLK * 4 + 1024 + 128;
       auto kern2 = flash_attn_bwd_regacc_kernel<HD>;

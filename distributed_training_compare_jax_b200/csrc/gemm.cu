@@ -972,38 +972,49 @@ gemm_grouped_wgrad_kernel(const __grid_constant__ GemmGroup grp, int K, int spli
 //   full[s]       lives in the leader; both CTAs' TMA loads complete_tx on it (expect_tx = bytes of both CTAs)
 //   empty[s]      one per CTA; tcgen05.commit multicasts the arrival to both
 //   tmem_full[b]  one per CTA (commit multicast); tmem_empty[b] lives in the leader, 16 arrivals (8 epilogue warps x 2 CTAs)
-// Epilogue as in the persistent kernel, in 128-column halves (BN = 256 has two).
+// Epilogue: two groups of four warps drain the two column halves in 64-column slab jobs (see P2Smem).
 // =========================================================================================================
-template <int BN>
+// Staging of the pair kernel's epilogue: NSLAB slab buffers of [128 rows x 64 bf16] (16 KB, 128B-swizzled = one TMA box).
+// The 8 epilogue warps form two groups of 4 (one warp per TMEM lane quadrant); group g drains the column half
+// [g*BN/2, (g+1)*BN/2) of the accumulator in 64-column slabs.  Every slab written to global is one "job": TMEM -> registers
+// -> bias / GELU / residual -> swizzled st.shared into a slab buffer -> ONE TMA store.  A group cycles through NSLAB/2
+// buffers, so the TMA store of job j drains while the group converts job j+1 (and the other group works on its own
+// half): the read-out of a tile is a pipeline of small stores instead of one long serial drain.
+template <int BN, int NSLAB>
 struct P2Smem {
   static constexpr int A_BYTES = BM * BK * 2;             // this CTA's 128 rows of A
   static constexpr int B_BYTES = (BN / 2) * BK * 2;       // this CTA's half of the B tile
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int HALF_BYTES = BM * 128;             // 128 rows x 64 bf16 (one TMA box)
-  static constexpr int OUT_BYTES = 2 * HALF_BYTES;        // staging for one 128-column half of the output
-  static constexpr int AUX_BYTES = (BN / 64) * HALF_BYTES;  // whole [128 x BN] aux tile / out2 staging
-  static constexpr int bytes(int stages) { return stages * STAGE_BYTES + OUT_BYTES + AUX_BYTES + 1024 + 256; }
+  static constexpr int SLAB_BYTES = BM * 128;             // 128 rows x 64 bf16 (one TMA box)
+  static constexpr int TAIL_BYTES = 512 /* barriers */ + 2 * BN * 2 /* bias, two tiles */;
+  static constexpr int bytes(int stages) { return stages * STAGE_BYTES + NSLAB * SLAB_BYTES + 1024 + TAIL_BYTES; }
 };
 
-template <bool A_MN, bool B_MN, int BN>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(PG_THREADS)
+template <int N>
+DTC_DEVICE void tma_store_wait_read_n() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+DTC_DEVICE void epi_group_sync(int g) { asm volatile("bar.sync %0, 128;" ::"r"(g + 1) : "memory"); }
+
+template <bool A_MN, bool B_MN, int BN, int NSLAB>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(PG_THREADS, NSLAB == 2 ? 2 : 1)
 gemm_2cta_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                  const __grid_constant__ CUtensorMap tma_out, const __grid_constant__ CUtensorMap tma_out2,
                  const __grid_constant__ CUtensorMap tma_aux, int M, int N, int K, int m_blocks /* of 256 rows */,
                  int n_blocks, int splits, int kb_per_split, int num_stages, GemmEpi epi) {
-  using S = P2Smem<BN>;
+  using S = P2Smem<BN, NSLAB>;
+  constexpr int GB = NSLAB / 2;  // slab buffers per epilogue group
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint8_t* stage_out = smem + num_stages * S::STAGE_BYTES;
-  uint8_t* stage_aux = stage_out + S::OUT_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(stage_aux + S::AUX_BYTES);
-  uint64_t* full_bar = bars;
-  uint64_t* empty_bar = bars + PG_STAGE_MAX;
-  uint64_t* tmem_full = bars + 2 * PG_STAGE_MAX;
-  uint64_t* tmem_empty = tmem_full + 2;
-  uint64_t* aux_full = tmem_empty + 2;
-  uint64_t* aux_empty = aux_full + 1;
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(aux_empty + 1);
+  uint8_t* slabs = smem + num_stages * S::STAGE_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(slabs + NSLAB * S::SLAB_BYTES);
+  uint64_t* full_bar = bars;                      // [PG_STAGE_MAX]
+  uint64_t* empty_bar = bars + PG_STAGE_MAX;      // [PG_STAGE_MAX]
+  uint64_t* tmem_full = bars + 2 * PG_STAGE_MAX;  // [2]
+  uint64_t* tmem_empty = tmem_full + 2;           // [2]
+  uint64_t* aux_full = tmem_empty + 2;            // [NSLAB <= 4]
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(aux_full + 4);
+  bf16* s_bias = reinterpret_cast<bf16*>(bars + 64);  // [2][BN], 512 B past the barriers
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -1020,6 +1031,8 @@ gemm_2cta_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
     tma_prefetch_desc(&tma_a);
     tma_prefetch_desc(&tma_b);
     if (bf16_out) tma_prefetch_desc(&tma_out);
+    if (use_aux) tma_prefetch_desc(&tma_aux);
+    if (mode == EPI_BIAS_GELU) tma_prefetch_desc(&tma_out2);
     for (int s = 0; s < num_stages; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
@@ -1028,8 +1041,7 @@ gemm_2cta_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
       mbar_init(&tmem_full[b], 1);
       mbar_init(&tmem_empty[b], 16);  // 8 epilogue warps of each CTA (used in the leader only)
     }
-    mbar_init(aux_full, 1);
-    mbar_init(aux_empty, 8);
+    for (int b = 0; b < 4; ++b) mbar_init(&aux_full[b], 1);
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -1048,21 +1060,13 @@ gemm_2cta_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
     // ------------------------------ TMA producer (both CTAs) ------------------------------
     if (elect_one()) {
       uint32_t kit = 0;
-      int it = 0;
-      for (int tile = pair; tile < total_tiles; tile += num_pairs, ++it) {
+      for (int tile = pair; tile < total_tiles; tile += num_pairs) {
         const int split = tile / tiles_mn, mn = tile % tiles_mn;
         const int m_blk = mn % m_blocks, n_blk = mn / m_blocks;
         const int row0 = m_blk * 256 + (int)cta * BM;       // this CTA's rows of A / of the output
         const int bcol0 = n_blk * BN + (int)cta * (BN / 2);  // this CTA's half of the B tile
         const int kb_begin = split * kb_per_split;
         const int nkb = min(total_kb, kb_begin + kb_per_split) - kb_begin;
-        if (use_aux) {
-          mbar_wait(aux_empty, (it & 1) ^ 1);
-          mbar_expect_tx(aux_full, S::AUX_BYTES);
-#pragma unroll
-          for (int hf = 0; hf < BN / 64; ++hf)
-            tma_load_2d(stage_aux + hf * S::HALF_BYTES, &tma_aux, aux_full, n_blk * BN + hf * 64, row0);
-        }
         for (int i = 0; i < nkb; ++i, ++kit) {
           const int s = kit % num_stages;
           const uint32_t ph = (kit / num_stages) & 1;
@@ -1126,42 +1130,49 @@ gemm_2cta_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
     }
   } else {
     // ------------------------------ epilogue (warps 2..9 of both CTAs) ------------------------------
-    const int q = warp & 3;
-    const int chalf = (warp - 2) >> 2;
+    const int q = warp & 3;                      // TMEM lane quadrant this warp may read
+    const int g = (warp - 2) >> 2;               // epilogue group = column half of the tile
     const int row = q * 32 + lane;
-    const bool store_leader = (threadIdx.x == 64);
+    const int gt = (int)threadIdx.x - 64 - g * 128;  // thread index inside the group
+    const bool leader = gt == 0;                 // issues this group's TMA loads / stores
     const float alpha = epi.alpha;
+    const bool has_bias = epi.bias != nullptr && mode != EPI_ATOMIC_F32 && mode != EPI_DGELU;
+    constexpr int SPG = BN / 128;                // 64-column slabs per group and tile
+    const int gcol = g * (BN / 2);               // first tile column of this group
+    uint8_t* gslab = slabs + g * GB * S::SLAB_BYTES;
+    uint64_t* gaux = aux_full + g * GB;
     int it = 0;
-    for (int tile = pair; tile < total_tiles; tile += num_pairs, ++it) {
-      const int mn = tile % tiles_mn;
-      const int m_blk = mn % m_blocks, n_blk = mn / m_blocks;
-      const int buf = it & 1;
-      const int row0 = m_blk * 256 + (int)cta * BM;
-      const long long gm = (long long)row0 + row;
-      const bool row_ok = gm < M;
-      mbar_wait(&tmem_full[buf], (it >> 1) & 1);
-      tc_fence_after();
-      if (use_aux) mbar_wait(aux_full, it & 1);
-      const uint32_t tmem_d = tmem_base + buf * BN + ((uint32_t)(q * 32) << 16);
+
+    if (!bf16_out) {
+      // fp32 outputs (split-K reduce-add / fp32 store): straight from registers, one accumulator row per thread
+      for (int tile = pair; tile < total_tiles; tile += num_pairs, ++it) {
+        const int mn = tile % tiles_mn;
+        const int m_blk = mn % m_blocks, n_blk = mn / m_blocks;
+        const int buf = it & 1;
+        const long long gm = (long long)m_blk * 256 + (int)cta * BM + row;
+        const bool row_ok = gm < M;
+        mbar_wait(&tmem_full[buf], (it >> 1) & 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + buf * BN + ((uint32_t)(q * 32) << 16) + gcol;
 #pragma unroll 1
-      for (int hp = 0; hp < BN / 128; ++hp) {  // 128-column halves of the tile
-        if (bf16_out) {
-          if (store_leader) tma_store_wait_read();  // previous stores have finished reading the staging tiles
-          epi_bar_sync();
-        }
-#pragma unroll 1
-        for (int c = chalf * 2; c < chalf * 2 + 2; ++c) {  // two 32-column chunks per warp and half
+        for (int c = 0; c < BN / 64; ++c) {
           uint32_t r[32];
-          tmem_ld_32x32b_x32(tmem_d + hp * 128 + c * 32, r);
+          tmem_ld_32x32b_x32(tmem_d + c * 32, r);
           tmem_ld_wait();
-          const int n0 = n_blk * BN + hp * 128 + c * 32;
+          if (c == BN / 64 - 1) {  // accumulator buffer drained by this warp
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(mapa_shared(smem_u32(&tmem_empty[buf]), 0));
+          }
+          const int n0 = n_blk * BN + gcol + c * 32;
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            const int n = n0 + g * 8;
+          for (int c8 = 0; c8 < 4; ++c8) {
+            const int n = n0 + c8 * 8;
+            if (!row_ok || n >= N) continue;
             float v[8];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]) * alpha;
-            if (epi.bias != nullptr && mode != EPI_ATOMIC_F32 && mode != EPI_DGELU && n < N) {
+            for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[c8 * 8 + j]) * alpha;
+            if (has_bias) {
               const uint4 bb = *reinterpret_cast<const uint4*>(epi.bias + n);
               const uint32_t bw[4] = {bb.x, bb.y, bb.z, bb.w};
 #pragma unroll
@@ -1171,70 +1182,134 @@ gemm_2cta_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
                 v[2 * j + 1] += f.y;
               }
             }
-            if (!bf16_out) {
-              if (!row_ok || n >= N) continue;
-              float* o = reinterpret_cast<float*>(epi.out) + gm * epi.ldo + n;
-              if (mode == EPI_ATOMIC_F32) {
-                red_add_v4_f32(o, v[0], v[1], v[2], v[3]);
-                red_add_v4_f32(o + 4, v[4], v[5], v[6], v[7]);
-              } else {
-                *reinterpret_cast<float4*>(o) = make_float4(v[0], v[1], v[2], v[3]);
-                *reinterpret_cast<float4*>(o + 4) = make_float4(v[4], v[5], v[6], v[7]);
-              }
-              continue;
+            float* o = reinterpret_cast<float*>(epi.out) + gm * epi.ldo + n;
+            if (mode == EPI_ATOMIC_F32) {
+              red_add_v4_f32(o, v[0], v[1], v[2], v[3]);
+              red_add_v4_f32(o + 4, v[4], v[5], v[6], v[7]);
+            } else {
+              *reinterpret_cast<float4*>(o) = make_float4(v[0], v[1], v[2], v[3]);
+              *reinterpret_cast<float4*>(o + 4) = make_float4(v[4], v[5], v[6], v[7]);
             }
-            // offsets inside the out staging (one 128-column half) and inside the whole-tile aux / out2 staging
-            const uint32_t off = (uint32_t)(c >> 1) * S::HALF_BYTES + swizzle_offset<3>(row * 128 + ((c & 1) * 4 + g) * 16);
-            const uint32_t aoff = (uint32_t)(hp * 2) * S::HALF_BYTES + off;
-            if (use_aux) {
-              const uint4 a = *reinterpret_cast<const uint4*>(stage_aux + aoff);
-              const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
-#pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                const float2 f = unpack_bf16x2(aw[j]);
-                if (mode == EPI_BIAS_RESIDUAL) {
-                  v[2 * j] += f.x;
-                  v[2 * j + 1] += f.y;
-                } else {
-                  v[2 * j] *= gelu_tanh_grad(f.x);
-                  v[2 * j + 1] *= gelu_tanh_grad(f.y);
-                }
-              }
-            }
-            *reinterpret_cast<uint4*>(stage_out + off) = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]),
-                                                                   pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
-            if (mode == EPI_BIAS_GELU) {
-              *reinterpret_cast<uint4*>(stage_aux + aoff) = make_uint4(
-                  pack_bf16x2(gelu_tanh(v[0]), gelu_tanh(v[1])), pack_bf16x2(gelu_tanh(v[2]), gelu_tanh(v[3])),
-                  pack_bf16x2(gelu_tanh(v[4]), gelu_tanh(v[5])), pack_bf16x2(gelu_tanh(v[6]), gelu_tanh(v[7])));
-            }
-          }
-        }
-        if (hp == BN / 128 - 1) {
-          // accumulator buffer drained: tell the leader's MMA warp (and free the aux tile for the producer)
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) {
-            mbar_arrive_cluster(mapa_shared(smem_u32(&tmem_empty[buf]), 0));
-            if (use_aux) mbar_arrive(aux_empty);
-          }
-        }
-        if (bf16_out) {
-          fence_proxy_async_smem();
-          epi_bar_sync();
-          if (store_leader) {
-#pragma unroll
-            for (int hf = 0; hf < 2; ++hf) {
-              const int col = n_blk * BN + hp * 128 + hf * 64;
-              tma_store_2d(&tma_out, stage_out + hf * S::HALF_BYTES, col, row0);
-              if (mode == EPI_BIAS_GELU) tma_store_2d(&tma_out2, stage_aux + (hp * 2 + hf) * S::HALF_BYTES, col, row0);
-            }
-            tma_store_commit();
           }
         }
       }
+    } else {
+      // bf16 outputs: pipelined slab jobs (see P2Smem)
+      uint32_t jc = 0;  // jobs issued by this group so far (uniform over its threads): buffer = jc % GB
+      if (use_aux && leader && pair < total_tiles) {  // residual / pre-activation slab of the first job
+        const int mn = pair % tiles_mn;
+        mbar_expect_tx(&gaux[0], S::SLAB_BYTES);
+        tma_load_2d(gslab, &tma_aux, &gaux[0], (mn / m_blocks) * BN + gcol, (mn % m_blocks) * 256 + (int)cta * BM);
+      }
+      const int n_out = (mode == EPI_BIAS_GELU) ? 2 : 1;
+      for (int tile = pair; tile < total_tiles; tile += num_pairs, ++it) {
+        const int mn = tile % tiles_mn;
+        const int m_blk = mn % m_blocks, n_blk = mn / m_blocks;
+        const int buf = it & 1;
+        const int row0 = m_blk * 256 + (int)cta * BM;
+        bf16* tbias = s_bias + (it & 1) * BN + gcol;
+        if (has_bias) {  // this group's bias slice -> smem while the mainloop of the tile is still running
+          if (gt < BN / 16) {
+            const int n = n_blk * BN + gcol + gt * 8;
+            uint4 bv = make_uint4(0, 0, 0, 0);
+            if (n < N) bv = *reinterpret_cast<const uint4*>(epi.bias + n);
+            *reinterpret_cast<uint4*>(tbias + gt * 8) = bv;
+          }
+          epi_group_sync(g);
+        }
+        mbar_wait(&tmem_full[buf], (it >> 1) & 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + buf * BN + ((uint32_t)(q * 32) << 16) + gcol;
+#pragma unroll 1
+        for (int sl = 0; sl < SPG; ++sl) {
+          uint32_t r[64];
+          tmem_ld_32x32b_x32(tmem_d + sl * 64, r);
+          tmem_ld_32x32b_x32(tmem_d + sl * 64 + 32, r + 32);
+          tmem_ld_wait();
+          if (sl == SPG - 1) {  // this warp has read its whole share of the accumulator: hand the buffer back early
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(mapa_shared(smem_u32(&tmem_empty[buf]), 0));
+          }
+          // v = alpha * acc + bias, kept in r as float bits
+#pragma unroll
+          for (int c8 = 0; c8 < 8; ++c8) {
+            uint4 bb = make_uint4(0, 0, 0, 0);
+            if (has_bias) bb = *reinterpret_cast<const uint4*>(tbias + sl * 64 + c8 * 8);
+            const uint32_t bw[4] = {bb.x, bb.y, bb.z, bb.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const float2 f = unpack_bf16x2(bw[j]);
+              r[c8 * 8 + 2 * j] = __float_as_uint(__uint_as_float(r[c8 * 8 + 2 * j]) * alpha + f.x);
+              r[c8 * 8 + 2 * j + 1] = __float_as_uint(__uint_as_float(r[c8 * 8 + 2 * j + 1]) * alpha + f.y);
+            }
+          }
+          const int col0 = n_blk * BN + gcol + sl * 64;
+#pragma unroll 1
+          for (int o = 0; o < n_out; ++o, ++jc) {
+            const int b = jc % GB;
+            uint8_t* sbuf = gslab + b * S::SLAB_BYTES;
+            if (use_aux) {
+              mbar_wait(&gaux[b], (jc / GB) & 1);  // the aux slab has landed (it was requested once the buffer was free)
+            } else {
+              if (leader) tma_store_wait_read_n<GB - 1>();  // the store that last used this buffer has read it
+              epi_group_sync(g);
+            }
+#pragma unroll
+            for (int c8 = 0; c8 < 8; ++c8) {
+              const uint32_t off = swizzle_offset<3>(row * 128 + c8 * 16);
+              float v[8];
+#pragma unroll
+              for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[c8 * 8 + j]);
+              if (use_aux) {
+                const uint4 a = *reinterpret_cast<const uint4*>(sbuf + off);
+                const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  const float2 f = unpack_bf16x2(aw[j]);
+                  if (mode == EPI_BIAS_RESIDUAL) {
+                    v[2 * j] += f.x;
+                    v[2 * j + 1] += f.y;
+                  } else {
+                    v[2 * j] *= gelu_tanh_grad(f.x);
+                    v[2 * j + 1] *= gelu_tanh_grad(f.y);
+                  }
+                }
+              }
+              if (o == 1) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[j] = gelu_tanh(v[j]);
+              }
+              *reinterpret_cast<uint4*>(sbuf + off) = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]),
+                                                                 pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+            }
+            fence_proxy_async_smem();
+            epi_group_sync(g);
+            if (leader) {
+              tma_store_2d(o == 0 ? &tma_out : &tma_out2, sbuf, col0, row0);
+              tma_store_commit();
+              if (use_aux) {
+                // request the aux slab of the group's NEXT job (same tile, next slab — or the next tile of this pair)
+                int ntile = tile, nsl = sl + 1;
+                if (nsl == SPG) {
+                  ntile = tile + num_pairs;
+                  nsl = 0;
+                }
+                if (ntile < total_tiles) {
+                  const int nb = (jc + 1) % GB;
+                  const int nmn = ntile % tiles_mn;
+                  tma_store_wait_read_n<GB - 1>();  // the store that last used buffer nb has read it
+                  mbar_expect_tx(&gaux[nb], S::SLAB_BYTES);
+                  tma_load_2d(gslab + nb * S::SLAB_BYTES, &tma_aux, &gaux[nb], (nmn / m_blocks) * BN + gcol + nsl * 64,
+                              (nmn % m_blocks) * 256 + (int)cta * BM);
+                }
+              }
+            }
+          }
+        }
+      }
+      if (leader) tma_store_wait_all();
     }
-    if (bf16_out && store_leader) tma_store_wait_all();
   }
 
   tc_fence_before();
@@ -1246,10 +1321,10 @@ gemm_2cta_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
   }
 }
 
-template <bool A_MN, bool B_MN, int BN>
+template <bool A_MN, bool B_MN, int BN, int NSLAB>
 static int launch_gemm_2cta(const void* A, long long lda, const void* B, long long ldb, int M, int N, int K, int splits,
                             int stages, const GemmEpi& epi, cudaStream_t stream) {
-  using S = P2Smem<BN>;
+  using S = P2Smem<BN, NSLAB>;
   CUtensorMap ta, tb, tout, tout2, taux;
   int rc;
   if (A_MN) rc = make_tmap_2d_bf16(&ta, A, K, M, lda, BK, 64, CU_TENSOR_MAP_SWIZZLE_128B);
@@ -1277,14 +1352,15 @@ static int launch_gemm_2cta(const void* A, long long lda, const void* B, long lo
   splits = (total_kb + kb_per_split - 1) / kb_per_split;
   if (stages < 2) stages = 2;
   if (stages > PG_STAGE_MAX) stages = PG_STAGE_MAX;
-  while (S::bytes(stages) > 227 * 1024) --stages;
+  const int smem_cap = NSLAB == 2 ? 112 * 1024 : 227 * 1024;  // light configuration: two CTAs (+1 KB reserved each) per SM
+  while (stages > 2 && S::bytes(stages) > smem_cap) --stages;
   const int smem_bytes = S::bytes(stages);
-  auto kern = gemm_2cta_kernel<A_MN, B_MN, BN>;
+  auto kern = gemm_2cta_kernel<A_MN, B_MN, BN, NSLAB>;
   static dtc::SmemOptIn configured;  // per device
-  DTC_CHECK_CUDA(dtc::ensure_dyn_smem(kern, 227 * 1024, configured));
+  DTC_CHECK_CUDA(dtc::ensure_dyn_smem(kern, NSLAB == 2 ? 113 * 1024 : 227 * 1024, configured));
   const int m_blocks = (M + 255) / 256, n_blocks = (N + BN - 1) / BN;
   const int total_tiles = m_blocks * n_blocks * splits;
-  const int max_pairs = num_sms() / 2;
+  const int max_pairs = (NSLAB == 2 ? 2 : 1) * (num_sms() / 2);
   const int pairs = total_tiles < max_pairs ? total_tiles : max_pairs;
   DTC_CHECK_CUDA(dtc::launch(kern, 2 * pairs, PG_THREADS, smem_bytes, stream, ta, tb, tout, tout2, taux, M, N, K, m_blocks, n_blocks, splits,
                                                       kb_per_split, stages, epi));
@@ -1377,8 +1453,8 @@ extern "C" int dtc_gemm_bf16(const void* A, long long lda, int a_mn_major, const
     const bool wide = (block_n == 256) || ((g_gemm_impl == 3 || g_gemm_impl == 0) && block_n == 0 && tiles256 >= 74);
     if (stages == 0) stages = PG_STAGE_MAX;
 #define DTC_2CTA_DISPATCH(AMN, BMN)                                                                               \
-  if (wide) return launch_gemm_2cta<AMN, BMN, 256>(A, lda, B, ldb, M, N, K, splits, stages, epi, stream);         \
-  return launch_gemm_2cta<AMN, BMN, 128>(A, lda, B, ldb, M, N, K, splits, stages, epi, stream);
+  if (wide) return launch_gemm_2cta<AMN, BMN, 256, 4>(A, lda, B, ldb, M, N, K, splits, stages, epi, stream);      \
+  return launch_gemm_2cta<AMN, BMN, 128, 4>(A, lda, B, ldb, M, N, K, splits, stages, epi, stream);
     if (!a_mn_major && !b_mn_major) { DTC_2CTA_DISPATCH(false, false) }
     if (!a_mn_major && b_mn_major) { DTC_2CTA_DISPATCH(false, true) }
     if (a_mn_major && !b_mn_major) { DTC_2CTA_DISPATCH(true, false) }

@@ -108,7 +108,18 @@ class _GraphedBody:
         native.add_launches(self.launches_per_replay)
 
 
-def create_train_step(parallel: str = "dp", cuda_graph: bool = True) -> Any:
+def resync_tp_replicas(state: "TrainState") -> None:
+    """Make the tensor-parallel ranks' copies of the replicated leaves bit-identical again (tp-rank 0 wins): master
+    weights, Adam moments and the bf16 compute copy of the replicated range.  Host-driven, outside the step graph."""
+    mesh, st = state.mesh, state.engine.store
+    if mesh.tp.size == 1 or st.rep_numel == 0:
+        return
+    for flat in (st.flat_master, st.flat_m, st.flat_v, st.flat_compute):
+        if flat is not None and flat.numel() >= st.rep_numel:
+            mesh.tp.broadcast(flat[:st.rep_numel], 0)
+
+
+def create_train_step(parallel: str = "dp", cuda_graph: bool = True, tp_resync_every: int = 0) -> Any:
     if parallel == "pp":
         raise ValueError("`parallel=pp` must use `create_pp_train_step`")
     cache: dict = {}
@@ -151,6 +162,9 @@ def create_train_step(parallel: str = "dp", cuda_graph: bool = True) -> Any:
             graphed[id(eng)] = _GraphedBody(body, enabled=cuda_graph and eng.backend == "native")
         graphed[id(eng)]()
         state.step += 1
+        if tp_resync_every and mesh.tp.size > 1 and state.step % tp_resync_every == 0 \
+                and not hasattr(opt, "sync_full_state"):
+            resync_tp_replicas(state)
         return state, eng.loss_sum[0]
 
     return train_step

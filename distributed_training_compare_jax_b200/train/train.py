@@ -140,6 +140,14 @@ def _run_loop(train_config: TrainConfig, model_config: ModelConfig, state: Train
                "tokens_per_step": tokens_per_step, "tokens_per_s": tokens_per_step * steps / (ms / 1e3) if ms else 0.0,
                "final_loss": log.loss_history[-1] if log.loss_history else None,
                "tp_seq_parallel": bool(getattr(state.engine, "seq_parallel", False) or hasattr(state.engine, "sp"))}
+    if mesh.tp.size > 1:   # how far the tensor-parallel copies of the replicated leaves have drifted apart (0.0 = bit-equal)
+        st = state.engine.store
+        mine = st.flat_master[:st.rep_numel]
+        ref = mine.clone()
+        mesh.tp.broadcast(ref, 0)
+        diff = (mine - ref).abs().max().reshape(1).float()
+        mesh.tp.all_reduce(diff, op=torch.distributed.ReduceOp.MAX)
+        metrics["tp_replica_max_abs_diff"] = float(diff.item())
     log.finish(metrics)
     if train_config.checkpoint_dir:
         if hasattr(state.optimizer, "sync_full_state"):
@@ -162,7 +170,8 @@ def train_dp_tp(train_config: TrainConfig, model_config: ModelConfig, opt_config
     chains = train_config.micro_chains if (tp == 1 and local_batch % max(train_config.micro_chains, 1) == 0) else 1
     state = build_state(train_config, model_config, opt_config, mesh, local_batch // chains, chains, global_batch * T,
                         local)
-    train_step = create_train_step(parallel=parallel_strategy, cuda_graph=train_config.cuda_graph)
+    train_step = create_train_step(parallel=parallel_strategy, cuda_graph=train_config.cuda_graph,
+                                   tp_resync_every=train_config.tp_resync_every)
     data_iterator = get_batch_iterator(batch_size=global_batch, seq_len=T + 1, seed=train_config.seed, rank=mesh.dp.rank,
                                        world=dp, synthetic=train_config.synthetic_data,
                                        skip_batches=state.batches_consumed)

@@ -110,6 +110,17 @@ def test_gemm_kernel_variants_agree(impl):
         want = R.gemm(x, dy, a_mn=True, b_mn=True, epi="atomic_f32", out=acc.clone())
         Fn.gemm(x, dy, a_mn=True, b_mn=True, epi="atomic_f32", out=acc, splits=4)
         assert rel_err(acc, want) < 1e-2
+        # several tiles per CTA pair (the slab-job pipeline of the pair epilogue crosses tile boundaries)
+        M2, K2, N2 = 4096, 192, 2560
+        x2, w2, bias2, res2 = randn(M2, K2), randn(K2, N2, scale=0.1), randn(N2), randn(M2, N2)
+        assert rel_err(Fn.gemm(x2, w2, b_mn=True, bias=bias2), R.gemm(x2, w2, b_mn=True, bias=bias2)) < 1e-2
+        assert rel_err(Fn.gemm(x2, w2, b_mn=True, bias=bias2, epi="bias_residual", aux=res2),
+                       R.gemm(x2, w2, b_mn=True, bias=bias2, epi="bias_residual", aux=res2)) < 1e-2
+        pre, act = Fn.gemm(x2, w2, b_mn=True, bias=bias2, epi="bias_gelu")
+        wpre, wact = R.gemm(x2, w2, b_mn=True, bias=bias2, epi="bias_gelu")
+        assert rel_err(pre, wpre) < 1e-2 and rel_err(act, wact) < 1e-2
+        dy2, f2 = randn(M2, N2), randn(M2, K2)
+        assert rel_err(Fn.gemm(dy2, w2, epi="dgelu", aux=f2), R.gemm(dy2, w2, epi="dgelu", aux=f2)) < 1e-2
         # ragged edges: M, N not multiples of the pair tile
         a2, b2 = randn(600, 200), randn(200, 392, scale=0.1)
         assert rel_err(Fn.gemm(a2, b2, b_mn=True), R.gemm(a2, b2, b_mn=True)) < 1e-2

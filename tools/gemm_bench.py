@@ -72,15 +72,21 @@ def main():
         peak = json.load(open(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json")))["bf16_tflops_sustained"]
     except Exception:
         pass
-    print(f"{'gemm (device time, graph replay)':34s} {'default us':>10s} {'TFLOP/s':>8s} {'frac':>5s} | {'1-CTA pers':>10s} | "
-          f"{'1-tile/CTA':>10s} | {'pair x128':>9s} | {'pair x256':>9s}")
+    impls = [0, 4, 1, 2, 3]
+    for a in sys.argv:
+        if a.startswith("--impls="):
+            impls = [int(v) for v in a.split("=")[1].split(",")]
+    only = [a.split("=")[1] for a in sys.argv if a.startswith("--only=")]
+    names = {0: "default", 4: "1-CTA pers", 1: "1-tile/CTA", 2: "pair x128", 3: "pair x256", 5: "pair light"}
+    print(f"{'gemm (device time, graph replay)':34s} " + " | ".join(f"{names.get(i, str(i)):>10s} us TFLOP/s frac" for i in impls))
     for name, ash, bsh, a_mn, b_mn, epi, splits in SHAPES:
-        u0, t0 = run(name, ash, bsh, a_mn, b_mn, epi, splits, 0)
-        u4, _ = run(name, ash, bsh, a_mn, b_mn, epi, splits, 4)
-        u1, _ = run(name, ash, bsh, a_mn, b_mn, epi, splits, 1)
-        u2, _ = run(name, ash, bsh, a_mn, b_mn, epi, splits, 2)
-        u3, _ = run(name, ash, bsh, a_mn, b_mn, epi, splits, 3)
-        line = f"{name:34s} {u0:10.1f} {t0:8.1f} {t0 / peak:5.2f} | {u4:10.1f} | {u1:10.1f} | {u2:9.1f} | {u3:9.1f}"
+        if only and not any(o in name for o in only):
+            continue
+        cells = []
+        for i in impls:
+            u, t = run(name, ash, bsh, a_mn, b_mn, epi, splits, i)
+            cells.append(f"{u:10.1f}    {t:7.1f} {t / peak:4.2f}")
+        line = f"{name:34s} " + " | ".join(cells)
         if "--torch" in sys.argv and not a_mn and epi == "store":
             a = torch.randn(ash, device="cuda").to(torch.bfloat16)
             b = torch.randn(bsh, device="cuda").to(torch.bfloat16)
