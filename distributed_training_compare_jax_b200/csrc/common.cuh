@@ -226,8 +226,13 @@ DTC_DEVICE uint32_t mapa_shared(uint32_t smem_addr, uint32_t rank) {
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_addr), "r"(rank));
   return r;
 }
+// Arrive on a barrier of another CTA of the cluster.  Default semantics (.release.cta), as CUTLASS's ClusterBarrier::arrive:
+// the explicit .release.cluster form compiles to MEMBAR.ALL.GPU + ERRBAR in front of the arrive, and an ncu source view of
+// the CTA-pair GEMM showed 34 % of all warp stalls on exactly that sequence (the epilogue warps handing the accumulator
+// buffer back to the leader's MMA warp).  What has to be ordered before this arrive are tcgen05.ld reads of tensor
+// memory, which tcgen05.fence::before_thread_sync (issued by the callers) covers; no global / shared data is published.
 DTC_DEVICE void mbar_arrive_cluster(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 // TMA load issued by either CTA of a pair; the transaction bytes are counted on `mbar_cluster_addr`
 // (a shared::cluster address — the leader CTA's barrier).

@@ -1426,6 +1426,7 @@ extern "C" int dtc_gemm_bf16(const void* A, long long lda, int a_mn_major, const
   epi.ldo2 = ldo2;
   epi.trace = g_gemm_trace;
   epi.coop_store = g_gemm_coop_store;
+  const int block_n_arg = block_n;  // 0 = let the dispatcher choose (the pair kernel decides on its own width below)
   if (block_n == 0) {
     block_n = (N <= 64) ? 64 : 128;
     // few 128-wide tiles (N = 512 layers: 128 tiles for 148 SMs): 64-wide tiles double the CTA count so that every SM
@@ -1450,7 +1451,7 @@ extern "C" int dtc_gemm_bf16(const void* A, long long lda, int a_mn_major, const
     const long long tiles256 = (long long)((M + 255) / 256) * ((N + 255) / 256) * (splits > 1 ? splits : 1);
     // 256-wide pair tiles (half the operand bytes per MMA cycle again) whenever they still fill all 74 CTA pairs;
     // ragged N is fine: TMA zero-fills the loads and clips the stores
-    const bool wide = (block_n == 256) || ((g_gemm_impl == 3 || g_gemm_impl == 0) && block_n == 0 && tiles256 >= 74);
+    const bool wide = (block_n_arg == 256) || ((g_gemm_impl == 3 || g_gemm_impl == 0) && block_n_arg == 0 && tiles256 >= 74);
     if (stages == 0) stages = PG_STAGE_MAX;
 #define DTC_2CTA_DISPATCH(AMN, BMN)                                                                               \
   if (wide) return launch_gemm_2cta<AMN, BMN, 256, 4>(A, lda, B, ldb, M, N, K, splits, stages, epi, stream);      \
