@@ -1318,6 +1318,305 @@ flash_attn_bwd_pipe_kernel(const __grid_constant__ CUtensorMap tm_q, const __gri
   }
 }
 
+// Backward, persistent + software-pipelined (head_dim 32, default).  One CTA per SM walks a static list of work items
+// (batch, head, 128-key block j), heaviest first; an item loops over the query blocks i >= j.  All (item, i) steps of a
+// CTA form ONE flattened sequence g = 0, 1, 2 ... and every resource is ring-indexed by g (or by the item ordinal k), so
+// the pipeline never drains between items: the issue warp loads K / V / Q / dO of the next item and issues its score
+// MMAs while the softmax warps are still finishing the current one, and the dK / dV read-out of item k overlaps the
+// first block of item k+1.  A launch therefore pays ONE prologue and one tail per SM instead of one per (b, h, j).
+//   * scores in the S = Q_i K_j^T orientation (thread r owns QUERY row r): lse2 / delta are two per-thread scalars;
+//   * 8 softmax warps: warps 0..3 take key columns [0,64), warps 4..7 take [64,128) of the same rows;
+//   * warp 8 is the issue warp (one elected lane): all TMA loads and tcgen05.mma; S_{g+1} / dP_{g+1} are issued as soon as
+//     every softmax warp has pulled S_g / dP_g into registers, i.e. they run under the exp2 work of step g;
+//   * P / dS tiles double-buffered in shared memory: the products of step g (dV += P^T dO_i, dK += dS^T Q_i,
+//     dQ_i = dS K_j) overlap the element-wise work of step g+1;
+//   * dK / dV accumulate in tensor memory across the steps of an item (two accumulator sets, by item parity); dQ_i is
+//     double-buffered in tensor memory and pushed to global (fp32 red.add) one step late.
+// TMEM columns: S [0,128) dP [128,256) {dV,dK} x 2 [256,384) dQ x 2 [384,448) -> 512 allocated, 1 CTA / SM.
+struct BwdCursor {
+  int w, k, it, n_it, b, h, jblk;
+  bool valid;
+};
+DTC_DEVICE void bwd_cursor_decode(BwdCursor& c, int n_items, int BH, int H, int nblk) {
+  c.valid = c.w < n_items;
+  if (!c.valid) return;
+  c.jblk = c.w / BH;  // items are ordered by key block: block 0 (most query blocks) first
+  const int rest = c.w - c.jblk * BH;
+  c.b = rest / H;
+  c.h = rest - c.b * H;
+  c.n_it = nblk - c.jblk;
+  c.it = 0;
+}
+DTC_DEVICE void bwd_cursor_next(BwdCursor& c, int stride, int n_items, int BH, int H, int nblk) {
+  if (++c.it < c.n_it) return;
+  c.w += stride;
+  ++c.k;
+  bwd_cursor_decode(c, n_items, BH, H, nblk);
+}
+
+template <int HD>
+__global__ void __launch_bounds__(288, 1)
+flash_attn_bwd_persist_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
+                              const __grid_constant__ CUtensorMap tm_v, const __grid_constant__ CUtensorMap tm_do,
+                              const float* __restrict__ lse2, const float* __restrict__ delta, float* __restrict__ dq_accum,
+                              long long lddq, bf16* __restrict__ dk, bf16* __restrict__ dv, long long lddkv, int T, int H,
+                              int B, float scale, float scale_log2) {
+  using C = AttnCfg<HD>;
+  static_assert(HD == 32, "the pipelined backward is laid out for head_dim 32");
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* sP = smem;                      // 2 buffers of [128 q x 128 k] bf16
+  uint8_t* sDS = sP + 2 * C::P_BYTES;      // 2 buffers
+  uint8_t* sK = sDS + 2 * C::P_BYTES;      // 2 buffers (item parity)
+  uint8_t* sV = sK + 2 * C::TILE_BYTES;    // 2 buffers
+  uint8_t* sQ = sV + 2 * C::TILE_BYTES;    // 2 stages (step parity)
+  uint8_t* sDO = sQ + 2 * C::TILE_BYTES;   // 2 stages
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sDO + 2 * C::TILE_BYTES);
+  uint64_t* bar_kv = bars;      // [2] K_j / V_j of item k landed
+  uint64_t* bar_ld = bars + 2;  // [2] Q_i and dO_i of step g landed
+  uint64_t* bar_s = bars + 4;   //     S_g / dP_g complete
+  uint64_t* bar_c = bars + 5;   //     S_g / dP_g pulled into registers by all 8 softmax warps
+  uint64_t* bar_p = bars + 6;   // [2] P_g / dS_g written (and the deferred read-outs of step g-1 done)
+  uint64_t* bar_d = bars + 8;   // [2] products of step g complete
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 10);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int nblk = T / ATT_BLK;
+  const int BH = B * H;
+  const int n_items = BH * nblk;
+  const int stride = gridDim.x;
+
+  if (tid == 0) {
+    tma_prefetch_desc(&tm_q);
+    tma_prefetch_desc(&tm_k);
+    tma_prefetch_desc(&tm_v);
+    tma_prefetch_desc(&tm_do);
+    mbar_init(bar_s, 1);
+    mbar_init(bar_c, 8);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&bar_kv[s], 1);
+      mbar_init(&bar_ld[s], 1);
+      mbar_init(&bar_p[s], 8);
+      mbar_init(&bar_d[s], 1);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 8) {
+    tmem_alloc(tmem_ptr_smem, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+  pdl_launch_dependents();
+  pdl_wait();
+  const uint32_t tm_s = tmem_base, tm_dp = tmem_base + 128;
+  const uint32_t tm_acc = tmem_base + 256;        // + (k & 1) * 2 * HD : dV, then dK at + HD
+  const uint32_t tm_dq = tmem_base + 256 + 4 * HD;  // + (g & 1) * HD
+
+  BwdCursor first;
+  first.w = blockIdx.x;
+  first.k = 0;
+  bwd_cursor_decode(first, n_items, BH, H, nblk);
+
+  if (warp == 8) {
+    // ------------------------------ issue warp ------------------------------
+    if (elect_one() && first.valid) {
+      constexpr uint32_t idesc_kk = make_idesc_bf16(128, 128, 0, 0);
+      constexpr uint32_t idesc_kn = make_idesc_bf16(128, HD, 0, 1);
+      constexpr uint32_t idesc_nn = make_idesc_bf16(128, HD, 1, 1);
+      auto load_kv = [&](const BwdCursor& c) {
+        const int kb = c.k & 1;
+        const int kv_row0 = c.b * T + c.jblk * ATT_BLK;
+        mbar_expect_tx(&bar_kv[kb], 2 * C::TILE_BYTES);
+        tma_load_2d(sK + kb * C::TILE_BYTES, &tm_k, &bar_kv[kb], c.h * HD, kv_row0);
+        tma_load_2d(sV + kb * C::TILE_BYTES, &tm_v, &bar_kv[kb], c.h * HD, kv_row0);
+      };
+      auto load_qdo = [&](const BwdCursor& c, int g) {
+        const int st = g & 1;
+        const int row = c.b * T + (c.jblk + c.it) * ATT_BLK;
+        mbar_expect_tx(&bar_ld[st], 2 * C::TILE_BYTES);
+        tma_load_2d(sQ + st * C::TILE_BYTES, &tm_q, &bar_ld[st], c.h * HD, row);
+        tma_load_2d(sDO + st * C::TILE_BYTES, &tm_do, &bar_ld[st], c.h * HD, row);
+      };
+      auto issue_scores = [&](const BwdCursor& c, int g) {  // S = Q_i K_j^T, dP = dO_i V_j^T
+        const int st = g & 1, kb = c.k & 1;
+        if (c.it == 0) mbar_wait(&bar_kv[kb], (c.k >> 1) & 1);
+        mbar_wait(&bar_ld[st], (g >> 1) & 1);
+        tc_fence_after();
+        const uint32_t ak = smem_u32(sK + kb * C::TILE_BYTES), av = smem_u32(sV + kb * C::TILE_BYTES),
+                       aq = smem_u32(sQ + st * C::TILE_BYTES), ado = smem_u32(sDO + st * C::TILE_BYTES);
+#pragma unroll
+        for (int kk = 0; kk < HD / 16; ++kk)
+          umma_bf16(tm_s, make_smem_desc(aq + kk * 32, 16, C::SBO, C::SWZ), make_smem_desc(ak + kk * 32, 16, C::SBO, C::SWZ),
+                    idesc_kk, kk > 0);
+#pragma unroll
+        for (int kk = 0; kk < HD / 16; ++kk)
+          umma_bf16(tm_dp, make_smem_desc(ado + kk * 32, 16, C::SBO, C::SWZ), make_smem_desc(av + kk * 32, 16, C::SBO, C::SWZ),
+                    idesc_kk, kk > 0);
+        umma_commit(bar_s);
+      };
+      BwdCursor cur = first, ld = first;
+      load_kv(ld);
+      load_qdo(ld, 0);
+      bwd_cursor_next(ld, stride, n_items, BH, H, nblk);
+      if (ld.valid) {
+        if (ld.it == 0) load_kv(ld);
+        load_qdo(ld, 1);
+        bwd_cursor_next(ld, stride, n_items, BH, H, nblk);
+      }
+      issue_scores(cur, 0);
+      for (int g = 0; cur.valid; ++g) {
+        const int st = g & 1;
+        const uint32_t ph = (g >> 1) & 1;
+        // S_g / dP_g are in registers everywhere: the tensor cores may start on step g+1 under the exp2 work
+        mbar_wait(bar_c, g & 1);
+        BwdCursor nxt = cur;
+        bwd_cursor_next(nxt, stride, n_items, BH, H, nblk);
+        if (nxt.valid) issue_scores(nxt, g + 1);
+        // P_g / dS_g are in shared memory (dQ buffer st and, for a new item, its accumulator set have been read out)
+        mbar_wait(&bar_p[st], ph);
+        tc_fence_after();
+        const int kb = cur.k & 1;
+        const uint32_t apt = smem_u32(sP + st * C::P_BYTES), adst = smem_u32(sDS + st * C::P_BYTES),
+                       aq = smem_u32(sQ + st * C::TILE_BYTES), ado = smem_u32(sDO + st * C::TILE_BYTES),
+                       ak = smem_u32(sK + kb * C::TILE_BYTES);
+        const uint32_t tm_dv = tm_acc + kb * 2 * HD, tm_dk = tm_dv + HD;
+        // dV += P^T dO_i ; dK += dS^T Q_i : A = the [q x k] tile read MN-major (M = keys contiguous, 16 query rows per step)
+#pragma unroll
+        for (int kk = 0; kk < ATT_BLK / 16; ++kk)
+          umma_bf16(tm_dv, make_smem_desc(apt + kk * 2048, ATT_BLK * 128, 1024, SWZ_128B),
+                    make_smem_desc(ado + kk * 16 * C::ROW_BYTES, 16, C::SBO, C::SWZ), idesc_nn,
+                    (cur.it > 0 || kk > 0) ? 1u : 0u);
+#pragma unroll
+        for (int kk = 0; kk < ATT_BLK / 16; ++kk)
+          umma_bf16(tm_dk, make_smem_desc(adst + kk * 2048, ATT_BLK * 128, 1024, SWZ_128B),
+                    make_smem_desc(aq + kk * 16 * C::ROW_BYTES, 16, C::SBO, C::SWZ), idesc_nn,
+                    (cur.it > 0 || kk > 0) ? 1u : 0u);
+        // dQ_i = dS K_j : A = the same tile K-major (two 64-key blocks), B = K_j MN-major
+#pragma unroll
+        for (int kk = 0; kk < ATT_BLK / 16; ++kk) {
+          const uint32_t a_off = (kk >> 2) * (ATT_BLK * 128) + (kk & 3) * 32;
+          umma_bf16(tm_dq + st * HD, make_smem_desc(adst + a_off, 16, 1024, SWZ_128B),
+                    make_smem_desc(ak + kk * 16 * C::ROW_BYTES, 16, C::SBO, C::SWZ), idesc_kn, kk > 0);
+        }
+        umma_commit(&bar_d[st]);
+        // operands of step g (Q / dO stage st; K / V of an item whose last step this was) are free once its products
+        // complete: fetch step g+2 — and the K / V of its item when it opens one — behind them
+        if (ld.valid) {
+          mbar_wait(&bar_d[st], ph);
+          if (ld.it == 0) load_kv(ld);
+          load_qdo(ld, g + 2);
+          bwd_cursor_next(ld, stride, n_items, BH, H, nblk);
+        }
+        cur = nxt;
+      }
+    }
+  } else {
+    // ------------------------------ softmax warps ------------------------------
+    const int row = (warp & 3) * 32 + lane;  // query row inside the block (TMEM lane)
+    const int gq = warp >> 2;                // key-column half handled by this warp
+    const uint32_t lane_sel = (uint32_t)((warp & 3) * 32) << 16;
+    // read-outs owed for the previous step: its dQ block and, when it closed an item, that item's dK / dV
+    auto flush = [&](const BwdCursor& p, int g) {
+      const int st = g & 1;
+      mbar_wait(&bar_d[st], (g >> 1) & 1);
+      tc_fence_after();
+      uint32_t rq[16];
+      tmem_ld_32x32b_x16(tm_dq + st * HD + lane_sel + gq * 16, rq);
+      const bool last = p.it == p.n_it - 1;
+      uint32_t rk[16], rv[16];
+      if (last) {
+        tmem_ld_32x32b_x16(tm_acc + (p.k & 1) * 2 * HD + lane_sel + gq * 16, rv);
+        tmem_ld_32x32b_x16(tm_acc + (p.k & 1) * 2 * HD + HD + lane_sel + gq * 16, rk);
+      }
+      tmem_ld_wait();
+      float* dq_row = dq_accum + (long long)(p.b * T + (p.jblk + p.it) * ATT_BLK + row) * lddq + p.h * HD + gq * 16;
+#pragma unroll
+      for (int e = 0; e < 16; e += 4)
+        red_add_v4_f32_attn(dq_row + e, __uint_as_float(rq[e]) * scale, __uint_as_float(rq[e + 1]) * scale,
+                            __uint_as_float(rq[e + 2]) * scale, __uint_as_float(rq[e + 3]) * scale);
+      if (last) {
+        const long long kv_row = (long long)(p.b * T + p.jblk * ATT_BLK + row);
+        bf16* dk_row = dk + kv_row * lddkv + p.h * HD + gq * 16;
+        bf16* dv_row = dv + kv_row * lddkv + p.h * HD + gq * 16;
+#pragma unroll
+        for (int gg = 0; gg < 2; ++gg) {
+          const int e = gg * 8;
+          float fk[8], fv[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            fk[u] = __uint_as_float(rk[e + u]) * scale;
+            fv[u] = __uint_as_float(rv[e + u]);
+          }
+          *reinterpret_cast<uint4*>(dk_row + e) = make_uint4(pack_bf16x2(fk[0], fk[1]), pack_bf16x2(fk[2], fk[3]),
+                                                             pack_bf16x2(fk[4], fk[5]), pack_bf16x2(fk[6], fk[7]));
+          *reinterpret_cast<uint4*>(dv_row + e) = make_uint4(pack_bf16x2(fv[0], fv[1]), pack_bf16x2(fv[2], fv[3]),
+                                                             pack_bf16x2(fv[4], fv[5]), pack_bf16x2(fv[6], fv[7]));
+        }
+      }
+    };
+    BwdCursor cur = first, prev = first;
+    int g = 0;
+    for (; cur.valid; ++g) {
+      const int st = g & 1;
+      const int i = cur.jblk + cur.it;
+      const long long stat = ((long long)cur.b * H + cur.h) * T + i * ATT_BLK + row;
+      const float lse_r = lse2[stat];
+      const float delta_r = delta[stat];
+      mbar_wait(bar_s, g & 1);
+      tc_fence_after();
+      uint32_t rs[64], rp[64];
+      tmem_ld_32x32b_x32(tm_s + lane_sel + gq * 64, rs);
+      tmem_ld_32x32b_x32(tm_s + lane_sel + gq * 64 + 32, rs + 32);
+      tmem_ld_32x32b_x32(tm_dp + lane_sel + gq * 64, rp);
+      tmem_ld_32x32b_x32(tm_dp + lane_sel + gq * 64 + 32, rp + 32);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_c);
+      if (cur.it == 0) {  // diagonal block (i == j): key column c is visible to query row r iff c <= r
+        const int lim = row - gq * 64;
+#pragma unroll
+        for (int e = 0; e < 64; ++e)
+          if (e > lim) rs[e] = 0xff800000u;  // -inf -> P = 0
+      }
+      uint8_t* pbuf = sP + st * C::P_BYTES;
+      uint8_t* dsbuf = sDS + st * C::P_BYTES;
+#pragma unroll
+      for (int gg = 0; gg < 8; ++gg) {
+        float p[8], ds[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          p[e] = ex2_ftz(fmaf(__uint_as_float(rs[gg * 8 + e]), scale_log2, -lse_r));
+          ds[e] = p[e] * (__uint_as_float(rp[gg * 8 + e]) - delta_r);
+        }
+        const uint32_t off = p_tile_offset(row, gq * 8 + gg);
+        *reinterpret_cast<uint4*>(pbuf + off) =
+            make_uint4(pack_bf16x2(p[0], p[1]), pack_bf16x2(p[2], p[3]), pack_bf16x2(p[4], p[5]), pack_bf16x2(p[6], p[7]));
+        *reinterpret_cast<uint4*>(dsbuf + off) = make_uint4(pack_bf16x2(ds[0], ds[1]), pack_bf16x2(ds[2], ds[3]),
+                                                            pack_bf16x2(ds[4], ds[5]), pack_bf16x2(ds[6], ds[7]));
+      }
+      if (g >= 1) flush(prev, g - 1);  // issued a whole element-wise pass ago: complete by now
+      fence_proxy_async_smem();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bar_p[st]);
+      prev = cur;
+      bwd_cursor_next(cur, stride, n_items, BH, H, nblk);
+    }
+    if (g >= 1) flush(prev, g - 1);
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 8) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
 template <int HD>
 static int attn_tmap(CUtensorMap* m, const void* p, long long rows, int H, long long ld) {
   return make_tmap_2d_bf16(m, p, rows, (uint64_t)H * HD, ld, ATT_BLK, HD,
@@ -1391,6 +1690,21 @@ static int launch_bwd(const void* q, const void* k, const void* v, long long ld,
   static const bool use_v1 = getenv("DTC_ATTN_BWD_V1") != nullptr;  // A/B switch: TMEM-accumulator kernel
   static const bool use_regacc = getenv("DTC_ATTN_BWD_REGACC") != nullptr;  // A/B switch: the un-pipelined register-accumulator kernel
   if constexpr (HD == 32) {
+    static const bool use_persist = getenv("DTC_ATTN_BWD_PERSIST") != nullptr;  // opt-in until validated on hardware
+    if (!use_v1 && !use_regacc && use_persist) {
+      const int smem4 = 4 * C::P_BYTES + 8 * C::TILE_BYTES + 1024 + 256;
+      auto kern4 = flash_attn_bwd_persist_kernel<HD>;
+      static dtc::SmemOptIn configured4;  // per device
+      DTC_CHECK_CUDA(dtc::ensure_dyn_smem(kern4, smem4, configured4));
+      int dev = 0, sms = 148;
+      if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+      const int n_items = B * H * (T / ATT_BLK);
+      const int grid4 = n_items < sms ? n_items : sms;
+      DTC_CHECK_CUDA(dtc::launch(kern4, grid4, 288, smem4, stream, tq, tk, tv, tdo, lse2, delta, dq_accum, lddq,
+                                 reinterpret_cast<bf16*>(dk), reinterpret_cast<bf16*>(dv), lddkv, T, H, B, scale_,
+                                 scale_ * LOG2E));
+      return 0;
+    }
     if (!use_v1 && !use_regacc) {
       const int smem3 = 4 * C::P_BYTES + 6 * C::TILE_BYTES + 1024 + 256;
       auto kern3 = flash_attn_bwd_pipe_kernel<HD>;

@@ -76,7 +76,34 @@ __global__ void cast_f32_to_bf16_2d_kernel(const float* __restrict__ in, long lo
   }
 }
 
+// Test aid for the cross-rank flag protocols: stall the stream for a pseudo-random time that differs per
+// rank, per call site and per training step, so that ranks reach every barrier / signal in a different order on every
+// replay of the captured step graph.  `step` is the device-side optimizer step counter (changes between replays).
+__global__ void jitter_kernel(unsigned seed, unsigned max_ns, const int* __restrict__ step) {
+  unsigned x = seed * 2654435761u + (unsigned)(step ? *step : 0) * 40503u + 0x9e3779b9u;
+  x ^= x >> 16;
+  x *= 0x85ebca6bu;
+  x ^= x >> 13;
+  x *= 0xc2b2ae35u;
+  x ^= x >> 16;
+  const unsigned long long want = max_ns ? (x % max_ns) : 0;
+  unsigned long long t0, t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  do {
+    __nanosleep(200);
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  } while (t - t0 < want);
+}
+
 }  // namespace dtc
+
+// Delay the stream by hash(seed, *step) % max_ns nanoseconds (one thread; see jitter_kernel).  max_ns <= 1 ms.
+extern "C" int dtc_jitter(unsigned seed, unsigned max_ns, const int* step, cudaStream_t stream) {
+  DTC_CHECK_ARG(max_ns <= 1000000u, "jitter: max_ns %u too large (<= 1000000)", max_ns);
+  DTC_CHECK_CUDA(dtc::launch(dtc::jitter_kernel, 1, 1, 0, stream, seed, max_ns, step));
+  DTC_CHECK_LAUNCH();
+  return 0;
+}
 
 extern "C" int dtc_cast_f32_to_bf16(const float* in, void* out, long long n, cudaStream_t stream) {
   DTC_CHECK_ARG(n >= 0, "cast: negative size");

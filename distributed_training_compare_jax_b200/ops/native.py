@@ -42,6 +42,7 @@ _PROTOS: dict[str, list[Any]] = {
     "dtc_adamw": [P, P, P, P, P, L, P, P, F, F, F, F, F, F, I],
     "dtc_colsum": [P, L, I, I, P],
     "dtc_symm_barrier": [P, I, I, I],
+    "dtc_jitter": [U32, U32, P],
     "dtc_gemm_bf16_scatter": [P, L, P, L, I, I, I, I, P, I, I, L, I, I],
     "dtc_gemm_wgrad_grouped": [I, P, P, P, P, P, P, I, P, P, F, I, I],
     "dtc_colsum_grouped": [I, P, P, P, P, P],

@@ -139,6 +139,7 @@ class FusedShardedStep:
         self.grad, self.compute = st.symm["grad"], st.symm["compute"]
         self.norm_slots = SymmBuffer(16, torch.float32, st.device, dp.group)
         self.barrier = FlagBarrier(st.device, dp.group)
+        self.barrier.step_counter = st.step
         self.scalars = torch.zeros(2, device=st.device, dtype=torch.float32)
         self.max_norm = cfg.grad_clip
         self.uses_multicast = bool(self.grad.mc_ptr and self.compute.mc_ptr)

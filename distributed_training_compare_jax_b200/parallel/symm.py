@@ -41,10 +41,21 @@ class FlagBarrier:
     N_SLOTS = 16
 
     def __init__(self, device: torch.device, group):
+        import os
         self.buf = SymmBuffer(self.N_SLOTS * 16, torch.int32, device, group)
         self.rank, self.world = self.buf.rank, self.buf.world
+        # Protocol stress test (tests/test_multigpu.py): DTC_SYNC_JITTER_NS=<max ns> puts a per-rank, per-call-site,
+        # per-step pseudo-random delay in front of every barrier, so ranks arrive in a different order on every replay
+        # of the step graph.  `step_counter` (device int that changes between replays) is set by the owner.
+        self.jitter_ns = int(os.environ.get("DTC_SYNC_JITTER_NS", "0"))
+        self.step_counter = None
+        self._calls = 0
 
     def __call__(self, slot: int) -> None:
+        if self.jitter_ns:
+            self._calls += 1
+            native.call("dtc_jitter", (self.rank * 7919 + self._calls * 104729 + slot) & 0xFFFFFFFF, self.jitter_ns,
+                        self.step_counter)
         native.call("dtc_symm_barrier", self.buf.ptr_array, self.rank, self.world, slot)
 
     @property

@@ -75,6 +75,8 @@ class SeqParallelState:
         self.dA, self.dB, self.dMID = full[2 * L + 1], full[2 * L + 2], full[2 * L + 3]
         self.part = full[2 * L + 4]                            # viewed by the kernels as [n, Ms, D]
         self.barrier_flags = FlagBarrier(dev, tp.group) if n > 1 else None
+        if self.barrier_flags is not None:
+            self.barrier_flags.step_counter = engine.store.step
         self._slot = 0
         self._ptr_cache: dict[int, tuple] = {}
         # ---- local: owned rows of the residual stream and the LayerNorm statistics

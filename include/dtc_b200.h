@@ -104,6 +104,9 @@ int dtc_colsum(const void* x, long long ld, int M, int N, float* out, cudaStream
  * *_ptrs: HOST arrays of `world` device addresses (every rank's copy of a symmetric buffer); mc_*: NVSwitch
  * multicast address of the same buffer (0 = none: peer loads / stores are used instead). */
 int dtc_symm_barrier(const unsigned long long* flag_ptrs, int rank, int world, int slot, cudaStream_t stream);
+/* Protocol stress aid (the reference has no race tooling): stalls the stream for
+ * hash(seed, *step) % max_ns nanoseconds, max_ns <= 1e6; `step` = device int that changes between graph replays (or NULL). */
+int dtc_jitter(unsigned seed, unsigned max_ns, const int* step, cudaStream_t stream);
 int dtc_dp_num_partials(long long n);
 int dtc_dp_reduce_scatter(float* local_grad, unsigned long long mc_grad, const unsigned long long* grad_ptrs, int rank,
                           int world, long long off, long long n, float* partials, cudaStream_t stream);

@@ -153,3 +153,21 @@ def test_tp2_sequence_parallel_folded_barriers(single, tmp_path, monkeypatch):
     monkeypatch.setenv("DTC_SP_FOLD", "1")
     loss = _run(tmp_path, "tp2_sp_fold", "tp", 2, tp_seq_parallel=True)
     np.testing.assert_allclose(loss, single, rtol=5e-3, atol=5e-3)
+
+
+@pytest.mark.skipif(NGPU < 2, reason="needs >= 2 GPUs")
+@pytest.mark.parametrize("parallel", ["tp", "dp"])
+def test_flag_protocols_survive_jitter_over_many_graph_replays(tmp_path, parallel, monkeypatch):
+    """Race check on hardware for the in-graph flag barriers (compute-sanitizer is closed on this pool):
+    6000 replays of the captured step graph, with a pseudo-random delay of up to 30 us — different per rank, per barrier
+    call site and per step — in front of every cross-rank barrier, so the ranks reach each of the 16 reused flag slots in
+    a different order every step.  A lost or stale flag shows up as a hang (bounded spins trap) or as a diverging loss:
+    the jittered run must reproduce the loss curve of the un-jittered one."""
+    steps = 6000
+    ref = _run(tmp_path, f"{parallel}2_calm", parallel, 2, steps=steps, log_every=2000, tp_seq_parallel=True)
+    monkeypatch.setenv("DTC_SYNC_JITTER_NS", "30000")
+    loss = _run(tmp_path, f"{parallel}2_jitter", parallel, 2, steps=steps, log_every=2000, tp_seq_parallel=True)
+    assert np.all(np.isfinite(loss))
+    # fp32 atomics make the two runs differ in rounding only; over 6000 steps that stays far below 2 % of the loss
+    np.testing.assert_allclose(loss[-200:].mean(), ref[-200:].mean(), rtol=2e-2)
+    np.testing.assert_allclose(loss[:50], ref[:50], rtol=5e-3, atol=5e-3)
