@@ -89,7 +89,7 @@ def run_arm(args, arm: str) -> dict:
                      output_dir="outputs/bench", pp_microbatches=args.pp_microbatches, warmup_steps=args.warmup,
                      global_batch_is_per_device=weak, sync_every_step=True, backend=args.backend,
                      pp_schedule=args.pp_schedule, fused_comm=not args.no_fused_comm, cuda_graph=not args.no_graph,
-                     dp_overlap=not args.no_dp_overlap, tp_fused=args.tp_fused,
+                     dp_overlap=not args.no_dp_overlap,
                      tp_seq_parallel=not args.no_tp_seq_parallel, pp_cuda_graph=not args.no_pp_graph)
     mc = load_model_config(os.path.join(ROOT, args.model_config), vocab_size=VOCAB_SIZE, parallel=strategy)
     oc = load_optim_config(os.path.join(ROOT, "configs/optim_config.yaml"))
@@ -174,8 +174,7 @@ def run_arm(args, arm: str) -> dict:
                  "tp": ("sequence-parallel: GEMM-epilogue reduce-scatter (P2P stores) + LayerNorm all-gather ("
                         + ("multimem.st" if eng.sp.use_mc else "peer stores") + ")"
                         if hasattr(eng, "sp") else
-                        "GEMM epilogue multimem.red all-reduce" if getattr(eng, "tp_hooks", None) is not None
-                        else ("GEMM + NCCL all-reduce" if tp > 1 else "none")),
+                        ("GEMM + NCCL all-reduce" if tp > 1 else "none")),
                  "pp": ("NCCL send/recv, one communicator per direction"
                         + (", one CUDA graph per (F|B, microbatch)" if tc.pp_cuda_graph and tc.cuda_graph else ", eager launches")
                         ) if pp > 1 else "none"}
@@ -268,7 +267,6 @@ def main() -> int:
     ap.add_argument("--backend", default="auto")
     ap.add_argument("--no-fused-comm", action="store_true")
     ap.add_argument("--no-dp-overlap", action="store_true")
-    ap.add_argument("--tp-fused", action="store_true", help="TP: fused GEMM + multimem.red all-reduce epilogue")
     ap.add_argument("--tp-seq-parallel", action="store_true", help="(default) TP: row-sharded residual stream, "
                     "GEMM-epilogue reduce-scatter + LayerNorm all-gather")
     ap.add_argument("--no-tp-seq-parallel", action="store_true", help="TP: replicated activations, GEMM + NCCL all-reduce")

@@ -73,7 +73,6 @@ class TrainConfig:
     sync_every_step: bool = True      # blocking loss fetch each step like the reference (train/train.py:82-83)
     backend: str = "auto"             # "auto" (native kernels on CUDA, torch oracle on CPU) | "native" | "torch"
     cuda_graph: bool = True           # replay the captured step graph on the native path
-    tp_fused: bool = False            # TP: GEMM epilogue multimem.red all-reduce instead of GEMM + NCCL all-reduce (measured slower)
     dp_overlap: bool = True           # fused DP: reduce-scatter each layer's gradient bucket during the backward pass
     tp_seq_parallel: bool = True      # TP: row-sharded residual stream, GEMM-epilogue reduce-scatter + LayerNorm all-gather (parallel/tp_sp.py; +22 % at TP2 vs GEMM + NCCL all-reduce, falls back when batch % tp != 0)
     pp_cuda_graph: bool = True        # PP: one CUDA graph per (forward | backward, microbatch) of a stage (2 GPUs: 7.49 -> 5.59 ms/step)

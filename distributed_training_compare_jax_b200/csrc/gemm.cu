@@ -38,10 +38,8 @@ enum GemmEpiMode : int {
   EPI_DGELU = 3,          // out_bf16 = acc * gelu_tanh'(aux)
   EPI_ATOMIC_F32 = 4,     // out_f32 += alpha*acc      (split-K / gradient accumulation)
   EPI_STORE_F32 = 5,      // out_f32 = alpha*acc + bias
-  // Fused GEMM -> all-reduce over NVSwitch multicast: every rank reduce-adds its partial tile (rank 0 also adds
-  // bias + residual) into ALL ranks' copies of a zeroed symmetric bf16 buffer with multimem.red (`out` is the
-  // multicast address).  Persistent kernel only.
-  EPI_MC_RED_BF16 = 6,
+  // (6 was the GEMM -> multimem.red all-reduce epilogue of round 1: slower than GEMM + NCCL at every rank count and
+  // superseded by the reduce-scatter epilogue below; removed)
   // Fused GEMM -> reduce-scatter for sequence-parallel TP: output rows [o*sp_rows, (o+1)*sp_rows) belong to rank o; the
   // bf16 tile is stored over NVLink into THIS rank's partial-sum slot of rank o's symmetric buffer
   // (peer_out[o] + (sp_rank*sp_rows + row - o*sp_rows)*ldo), tile by tile while later tiles are still in the tensor
@@ -105,11 +103,6 @@ struct GemmSmem {
   static constexpr int bytes(int stages) { return stages * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/; }
 };
 
-DTC_DEVICE void mc_red_add_bf16x8(bf16* mc_addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
-  asm volatile("multimem.red.relaxed.sys.global.add.v4.bf16x2 [%0], {%1, %2, %3, %4};" ::"l"(mc_addr), "r"(a), "r"(b),
-               "r"(c), "r"(d)
-               : "memory");
-}
 DTC_DEVICE void red_add_v4_f32(float* addr, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
@@ -394,7 +387,7 @@ gemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
   const int total_tiles = tiles_mn * splits;
   const int mode = epi.mode;
   const bool bf16_out = mode <= EPI_DGELU || SCATTER;  // outputs that leave through the smem staging tile
-  const bool use_aux = (mode == EPI_BIAS_RESIDUAL || mode == EPI_DGELU || (mode == EPI_MC_RED_BF16 && epi.aux != nullptr));
+  const bool use_aux = (mode == EPI_BIAS_RESIDUAL || mode == EPI_DGELU);
   const bool coop_store = SCATTER || epi.coop_store;   // staged tile written out by the epilogue warps (no TMA store)
 
   if (warp == 0 && lane == 0) {
@@ -572,24 +565,6 @@ gemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
               v[2 * j + 1] += f.y;
             }
           }
-          if (mode == EPI_MC_RED_BF16) {
-            if (use_aux) {  // rank 0 carries the residual tile (TMA-staged like the residual epilogue)
-              const uint32_t aoff =
-                  (uint32_t)(c >> 1) * S::HALF_BYTES + swizzle_offset<3>(row * 128 + ((c & 1) * 4 + g) * 16);
-              const uint4 a = *reinterpret_cast<const uint4*>(stage_aux + aoff);
-              const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
-#pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                const float2 f = unpack_bf16x2(aw[j]);
-                v[2 * j] += f.x;
-                v[2 * j + 1] += f.y;
-              }
-            }
-            if (!row_ok || n >= N) continue;
-            mc_red_add_bf16x8(reinterpret_cast<bf16*>(epi.out) + gm * epi.ldo + n, pack_bf16x2(v[0], v[1]),
-                              pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
-            continue;
-          }
           if (!bf16_out) {
             if (!row_ok || n >= N) continue;
             float* o = reinterpret_cast<float*>(epi.out) + gm * epi.ldo + n;
@@ -749,9 +724,6 @@ static int launch_gemm_persistent(const void* A, long long lda, const void* B, l
         (rc = make_tmap_2d_bf16(&taux, epi.aux, M, N, epi.ld_aux, BM, 64, CU_TENSOR_MAP_SWIZZLE_128B)))
       return rc;
   }
-  if (epi.mode == EPI_MC_RED_BF16 && epi.aux != nullptr &&
-      (rc = make_tmap_2d_bf16(&taux, epi.aux, M, N, epi.ld_aux, BM, 64, CU_TENSOR_MAP_SWIZZLE_128B)))
-    return rc;
   const int total_kb = (K + BK - 1) / BK;
   if (splits < 1) splits = 1;
   if (splits > total_kb) splits = total_kb;
@@ -1408,7 +1380,7 @@ extern "C" int dtc_gemm_bf16(const void* A, long long lda, int a_mn_major, const
   DTC_CHECK_ARG(lda % 8 == 0 && ldb % 8 == 0, "gemm: lda=%lld ldb=%lld must be multiples of 8 elements", lda, ldb);
   DTC_CHECK_ARG(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0 && ((uintptr_t)out & 15) == 0,
                 "gemm: operand pointers must be 16-byte aligned");
-  DTC_CHECK_ARG(epi_mode >= 0 && epi_mode <= 6, "gemm: bad epilogue mode %d (the scatter epilogue has its own entry point)", epi_mode);
+  DTC_CHECK_ARG(epi_mode >= 0 && epi_mode <= 5, "gemm: bad epilogue mode %d (the scatter epilogue has its own entry point)", epi_mode);
   DTC_CHECK_ARG(splits <= 1 || epi_mode == EPI_ATOMIC_F32, "gemm: split-K needs the fp32 reduce-add epilogue");
   DTC_CHECK_ARG(!(epi_mode == EPI_BIAS_RESIDUAL || epi_mode == EPI_DGELU) || aux != nullptr, "gemm: aux missing");
   DTC_CHECK_ARG(epi_mode != EPI_BIAS_GELU || out2 != nullptr, "gemm: out2 missing");
@@ -1432,21 +1404,24 @@ extern "C" int dtc_gemm_bf16(const void* A, long long lda, int a_mn_major, const
     // few 128-wide tiles (N = 512 layers: 128 tiles for 148 SMs): 64-wide tiles double the CTA count so that every SM
     // runs two CTAs, each served by the TMA path at its own ~48 B/cycle
     const long long t128 = (long long)((M + 127) / 128) * ((N + 127) / 128) * (splits > 1 ? splits : 1);
-    if (g_gemm_dual && g_gemm_bn64 && t128 <= num_sms() && N % 64 == 0 && epi_mode != EPI_BIAS_GELU &&
-        epi_mode != EPI_MC_RED_BF16)
+    if (g_gemm_dual && g_gemm_bn64 && t128 <= num_sms() && N % 64 == 0 && epi_mode != EPI_BIAS_GELU)
       block_n = 64;
   }
   static const bool env_v1 = getenv("DTC_GEMM_V1") != nullptr;  // A/B switch: one-tile-per-CTA kernel
-  const bool use_v1 = (env_v1 || g_gemm_impl == 1) && epi_mode != EPI_MC_RED_BF16;
-  if (epi_mode == EPI_MC_RED_BF16 && block_n == 256) block_n = 128;
-  // CTA-pair kernel: needs >= 256 rows; 256-wide tiles when that still leaves enough pair-tiles to fill the GPU
-  // default policy (impl 0): the CTA-pair kernel pays off on the big GEMMs (lm_head: +27 % on dgrad / wgrad,
-  // profiles/r1/gemm_microbench.txt); the layer GEMMs of this model are launch/latency-bound and stay 1-CTA
-  // (measured, device time: lm_head dgrad 306 -> 237 us, wgrad 309 -> 246 us; the forward orientation — A K-major,
-  // B MN-major, 412 MB of output — is no faster with pairs: 299 vs 288 us, so it keeps the 1-CTA kernel)
-  const bool big = 2.0 * M * N * (double)K >= 1e11 && (a_mn_major || !b_mn_major);
-  const bool want_2cta = (g_gemm_impl == 2 || g_gemm_impl == 3 || (g_gemm_impl == 0 && big && !env_v1)) &&
-                         epi_mode != EPI_MC_RED_BF16 && M >= 256 && N >= 128;  // impl 4 forces the 1-CTA persistent kernel
+  const bool use_v1 = env_v1 || g_gemm_impl == 1;
+  // CTA-pair kernel: needs >= 256 rows; 256-wide tiles when that still leaves enough pair-tiles to fill the GPU.
+  // Default policy (impl 0), from profiles/r2/gemm_microbench.txt (device time, this kernel vs the 1-CTA persistent one):
+  //   * big GEMMs (lm_head, >= 1e11 FLOP): always pairs — forward 251 -> 183 us, wgrad 234 -> 188 us;
+  //   * layer GEMMs of >= 6 GFLOP with a plain / GELU / residual epilogue (qkv 16.4 -> 14.3, fc1 23.5 -> 20.4,
+  //     fc2 20.6 -> 17.7, fc1 dgrad 20.2 -> 16.6 us); smaller ones (out_proj) and the GELU-backward epilogue are faster
+  //     on the 1-CTA kernel and stay there.  DTC_GEMM_PAIR_LAYERS=0 keeps every layer GEMM on the 1-CTA kernel.
+  static const bool pair_layers = !(getenv("DTC_GEMM_PAIR_LAYERS") && getenv("DTC_GEMM_PAIR_LAYERS")[0] == '0');
+  const double flops = 2.0 * M * N * (double)K;
+  const bool big = flops >= 1e11;
+  const bool mid = pair_layers && flops >= 6e9 && !a_mn_major && splits <= 1 &&
+                   (epi_mode == EPI_STORE_BF16 || epi_mode == EPI_BIAS_GELU || epi_mode == EPI_BIAS_RESIDUAL);
+  const bool want_2cta = (g_gemm_impl == 2 || g_gemm_impl == 3 || (g_gemm_impl == 0 && (big || mid) && !env_v1)) &&
+                         M >= 256 && N >= 128;  // impl 4 forces the 1-CTA persistent kernel
   if (want_2cta) {
     const long long tiles256 = (long long)((M + 255) / 256) * ((N + 255) / 256) * (splits > 1 ? splits : 1);
     // 256-wide pair tiles (half the operand bytes per MMA cycle again) whenever they still fill all 74 CTA pairs;
@@ -1468,7 +1443,7 @@ extern "C" int dtc_gemm_bf16(const void* A, long long lda, int a_mn_major, const
     // and the multicast-reduce epilogue, which need the second staging tile)
     const long long tiles128 = (long long)((M + 127) / 128) * ((N + block_n - 1) / block_n) * (splits > 1 ? splits : 1);
     // (always: the light configuration also lets a GEMM from the side stream share the SM)
-    const bool dual = g_gemm_dual && epi_mode != EPI_BIAS_GELU && epi_mode != EPI_MC_RED_BF16;
+    const bool dual = g_gemm_dual && epi_mode != EPI_BIAS_GELU;
     (void)tiles128;
 #define DTC_PGEMM_DISPATCH(AMN, BMN)                                                                                      \
   if (dual) {                                                                                                             \

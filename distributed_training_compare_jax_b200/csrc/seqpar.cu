@@ -60,7 +60,7 @@ DTC_DEVICE uint4 sp_load16(const bf16* p) {
   return *reinterpret_cast<const uint4*>(p);
 }
 
-// one warp per owned row; D = NCH * 256, the row lives in registers (body of the folded-barrier variant)
+// one warp per owned row; D = NCH * 256, the row lives in registers (shared by both kernel variants)
 template <int NCH, bool L2_COHERENT>
 DTC_DEVICE void sp_ln_fwd_row(const bf16* __restrict__ res, const bf16* __restrict__ bias, const bf16* __restrict__ part,
                               int n_part, long long part_stride, const bf16* __restrict__ gamma,
@@ -119,7 +119,8 @@ DTC_DEVICE void sp_ln_fwd_row(const bf16* __restrict__ res, const bf16* __restri
   }
 }
 
-// (validated kernel: kept verbatim, the folded-barrier variant below shares nothing with it but the math)
+// Barrier-kernel variant (default): the partial-sum slots were completed before this kernel started (flag barrier in
+// front of it), so the plain read-only load path is safe.
 template <int NCH>
 __global__ void __launch_bounds__(SP_WARPS * 32)
 sp_ln_fwd_kernel(const bf16* __restrict__ res, const bf16* __restrict__ bias, const bf16* __restrict__ part, int n_part,
@@ -128,59 +129,11 @@ sp_ln_fwd_kernel(const bf16* __restrict__ res, const bf16* __restrict__ bias, co
                  SpPeers peers, int n_out, long long out_row0, int Ms, float eps) {
   pdl_launch_dependents();  // PDL: let the next kernel's prologue overlap this kernel
   pdl_wait();               // ... and do not touch global memory before the previous kernel has completed
-  constexpr int D = NCH * 256;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long row = (long long)blockIdx.x * SP_WARPS + warp;
   if (row >= Ms) return;
-  float x[NCH * 8];
-  float s = 0.f, ss = 0.f;
-#pragma unroll
-  for (int k = 0; k < NCH; ++k) {
-    const int c = k * 256 + lane * 8;
-    const long long off = row * D + c;
-    float* xk = x + k * 8;
-#pragma unroll
-    for (int j = 0; j < 8; ++j) xk[j] = 0.f;
-    add_bf16x8(xk, *reinterpret_cast<const uint4*>(res + off));
-    if (bias != nullptr) add_bf16x8(xk, *reinterpret_cast<const uint4*>(bias + c));
-    for (int p = 0; p < n_part; ++p) add_bf16x8(xk, *reinterpret_cast<const uint4*>(part + p * part_stride + off));
-    // the residual stream is stored in bf16: normalise exactly what the backward pass will read back
-    const uint4 packed = make_uint4(pack_bf16x2(xk[0], xk[1]), pack_bf16x2(xk[2], xk[3]), pack_bf16x2(xk[4], xk[5]),
-                                    pack_bf16x2(xk[6], xk[7]));
-    if (hsum != nullptr) *reinterpret_cast<uint4*>(hsum + off) = packed;
-    const uint32_t w[4] = {packed.x, packed.y, packed.z, packed.w};
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const float2 f = unpack_bf16x2(w[j]);
-      xk[2 * j] = f.x;
-      xk[2 * j + 1] = f.y;
-      s += f.x + f.y;
-      ss += f.x * f.x + f.y * f.y;
-    }
-  }
-  s = warp_sum(s);
-  ss = warp_sum(ss);
-  const float mean = s / D;
-  const float var = fmaxf(ss / D - mean * mean, 0.f);
-  const float rstd = rsqrtf(var + eps);
-  if (lane == 0) {
-    mean_out[row] = mean;
-    rstd_out[row] = rstd;
-  }
-#pragma unroll
-  for (int k = 0; k < NCH; ++k) {
-    const int c = k * 256 + lane * 8;
-    const uint4 g = *reinterpret_cast<const uint4*>(gamma + c);
-    const uint4 b = *reinterpret_cast<const uint4*>(beta + c);
-    const uint32_t gw[4] = {g.x, g.y, g.z, g.w}, bw[4] = {b.x, b.y, b.z, b.w};
-    uint32_t o[4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const float2 gg = unpack_bf16x2(gw[j]), bb = unpack_bf16x2(bw[j]);
-      o[j] = pack_bf16x2((x[k * 8 + 2 * j] - mean) * rstd * gg.x + bb.x, (x[k * 8 + 2 * j + 1] - mean) * rstd * gg.y + bb.y);
-    }
-    sp_push16(mc_out, peers, n_out, (out_row0 + row) * D + c, make_uint4(o[0], o[1], o[2], o[3]));
-  }
+  sp_ln_fwd_row<NCH, false>(res, bias, part, n_part, part_stride, gamma, beta, hsum, mean_out, rstd_out, mc_out, peers,
+                            n_out, out_row0, eps, row, lane);
 }
 
 // Folded-barrier variant: optionally waits for the partial-sum slots of every rank in its prologue (wait_in) and

@@ -10,7 +10,7 @@ import torch
 
 from . import native
 
-EPI = {"store": 0, "bias_gelu": 1, "bias_residual": 2, "dgelu": 3, "atomic_f32": 4, "store_f32": 5, "mc_red": 6}
+EPI = {"store": 0, "bias_gelu": 1, "bias_residual": 2, "dgelu": 3, "atomic_f32": 4, "store_f32": 5}
 BF16 = torch.bfloat16
 F32 = torch.float32
 
@@ -44,7 +44,7 @@ def _check_rowmajor(t: torch.Tensor, name: str) -> None:
 def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = False, epi: str = "store",
          alpha: float = 1.0, bias: torch.Tensor | None = None, aux: torch.Tensor | None = None,
          out: torch.Tensor | None = None, out2: torch.Tensor | None = None, splits: int = 0, stages: int = 0,
-         block_n: int = 0, mc_out: tuple[int, int] | None = None) -> torch.Tensor:
+         block_n: int = 0) -> torch.Tensor:
     """D[M,N] = A·Bᵀ on the tcgen05 GEMM.  ``a`` is [M,K] (or [K,M] when ``a_mn``), ``b`` is [N,K]
     (or [K,N] when ``b_mn``).  See ``dtc_gemm_bf16`` for the epilogues."""
     _check_rowmajor(a, "a")
@@ -54,11 +54,6 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
     if K != Kb:
         raise ValueError(f"gemm: reduction dims differ ({K} vs {Kb})")
     mode = EPI[epi]
-    if mode == 6:  # fused GEMM -> NVLS all-reduce: `mc_out` = (multicast address of the symmetric buffer, its ld)
-        native.call("dtc_gemm_bf16", a, a.stride(0), int(a_mn), b, b.stride(0), int(b_mn), M, N, K, mode, float(alpha),
-                    bias, aux, aux.stride(0) if aux is not None else 0, mc_out[0], mc_out[1], None, 0, splits, stages,
-                    block_n)
-        return None
     if out is None:
         if mode == 4:
             raise ValueError("gemm: the fp32 reduce-add epilogue needs a caller-provided accumulator")

@@ -133,19 +133,10 @@ class NativeStageEngine(StageEngineBase):
                               torch.empty(M, D, device=self.device, dtype=BF16))]
                 w.group_args = {}
             self.ws.append(w)
-        self.tp_hooks = None  # set by parallel/tp.py when the fused GEMM+collective kernels are enabled
-
-    def begin_step(self) -> None:
-        super().begin_step()
-        if self.tp_hooks is not None:
-            self.tp_hooks.begin_step()
 
     # ---- building block shared by attention-out and fc2 (row-parallel Linear + bias + residual) ----
     def row_parallel_out(self, x, w, bias, residual, out) -> None:
         tp = self.mesh.tp
-        if self.tp_hooks is not None:
-            self.tp_hooks.row_parallel_out(self, x, w, bias, residual, out)
-            return
         if tp.size == 1 or tp.rank == 0:
             Fn.gemm(x, w, b_mn=True, bias=bias, epi="bias_residual", aux=residual, out=out)
         else:
@@ -180,10 +171,7 @@ class NativeStageEngine(StageEngineBase):
         return Fn.gemm_impl(self.bwd_gemm_impl)
 
     def tp_reduced_gemm(self, a, w, out) -> torch.Tensor:
-        """sum over TP ranks of a · wᵀ (dX of a column-parallel Linear, collectives X5 / X8).  Returns the tensor that
-        holds the result: ``out``, or — on the fused path — a dedicated symmetric buffer."""
-        if self.tp_hooks is not None:
-            return self.tp_hooks.reduced_gemm(self, a, w, out)
+        """sum over TP ranks of a · wᵀ (dX of a column-parallel Linear, collectives X5 / X8); returns ``out``."""
         Fn.gemm(a, w, out=out)
         self.mesh.tp.all_reduce(out)
         return out

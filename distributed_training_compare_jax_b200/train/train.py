@@ -66,10 +66,6 @@ def build_state(train_config: TrainConfig, model_config: ModelConfig, opt_config
     if native_dp and not fused_dp:
         from ..parallel.dp import make_grad_reducer
         reducer = make_grad_reducer(engine, mesh)   # NCCL: per-layer buckets overlapped with the backward pass
-    if (backend == "native" and mesh.tp.size > 1 and train_config.fused_comm and train_config.tp_fused
-            and not hasattr(engine, "sp")):
-        from ..parallel.tp import attach_fused_tp
-        attach_fused_tp(engine, mesh)
     if fused_dp:
         from ..parallel.dp import FusedShardedStep
         opt = FusedShardedStep(opt_config, engine, mesh, overlap=train_config.dp_overlap)

@@ -25,7 +25,7 @@ def test_bench_json_line_has_the_contract_keys():
               "vs_baseline", "dtype", "data", "config", "e2e", "gpu_launches", "clocks"):
         assert k in d, k
     assert d["n_gpus"] == 1 and d["steps"] == 3 and d["warmup"] >= 3 and d["higher_is_better"] is True
-    assert d["unit"] == "tokens/s" and d["value"] > 0 and d["scaling"] == "weak"
+    assert d["unit"] == "tokens/s" and d["value"] > 0 and d["scaling"] == "strong"   # the headline arm keeps the reference's GLOBAL batch 8
     assert set(d["e2e"]) >= {"value", "unit", "h2d_bytes_per_step", "d2h_bytes_per_step"}
     assert d["e2e"]["h2d_bytes_per_step"] == 2 * 2 * 128 * 4 and d["e2e"]["d2h_bytes_per_step"] == 4
     assert d["config"]["global_batch"] == 2 and d["config"]["seq_len"] == 128 and d["config"]["parallelism"] == "dp1"

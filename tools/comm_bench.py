@@ -83,17 +83,7 @@ del p, m, v, g2
 M, D, F = 4096, 512, 2048 // world
 x = (torch.randn(M, F, device=dev)).to(torch.bfloat16)
 w = (torch.randn(F, D, device=dev) * 0.05).to(torch.bfloat16)
-buf = SymmBuffer(M * D, torch.bfloat16, dev, grp)
 outb = torch.empty(M, D, device=dev, dtype=torch.bfloat16)
-slot = [0]
-
-
-def fused():
-    Fn.gemm(x, w, b_mn=True, epi="mc_red", mc_out=(buf.mc_ptr, D))
-    bar(3 + slot[0] % 12)
-    slot[0] += 1
-    outb.copy_(buf.tensor.view(M, D))
-    buf.tensor.zero_()
 
 
 def unfused():
@@ -114,15 +104,9 @@ def graphed(fn, reps=20):
     return lambda: g.replay(), reps
 
 
-if buf.mc_ptr:
-    slot[0] = 0
-    rf, reps = graphed(fused)
-    t_f = timed(rf, iters=5) / reps
-    ru, reps = graphed(unfused)
-    t_u = timed(ru, iters=5) / reps
-    wire = M * D * 2  # bf16 tile data every rank must push into the switch once
-    out["tp"] = {"fused_gemm_mcred_barrier_copy_zero_us": t_f, "gemm_plus_nccl_allreduce_us": t_u,
-                 "wire_time_at_770GBps_us": wire / LINK * 1e6, "shape": [M, D, F]}
+ru, reps = graphed(unfused)
+t_u = timed(ru, iters=5) / reps
+out["tp"] = {"gemm_plus_nccl_allreduce_us": t_u, "wire_time_at_770GBps_us": M * D * 2 / LINK * 1e6, "shape": [M, D, F]}
 # ---------------------------------------------------------------- TP, sequence-parallel form (parallel/tp_sp.py)
 # one sublayer boundary: row-parallel GEMM -> [sum over ranks + bias + residual] -> LayerNorm -> operand of the next GEMM
 #   plain : GEMM(+bias+residual epilogue) -> NCCL all-reduce of [M, D] -> LayerNorm over all M rows on every rank
