@@ -1417,7 +1417,7 @@ extern "C" int dtc_gemm_bf16(const void* A, long long lda, int a_mn_major, const
   //     on the 1-CTA kernel and stay there.  DTC_GEMM_PAIR_LAYERS=0 keeps every layer GEMM on the 1-CTA kernel.
   static const bool pair_layers = !(getenv("DTC_GEMM_PAIR_LAYERS") && getenv("DTC_GEMM_PAIR_LAYERS")[0] == '0');
   const double flops = 2.0 * M * N * (double)K;
-  const bool big = flops >= 1e11;
+  const bool big = flops >= 1e11 || (flops >= 2e10 && splits > 1);  // (split-K: the lm_head dgrad of a small local batch)
   const bool mid = pair_layers && flops >= 6e9 && !a_mn_major && splits <= 1 &&
                    (epi_mode == EPI_STORE_BF16 || epi_mode == EPI_BIAS_GELU || epi_mode == EPI_BIAS_RESIDUAL);
   const bool want_2cta = (g_gemm_impl == 2 || g_gemm_impl == 3 || (g_gemm_impl == 0 && (big || mid) && !env_v1)) &&
@@ -1426,7 +1426,7 @@ extern "C" int dtc_gemm_bf16(const void* A, long long lda, int a_mn_major, const
     const long long tiles256 = (long long)((M + 255) / 256) * ((N + 255) / 256) * (splits > 1 ? splits : 1);
     // 256-wide pair tiles (half the operand bytes per MMA cycle again) whenever they still fill all 74 CTA pairs;
     // ragged N is fine: TMA zero-fills the loads and clips the stores
-    const bool wide = (block_n_arg == 256) || ((g_gemm_impl == 3 || g_gemm_impl == 0) && block_n_arg == 0 && tiles256 >= 74);
+    const bool wide = (block_n_arg == 256) || ((g_gemm_impl == 3 || g_gemm_impl == 0) && block_n_arg == 0 && tiles256 >= 56);  // >= 3/4 of the 74 CTA pairs busy
     if (stages == 0) stages = PG_STAGE_MAX;
 #define DTC_2CTA_DISPATCH(AMN, BMN)                                                                               \
   if (wide) return launch_gemm_2cta<AMN, BMN, 256, 4>(A, lda, B, ldb, M, N, K, splits, stages, epi, stream);      \

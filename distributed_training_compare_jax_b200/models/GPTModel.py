@@ -117,7 +117,16 @@ class GPTModel:
             Fn.gemm(ws.lnf, ws.logits, a_mn=True, b_mn=True, epi="atomic_f32", out=g["wlm"], splits=1)
 
         eng.side_work(head_param_grads)
-        ws.dln_cur = eng.tp_reduced_gemm(ws.logits, c["wlm"], out=ws.dln)
+        # dL/d(lnf out) = dlogits · W_lmᵀ: [M, D] output (M/256 x D/256 pair tiles — 32 for the reference shapes, 4 for one
+        # sequence per rank) over a reduction of V = 50304: split K so that every CTA pair has a slice, accumulate in fp32
+        splits = max(1, 74 // max(1, -(-ws.M // 256) * -(-self.config.d_model // 256)))
+        if tp.size == 1 and splits > 1:
+            ws.dln_f32.zero_()
+            Fn.gemm(ws.logits, c["wlm"], epi="atomic_f32", out=ws.dln_f32, splits=min(splits, 32))
+            Fn.cast_bf16(ws.dln_f32, ws.dln)
+            ws.dln_cur = ws.dln
+        else:
+            ws.dln_cur = eng.tp_reduced_gemm(ws.logits, c["wlm"], out=ws.dln)
         Fn.layernorm_bwd(ws.dln_cur, ws.h[L], ws.meanf, ws.rstdf, c["lnf_g"], g["lnf_g"], g["lnf_b"], dres=None, out=ws.dh_a)
         if eng.has_grad_hooks:
             eng.side_join()
