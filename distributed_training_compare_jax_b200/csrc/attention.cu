@@ -6,12 +6,12 @@
 // Layout: q, k, v are column slices of one [M = B*T, ld] bf16 buffer (head h occupies columns
 // [h*HD, (h+1)*HD) of each slice); o / do / dq / dk / dv use the same convention.
 //
-// Forward  (CTA = one (batch, head, 128-query block), 128 threads, thread r owns query row r):
-//   S  = Q K_j^T      tcgen05.mma 128x128xHD   -> TMEM cols [0,128)
+// Forward  (flash_attn_fwd_pipe_kernel; CTA = one (batch, head, 128-query block), thread r of the softmax warps owns query row r):
+//   S  = Q K_j^T      tcgen05.mma 128x64xHD    -> TMEM, double-buffered; issued one key block ahead by the issue warp
 //   online softmax: tcgen05.ld of the thread's row, exp2, P (bf16) -> 128B-swizzled smem (K-major A operand)
-//   PV = P V_j        tcgen05.mma 128xHDx128 (V consumed MN-major straight from its TMA tile) -> TMEM cols [128,128+HD)
-//   O  = O*alpha + PV in registers; K/V tiles double-buffered by TMA.
-// Backward (CTA = one (batch, head, 128-key block j); loops over query blocks i >= j; thread r owns key row r):
+//   PV = P V_j        tcgen05.mma 128xHDx64 (V consumed MN-major straight from its TMA tile) -> TMEM, folded one block late
+// Backward (head_dim 32: flash_attn_bwd_persist_kernel, see there; head_dim 64: flash_attn_bwd_kernel —
+//   CTA = one (batch, head, 128-key block j); loops over query blocks i >= j; thread r owns key row r):
 //   St  = K_j Q_i^T ; dPt = V_j dO_i^T                         (TMEM cols [0,128), [128,256))
 //   Pt  = exp2(St*c - lse2_i) ; dSt = Pt o (dPt - delta_i)     -> two swizzled smem tiles
 //   dV += Pt dO_i ; dK += dSt Q_i     (accumulate in TMEM across i)
@@ -40,347 +40,6 @@ struct AttnCfg {
 DTC_DEVICE uint32_t p_tile_offset(int row, int col8 /* 16-byte chunk index 0..15 */) {
   const uint32_t blk = col8 >> 3;
   return blk * (ATT_BLK * 128) + swizzle_offset<3>(row * 128 + (col8 & 7) * 16);
-}
-
-template <int HD>
-__global__ void __launch_bounds__(128)
-flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
-                      const __grid_constant__ CUtensorMap tm_v, bf16* __restrict__ out, long long ldo,
-                      float* __restrict__ lse2_out, int T, int H, float scale_log2) {
-  using C = AttnCfg<HD>;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint8_t* sQ = smem;
-  uint8_t* sK = sQ + C::TILE_BYTES;      // 2 stages
-  uint8_t* sV = sK + 2 * C::TILE_BYTES;  // 2 stages
-  uint8_t* sP = sV + 2 * C::TILE_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + C::P_BYTES);
-  uint64_t* bar_q = bars;
-  uint64_t* bar_kv = bars + 1;  // [2]
-  uint64_t* bar_s = bars + 3;
-  uint64_t* bar_o = bars + 4;
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 5);
-
-  const int tid = threadIdx.x, warp = tid >> 5;
-  // heaviest tiles first: query block i attends i+1 key blocks, so launch the last query blocks first
-  const int qblk = gridDim.x - 1 - blockIdx.x, h = blockIdx.y, b = blockIdx.z;
-  const int row0 = b * T + qblk * ATT_BLK;  // first global row of the query tile
-  const int nkv = qblk + 1;                 // causal: key blocks 0..qblk
-
-  if (tid == 0) {
-    tma_prefetch_desc(&tm_q);
-    tma_prefetch_desc(&tm_k);
-    tma_prefetch_desc(&tm_v);
-    mbar_init(bar_q, 1);
-    mbar_init(&bar_kv[0], 1);
-    mbar_init(&bar_kv[1], 1);
-    mbar_init(bar_s, 1);
-    mbar_init(bar_o, 1);
-    fence_barrier_init();
-  }
-  if (warp == 0) {
-    tmem_alloc(tmem_ptr_smem, 256);
-    tmem_relinquish();
-  }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = *tmem_ptr_smem;
-  pdl_launch_dependents();  // PDL: only after this CTA owns its TMEM (a dependent may not allocate first)
-  pdl_wait();               // inputs come from the previous kernel: no global access before it has completed
-  const uint32_t tmem_s = tmem_base, tmem_pv = tmem_base + 128;
-  const uint32_t lane_sel = (uint32_t)(warp * 32) << 16;
-
-  if (tid == 0) {
-    mbar_expect_tx(bar_q, C::TILE_BYTES);
-    tma_load_2d(sQ, &tm_q, bar_q, h * HD, row0);
-    mbar_expect_tx(&bar_kv[0], 2 * C::TILE_BYTES);
-    tma_load_2d(sK, &tm_k, &bar_kv[0], h * HD, b * T);
-    tma_load_2d(sV, &tm_v, &bar_kv[0], h * HD, b * T);
-  }
-
-  constexpr uint32_t idesc_s = make_idesc_bf16(128, 128, 0, 0);
-  constexpr uint32_t idesc_pv = make_idesc_bf16(128, HD, 0, 1);
-
-  float o_acc[HD];
-#pragma unroll
-  for (int j = 0; j < HD; ++j) o_acc[j] = 0.f;
-  float m_run = -INFINITY, l_run = 0.f;
-
-  for (int j = 0; j < nkv; ++j) {
-    const int st = j & 1;
-    if (j == 0) mbar_wait(bar_q, 0);
-    mbar_wait(&bar_kv[st], (j >> 1) & 1);
-    tc_fence_after();
-    if (tid == 0) {
-      const uint32_t aq = smem_u32(sQ), ak = smem_u32(sK + st * C::TILE_BYTES);
-#pragma unroll
-      for (int k = 0; k < HD / 16; ++k)
-        umma_bf16(tmem_s, make_smem_desc(aq + k * 32, 16, C::SBO, C::SWZ), make_smem_desc(ak + k * 32, 16, C::SBO, C::SWZ),
-                  idesc_s, k > 0);
-      umma_commit(bar_s);
-      if (j + 1 < nkv) {  // prefetch next K/V tile (its buffer was released when PV of block j-1 completed)
-        const int ns = st ^ 1;
-        mbar_expect_tx(&bar_kv[ns], 2 * C::TILE_BYTES);
-        tma_load_2d(sK + ns * C::TILE_BYTES, &tm_k, &bar_kv[ns], h * HD, b * T + (j + 1) * ATT_BLK);
-        tma_load_2d(sV + ns * C::TILE_BYTES, &tm_v, &bar_kv[ns], h * HD, b * T + (j + 1) * ATT_BLK);
-      }
-    }
-    mbar_wait(bar_s, j & 1);
-    tc_fence_after();
-
-    // ---- online softmax on this thread's row (two sweeps over TMEM: max, then exp + P write) ----
-    const bool diag = (j == qblk);
-    float mx = -INFINITY;
-#pragma unroll 1
-    for (int c = 0; c < 4; ++c) {
-      uint32_t r[32];
-      tmem_ld_32x32b_x32(tmem_s + lane_sel + c * 32, r);
-      tmem_ld_wait();
-#pragma unroll
-      for (int i = 0; i < 32; ++i) {
-        const float s = __uint_as_float(r[i]);
-        if (!diag || (c * 32 + i) <= tid) mx = fmaxf(mx, s);
-      }
-    }
-    const float m_new = fmaxf(m_run, mx * scale_log2);  // row always has >= 1 unmasked column
-    const float alpha = exp2f(m_run - m_new);
-    float l_blk = 0.f;
-#pragma unroll 1
-    for (int c = 0; c < 4; ++c) {
-      uint32_t r[32];
-      tmem_ld_32x32b_x32(tmem_s + lane_sel + c * 32, r);
-      tmem_ld_wait();
-#pragma unroll
-      for (int g = 0; g < 4; ++g) {
-        float p[8];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int col = c * 32 + g * 8 + i;
-          const float s = __uint_as_float(r[g * 8 + i]);
-          p[i] = (!diag || col <= tid) ? exp2f(s * scale_log2 - m_new) : 0.f;
-          l_blk += p[i];
-        }
-        *reinterpret_cast<uint4*>(sP + p_tile_offset(tid, c * 4 + g)) =
-            make_uint4(pack_bf16x2(p[0], p[1]), pack_bf16x2(p[2], p[3]), pack_bf16x2(p[4], p[5]), pack_bf16x2(p[6], p[7]));
-      }
-    }
-    l_run = l_run * alpha + l_blk;
-    m_run = m_new;
-    fence_proxy_async_smem();
-    tc_fence_before();
-    __syncthreads();
-    if (tid == 0) {
-      tc_fence_after();
-      const uint32_t ap = smem_u32(sP), av = smem_u32(sV + st * C::TILE_BYTES);
-#pragma unroll
-      for (int k = 0; k < ATT_BLK / 16; ++k)
-        umma_bf16(tmem_pv, make_smem_desc(ap + (k >> 2) * (ATT_BLK * 128) + (k & 3) * 32, 16, 1024, SWZ_128B),
-                  make_smem_desc(av + k * 16 * C::ROW_BYTES, 16, C::SBO, C::SWZ), idesc_pv, k > 0);
-      umma_commit(bar_o);
-    }
-    mbar_wait(bar_o, j & 1);
-    tc_fence_after();
-#pragma unroll
-    for (int c = 0; c < HD / 32; ++c) {
-      uint32_t r[32];
-      tmem_ld_32x32b_x32(tmem_pv + lane_sel + c * 32, r);
-      tmem_ld_wait();
-#pragma unroll
-      for (int i = 0; i < 32; ++i) o_acc[c * 32 + i] = o_acc[c * 32 + i] * alpha + __uint_as_float(r[i]);
-    }
-    tc_fence_before();
-    __syncthreads();  // all TMEM reads / sP writes of this block retired before the next block's MMAs
-  }
-
-  const float inv_l = 1.f / l_run;
-  bf16* orow = out + (long long)(row0 + tid) * ldo + h * HD;
-#pragma unroll
-  for (int c = 0; c < HD / 8; ++c) {
-    *reinterpret_cast<uint4*>(orow + c * 8) =
-        make_uint4(pack_bf16x2(o_acc[c * 8] * inv_l, o_acc[c * 8 + 1] * inv_l),
-                   pack_bf16x2(o_acc[c * 8 + 2] * inv_l, o_acc[c * 8 + 3] * inv_l),
-                   pack_bf16x2(o_acc[c * 8 + 4] * inv_l, o_acc[c * 8 + 5] * inv_l),
-                   pack_bf16x2(o_acc[c * 8 + 6] * inv_l, o_acc[c * 8 + 7] * inv_l));
-  }
-  lse2_out[((long long)b * H + h) * T + qblk * ATT_BLK + tid] = m_run + log2f(l_run);
-
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 0) {
-    tc_fence_after();
-    tmem_dealloc(tmem_base, 256);
-  }
-}
-
-// Forward, 64-key blocks (default): same algorithm as flash_attn_fwd_kernel, but a key/value block is 64 rows, so the
-// S accumulator needs 64 TMEM columns and the P tile 16 KB: with 128 allocated TMEM columns and ~42 KB of shared
-// memory FOUR CTAs fit on an SM (the 128-key version: two), which doubles the warps available to hide the
-// MMA -> tcgen05.ld -> exp2 -> st.shared -> MMA round trips this latency-bound kernel consists of.
-template <int HD>
-__global__ void __launch_bounds__(128, 4)
-flash_attn_fwd_kv64_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
-                           const __grid_constant__ CUtensorMap tm_v, bf16* __restrict__ out, long long ldo,
-                           float* __restrict__ lse2_out, int T, int H, float scale_log2) {
-  using C = AttnCfg<HD>;
-  constexpr int KVB = 64;
-  constexpr int KV_BYTES = KVB * C::ROW_BYTES;
-  constexpr int P64_BYTES = ATT_BLK * 128;  // [128 x 64] bf16, one K-major 128B-swizzled block
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint8_t* sQ = smem;
-  uint8_t* sP = sQ + C::TILE_BYTES;
-  uint8_t* sK = sP + P64_BYTES;     // 2 stages
-  uint8_t* sV = sK + 2 * KV_BYTES;  // 2 stages
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sV + 2 * KV_BYTES);
-  uint64_t* bar_q = bars;
-  uint64_t* bar_kv = bars + 1;  // [2]
-  uint64_t* bar_s = bars + 3;
-  uint64_t* bar_o = bars + 4;
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 5);
-
-  const int tid = threadIdx.x, warp = tid >> 5;
-  const int qblk = gridDim.x - 1 - blockIdx.x, h = blockIdx.y, b = blockIdx.z;  // heaviest query blocks first
-  const int row0 = b * T + qblk * ATT_BLK;
-  const int nkv = 2 * (qblk + 1);  // causal: 64-key blocks 0 .. 2*qblk+1
-  const int qrow = qblk * ATT_BLK + tid;  // position of this thread's query inside the sequence
-
-  if (tid == 0) {
-    tma_prefetch_desc(&tm_q);
-    tma_prefetch_desc(&tm_k);
-    tma_prefetch_desc(&tm_v);
-    mbar_init(bar_q, 1);
-    mbar_init(&bar_kv[0], 1);
-    mbar_init(&bar_kv[1], 1);
-    mbar_init(bar_s, 1);
-    mbar_init(bar_o, 1);
-    fence_barrier_init();
-  }
-  if (warp == 0) {
-    tmem_alloc(tmem_ptr_smem, 128);
-    tmem_relinquish();
-  }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = *tmem_ptr_smem;
-  pdl_launch_dependents();
-  pdl_wait();
-  const uint32_t tmem_s = tmem_base, tmem_pv = tmem_base + 64;
-  const uint32_t lane_sel = (uint32_t)(warp * 32) << 16;
-
-  if (tid == 0) {
-    mbar_expect_tx(bar_q, C::TILE_BYTES);
-    tma_load_2d(sQ, &tm_q, bar_q, h * HD, row0);
-    mbar_expect_tx(&bar_kv[0], 2 * KV_BYTES);
-    tma_load_2d(sK, &tm_k, &bar_kv[0], h * HD, b * T);
-    tma_load_2d(sV, &tm_v, &bar_kv[0], h * HD, b * T);
-  }
-
-  constexpr uint32_t idesc_s = make_idesc_bf16(128, KVB, 0, 0);
-  constexpr uint32_t idesc_pv = make_idesc_bf16(128, HD, 0, 1);
-
-  float o_acc[HD];
-#pragma unroll
-  for (int j = 0; j < HD; ++j) o_acc[j] = 0.f;
-  float m_run = -INFINITY, l_run = 0.f;
-
-  for (int j = 0; j < nkv; ++j) {
-    const int st = j & 1;
-    if (j == 0) mbar_wait(bar_q, 0);
-    mbar_wait(&bar_kv[st], (j >> 1) & 1);
-    tc_fence_after();
-    if (tid == 0) {
-      const uint32_t aq = smem_u32(sQ), ak = smem_u32(sK + st * KV_BYTES);
-#pragma unroll
-      for (int k = 0; k < HD / 16; ++k)
-        umma_bf16(tmem_s, make_smem_desc(aq + k * 32, 16, C::SBO, C::SWZ), make_smem_desc(ak + k * 32, 16, C::SBO, C::SWZ),
-                  idesc_s, k > 0);
-      umma_commit(bar_s);
-      if (j + 1 < nkv) {
-        const int ns = st ^ 1;
-        mbar_expect_tx(&bar_kv[ns], 2 * KV_BYTES);
-        tma_load_2d(sK + ns * KV_BYTES, &tm_k, &bar_kv[ns], h * HD, b * T + (j + 1) * KVB);
-        tma_load_2d(sV + ns * KV_BYTES, &tm_v, &bar_kv[ns], h * HD, b * T + (j + 1) * KVB);
-      }
-    }
-    mbar_wait(bar_s, j & 1);
-    tc_fence_after();
-
-    // key column c of this block is visible to this query iff j*64 + c <= qrow  <=>  c <= lim
-    const int lim = qrow - j * KVB;
-    uint32_t r0[32], r1[32];
-    tmem_ld_32x32b_x32(tmem_s + lane_sel, r0);
-    tmem_ld_32x32b_x32(tmem_s + lane_sel + 32, r1);
-    tmem_ld_wait();
-    float mx = -INFINITY;
-#pragma unroll
-    for (int i = 0; i < 32; ++i) {
-      if (i <= lim) mx = fmaxf(mx, __uint_as_float(r0[i]));
-      if (i + 32 <= lim) mx = fmaxf(mx, __uint_as_float(r1[i]));
-    }
-    const float m_new = fmaxf(m_run, mx * scale_log2);  // block 0 always has a visible key, so m_new is finite
-    const float alpha = exp2f(m_run - m_new);
-    float l_blk = 0.f;
-#pragma unroll
-    for (int g = 0; g < 8; ++g) {
-      float p[8];
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const int col = g * 8 + i;
-        const float sv = __uint_as_float(g < 4 ? r0[col] : r1[col - 32]);
-        p[i] = (col <= lim) ? exp2f(sv * scale_log2 - m_new) : 0.f;
-        l_blk += p[i];
-      }
-      *reinterpret_cast<uint4*>(sP + swizzle_offset<3>(tid * 128 + g * 16)) =
-          make_uint4(pack_bf16x2(p[0], p[1]), pack_bf16x2(p[2], p[3]), pack_bf16x2(p[4], p[5]), pack_bf16x2(p[6], p[7]));
-    }
-    l_run = l_run * alpha + l_blk;
-    m_run = m_new;
-    fence_proxy_async_smem();
-    tc_fence_before();
-    __syncthreads();
-    if (tid == 0) {
-      tc_fence_after();
-      const uint32_t ap = smem_u32(sP), av = smem_u32(sV + st * KV_BYTES);
-#pragma unroll
-      for (int k = 0; k < KVB / 16; ++k)
-        umma_bf16(tmem_pv, make_smem_desc(ap + k * 32, 16, 1024, SWZ_128B),
-                  make_smem_desc(av + k * 16 * C::ROW_BYTES, 16, C::SBO, C::SWZ), idesc_pv, k > 0);
-      umma_commit(bar_o);
-    }
-    mbar_wait(bar_o, j & 1);
-    tc_fence_after();
-#pragma unroll
-    for (int c = 0; c < HD / 32; ++c) {
-      uint32_t r[32];
-      tmem_ld_32x32b_x32(tmem_pv + lane_sel + c * 32, r);
-      tmem_ld_wait();
-#pragma unroll
-      for (int i = 0; i < 32; ++i) o_acc[c * 32 + i] = o_acc[c * 32 + i] * alpha + __uint_as_float(r[i]);
-    }
-    tc_fence_before();
-    __syncthreads();
-  }
-
-  const float inv_l = 1.f / l_run;
-  bf16* orow = out + (long long)(row0 + tid) * ldo + h * HD;
-#pragma unroll
-  for (int c = 0; c < HD / 8; ++c) {
-    *reinterpret_cast<uint4*>(orow + c * 8) =
-        make_uint4(pack_bf16x2(o_acc[c * 8] * inv_l, o_acc[c * 8 + 1] * inv_l),
-                   pack_bf16x2(o_acc[c * 8 + 2] * inv_l, o_acc[c * 8 + 3] * inv_l),
-                   pack_bf16x2(o_acc[c * 8 + 4] * inv_l, o_acc[c * 8 + 5] * inv_l),
-                   pack_bf16x2(o_acc[c * 8 + 6] * inv_l, o_acc[c * 8 + 7] * inv_l));
-  }
-  lse2_out[((long long)b * H + h) * T + qblk * ATT_BLK + tid] = m_run + log2f(l_run);
-
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 0) {
-    tc_fence_after();
-    tmem_dealloc(tmem_base, 128);
-  }
 }
 
 // Forward, software-pipelined (default).  Same math as the kernels above; what changes is who waits for whom:
@@ -854,471 +513,11 @@ flash_attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
   }
 }
 
-// Backward, register-accumulator variant (head_dim 32, default): dK / dV accumulate in registers (one key row per
-// thread, like the forward's O) instead of tensor memory, and the per-iteration dV / dK / dQ products land in the
-// St / dPt columns once those have been consumed.  The CTA then needs 256 TMEM columns and ~107 KB of shared
-// memory (dO single-buffered), so TWO CTAs fit on an SM (flash_attn_bwd_kernel: 512 columns -> one CTA, 4 warps per SM).
-template <int HD>
-__global__ void __launch_bounds__(128, 2)
-flash_attn_bwd_regacc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
-                             const __grid_constant__ CUtensorMap tm_v, const __grid_constant__ CUtensorMap tm_do,
-                             const float* __restrict__ lse2, const float* __restrict__ delta, float* __restrict__ dq_accum,
-                             long long lddq, bf16* __restrict__ dk, bf16* __restrict__ dv, long long lddkv, int T, int H,
-                             float scale, float scale_log2) {
-  using C = AttnCfg<HD>;
-  static_assert(HD == 32, "register accumulators are sized for head_dim 32");
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint8_t* sK = smem;
-  uint8_t* sV = sK + C::TILE_BYTES;
-  uint8_t* sQ = sV + C::TILE_BYTES;       // 2 stages
-  uint8_t* sDO = sQ + 2 * C::TILE_BYTES;  // 1 stage
-  uint8_t* sPt = sDO + C::TILE_BYTES;
-  uint8_t* sDSt = sPt + C::P_BYTES;
-  float* s_lse = reinterpret_cast<float*>(sDSt + C::P_BYTES);  // [128]
-  float* s_delta = s_lse + ATT_BLK;                            // [128]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_delta + ATT_BLK);
-  uint64_t* bar_kv = bars;
-  uint64_t* bar_q = bars + 1;  // [2]
-  uint64_t* bar_do = bars + 3;
-  uint64_t* bar_s = bars + 4;
-  uint64_t* bar_d = bars + 5;
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 6);
-
-  const int tid = threadIdx.x, warp = tid >> 5;
-  const int jblk = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
-  const int nblk = T / ATT_BLK;
-  const int kv_row0 = b * T + jblk * ATT_BLK;
-  const long long stat_base = ((long long)b * H + h) * T;
-
-  if (tid == 0) {
-    tma_prefetch_desc(&tm_q);
-    tma_prefetch_desc(&tm_k);
-    tma_prefetch_desc(&tm_v);
-    tma_prefetch_desc(&tm_do);
-    mbar_init(bar_kv, 1);
-    mbar_init(&bar_q[0], 1);
-    mbar_init(&bar_q[1], 1);
-    mbar_init(bar_do, 1);
-    mbar_init(bar_s, 1);
-    mbar_init(bar_d, 1);
-    fence_barrier_init();
-  }
-  if (warp == 0) {
-    tmem_alloc(tmem_ptr_smem, 256);
-    tmem_relinquish();
-  }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = *tmem_ptr_smem;
-  pdl_launch_dependents();
-  pdl_wait();
-  const uint32_t tm_st = tmem_base, tm_dpt = tmem_base + 128;
-  // per-iteration products, written over the (already consumed) St columns
-  const uint32_t tm_dv = tmem_base, tm_dk = tmem_base + HD, tm_dq = tmem_base + 2 * HD;
-  const uint32_t lane_sel = (uint32_t)(warp * 32) << 16;
-
-  if (tid == 0) {
-    mbar_expect_tx(bar_kv, 2 * C::TILE_BYTES);
-    tma_load_2d(sK, &tm_k, bar_kv, h * HD, kv_row0);
-    tma_load_2d(sV, &tm_v, bar_kv, h * HD, kv_row0);
-    mbar_expect_tx(&bar_q[0], C::TILE_BYTES);
-    tma_load_2d(sQ, &tm_q, &bar_q[0], h * HD, b * T + jblk * ATT_BLK);
-    mbar_expect_tx(bar_do, C::TILE_BYTES);
-    tma_load_2d(sDO, &tm_do, bar_do, h * HD, b * T + jblk * ATT_BLK);
-  }
-
-  constexpr uint32_t idesc_kk = make_idesc_bf16(128, 128, 0, 0);
-  constexpr uint32_t idesc_kn = make_idesc_bf16(128, HD, 0, 1);
-  constexpr uint32_t idesc_nn = make_idesc_bf16(128, HD, 1, 1);
-
-  float acc_dk[HD], acc_dv[HD];
-#pragma unroll
-  for (int e = 0; e < HD; ++e) {
-    acc_dk[e] = 0.f;
-    acc_dv[e] = 0.f;
-  }
-
-  int it = 0;
-  for (int i = jblk; i < nblk; ++i, ++it) {
-    const int st = it & 1;
-    s_lse[tid] = lse2[stat_base + i * ATT_BLK + tid];
-    s_delta[tid] = delta[stat_base + i * ATT_BLK + tid];
-    if (it == 0) mbar_wait(bar_kv, 0);
-    mbar_wait(&bar_q[st], (it >> 1) & 1);
-    mbar_wait(bar_do, it & 1);
-    tc_fence_after();
-    __syncthreads();
-    if (tid == 0) {
-      const uint32_t ak = smem_u32(sK), av = smem_u32(sV), aq = smem_u32(sQ + st * C::TILE_BYTES), ado = smem_u32(sDO);
-#pragma unroll
-      for (int k = 0; k < HD / 16; ++k)
-        umma_bf16(tm_st, make_smem_desc(ak + k * 32, 16, C::SBO, C::SWZ), make_smem_desc(aq + k * 32, 16, C::SBO, C::SWZ),
-                  idesc_kk, k > 0);
-#pragma unroll
-      for (int k = 0; k < HD / 16; ++k)
-        umma_bf16(tm_dpt, make_smem_desc(av + k * 32, 16, C::SBO, C::SWZ), make_smem_desc(ado + k * 32, 16, C::SBO, C::SWZ),
-                  idesc_kk, k > 0);
-      umma_commit(bar_s);
-      if (i + 1 < nblk) {  // next Q tile (its buffer was last read by the MMAs of the previous iteration)
-        const int ns = st ^ 1;
-        mbar_expect_tx(&bar_q[ns], C::TILE_BYTES);
-        tma_load_2d(sQ + ns * C::TILE_BYTES, &tm_q, &bar_q[ns], h * HD, b * T + (i + 1) * ATT_BLK);
-      }
-    }
-    mbar_wait(bar_s, it & 1);
-    tc_fence_after();
-
-    const bool diag = (i == jblk);
-#pragma unroll 1
-    for (int c = 0; c < 4; ++c) {
-      uint32_t rs[32], rp[32];
-      tmem_ld_32x32b_x32(tm_st + lane_sel + c * 32, rs);
-      tmem_ld_32x32b_x32(tm_dpt + lane_sel + c * 32, rp);
-      tmem_ld_wait();
-#pragma unroll
-      for (int g = 0; g < 4; ++g) {
-        float p[8], ds[8];
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          const int q = c * 32 + g * 8 + e;
-          const float sv = __uint_as_float(rs[g * 8 + e]);
-          const float pv = (!diag || q >= tid) ? exp2f(sv * scale_log2 - s_lse[q]) : 0.f;
-          p[e] = pv;
-          ds[e] = pv * (__uint_as_float(rp[g * 8 + e]) - s_delta[q]);
-        }
-        const uint32_t off = p_tile_offset(tid, c * 4 + g);
-        *reinterpret_cast<uint4*>(sPt + off) =
-            make_uint4(pack_bf16x2(p[0], p[1]), pack_bf16x2(p[2], p[3]), pack_bf16x2(p[4], p[5]), pack_bf16x2(p[6], p[7]));
-        *reinterpret_cast<uint4*>(sDSt + off) = make_uint4(pack_bf16x2(ds[0], ds[1]), pack_bf16x2(ds[2], ds[3]),
-                                                           pack_bf16x2(ds[4], ds[5]), pack_bf16x2(ds[6], ds[7]));
-      }
-    }
-    fence_proxy_async_smem();
-    tc_fence_before();
-    __syncthreads();
-    if (tid == 0) {
-      tc_fence_after();
-      const uint32_t apt = smem_u32(sPt), adst = smem_u32(sDSt), aq = smem_u32(sQ + st * C::TILE_BYTES),
-                     ado = smem_u32(sDO), ak = smem_u32(sK);
-#pragma unroll
-      for (int k = 0; k < ATT_BLK / 16; ++k) {
-        const uint32_t a_off = (k >> 2) * (ATT_BLK * 128) + (k & 3) * 32;
-        umma_bf16(tm_dv, make_smem_desc(apt + a_off, 16, 1024, SWZ_128B),
-                  make_smem_desc(ado + k * 16 * C::ROW_BYTES, 16, C::SBO, C::SWZ), idesc_kn, k > 0);
-      }
-#pragma unroll
-      for (int k = 0; k < ATT_BLK / 16; ++k) {
-        const uint32_t a_off = (k >> 2) * (ATT_BLK * 128) + (k & 3) * 32;
-        umma_bf16(tm_dk, make_smem_desc(adst + a_off, 16, 1024, SWZ_128B),
-                  make_smem_desc(aq + k * 16 * C::ROW_BYTES, 16, C::SBO, C::SWZ), idesc_kn, k > 0);
-      }
-#pragma unroll
-      for (int k = 0; k < ATT_BLK / 16; ++k)
-        umma_bf16(tm_dq, make_smem_desc(adst + k * 2048, ATT_BLK * 128, 1024, SWZ_128B),
-                  make_smem_desc(ak + k * 16 * C::ROW_BYTES, 16, C::SBO, C::SWZ), idesc_nn, k > 0);
-      umma_commit(bar_d);
-    }
-    mbar_wait(bar_d, it & 1);
-    tc_fence_after();
-    if (tid == 0 && i + 1 < nblk) {  // the dO tile is free again: fetch the next one behind this iteration's tail
-      mbar_expect_tx(bar_do, C::TILE_BYTES);
-      tma_load_2d(sDO, &tm_do, bar_do, h * HD, b * T + (i + 1) * ATT_BLK);
-    }
-    {
-      uint32_t rq[32], rv[32], rk[32];
-      tmem_ld_32x32b_x32(tm_dq + lane_sel, rq);
-      tmem_ld_32x32b_x32(tm_dv + lane_sel, rv);
-      tmem_ld_32x32b_x32(tm_dk + lane_sel, rk);
-      tmem_ld_wait();
-      float* dq_row = dq_accum + (long long)(b * T + i * ATT_BLK + tid) * lddq + h * HD;
-#pragma unroll
-      for (int e = 0; e < 32; e += 4)
-        asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dq_row + e), "f"(__uint_as_float(rq[e]) * scale),
-                     "f"(__uint_as_float(rq[e + 1]) * scale), "f"(__uint_as_float(rq[e + 2]) * scale),
-                     "f"(__uint_as_float(rq[e + 3]) * scale)
-                     : "memory");
-#pragma unroll
-      for (int e = 0; e < 32; ++e) {
-        acc_dv[e] += __uint_as_float(rv[e]);
-        acc_dk[e] += __uint_as_float(rk[e]);
-      }
-    }
-    tc_fence_before();
-    __syncthreads();
-  }
-
-  bf16* dk_row = dk + (long long)(kv_row0 + tid) * lddkv + h * HD;
-  bf16* dv_row = dv + (long long)(kv_row0 + tid) * lddkv + h * HD;
-#pragma unroll
-  for (int g = 0; g < HD / 8; ++g) {
-    const int e = g * 8;
-    *reinterpret_cast<uint4*>(dk_row + e) =
-        make_uint4(pack_bf16x2(acc_dk[e] * scale, acc_dk[e + 1] * scale), pack_bf16x2(acc_dk[e + 2] * scale, acc_dk[e + 3] * scale),
-                   pack_bf16x2(acc_dk[e + 4] * scale, acc_dk[e + 5] * scale), pack_bf16x2(acc_dk[e + 6] * scale, acc_dk[e + 7] * scale));
-    *reinterpret_cast<uint4*>(dv_row + e) = make_uint4(pack_bf16x2(acc_dv[e], acc_dv[e + 1]), pack_bf16x2(acc_dv[e + 2], acc_dv[e + 3]),
-                                                       pack_bf16x2(acc_dv[e + 4], acc_dv[e + 5]), pack_bf16x2(acc_dv[e + 6], acc_dv[e + 7]));
-  }
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 0) {
-    tc_fence_after();
-    tmem_dealloc(tmem_base, 256);
-  }
-}
-
 DTC_DEVICE void red_add_v4_f32_attn(float* addr, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
-// Backward, software-pipelined (head_dim 32, default).  CTA = one (batch, head, 128-key block j), looping over the query
-// blocks i >= j as before, but
-//   * scores are kept in the S = Q_i K_j^T orientation (thread r owns QUERY row r), so lse2 / delta are two per-thread
-//     scalars instead of two shared-memory loads per element;
-//   * 8 softmax warps: warps 0..3 take key columns [0,64), warps 4..7 take [64,128) of the same rows — twice the warps
-//     per scheduler for the exp2 / FMA work that bounds this kernel;
-//   * warp 8 is the issue warp (one elected lane): all TMA loads and tcgen05.mma.  S_{i+1} / dP_{i+1} are issued as soon as
-//     every softmax warp has pulled S_i / dP_i into registers, i.e. they run UNDER the element-wise work of block i;
-//   * P / dS tiles are double-buffered in shared memory, so the three product GEMMs of block i (dV += P^T dO_i,
-//     dK += dS^T Q_i, dQ_i = dS K_j) overlap the element-wise work of block i+1;
-//   * dK / dV accumulate in tensor memory across i (no per-iteration read-back); dQ_i is double-buffered in tensor
-//     memory and pushed to global (fp32 red.add) one block late, when its MMAs are certainly complete.
-// TMEM columns: S [0,128) dP [128,256) dV [256,288) dK [288,320) dQ0 [320,352) dQ1 [352,384) -> 512 allocated, 1 CTA / SM.
-template <int HD>
-__global__ void __launch_bounds__(288, 1)
-flash_attn_bwd_pipe_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
-                           const __grid_constant__ CUtensorMap tm_v, const __grid_constant__ CUtensorMap tm_do,
-                           const float* __restrict__ lse2, const float* __restrict__ delta, float* __restrict__ dq_accum,
-                           long long lddq, bf16* __restrict__ dk, bf16* __restrict__ dv, long long lddkv, int T, int H,
-                           float scale, float scale_log2) {
-  using C = AttnCfg<HD>;
-  static_assert(HD == 32, "the pipelined backward is laid out for head_dim 32");
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint8_t* sP = smem;                      // 2 buffers of [128 q x 128 k] bf16
-  uint8_t* sDS = sP + 2 * C::P_BYTES;      // 2 buffers
-  uint8_t* sK = sDS + 2 * C::P_BYTES;
-  uint8_t* sV = sK + C::TILE_BYTES;
-  uint8_t* sQ = sV + C::TILE_BYTES;        // 2 stages
-  uint8_t* sDO = sQ + 2 * C::TILE_BYTES;   // 2 stages
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sDO + 2 * C::TILE_BYTES);
-  uint64_t* bar_kv = bars;
-  uint64_t* bar_ld = bars + 1;  // [2] Q_i and dO_i landed
-  uint64_t* bar_s = bars + 3;   //     S_i / dP_i complete
-  uint64_t* bar_c = bars + 4;   //     S_i / dP_i pulled into registers by all 8 softmax warps
-  uint64_t* bar_p = bars + 5;   // [2] P_i / dS_i written (and dQ_{i-1} read out)
-  uint64_t* bar_d = bars + 7;   // [2] products of block i complete
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 9);
-
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int jblk = blockIdx.x, h = blockIdx.y, b = blockIdx.z;  // key block 0 has the most query blocks: heaviest first
-  const int nblk = T / ATT_BLK;
-  const int n_it = nblk - jblk;
-  const int kv_row0 = b * T + jblk * ATT_BLK;
-  const long long stat_base = ((long long)b * H + h) * T;
-
-  if (tid == 0) {
-    tma_prefetch_desc(&tm_q);
-    tma_prefetch_desc(&tm_k);
-    tma_prefetch_desc(&tm_v);
-    tma_prefetch_desc(&tm_do);
-    mbar_init(bar_kv, 1);
-    mbar_init(bar_s, 1);
-    mbar_init(bar_c, 8);
-    for (int s = 0; s < 2; ++s) {
-      mbar_init(&bar_ld[s], 1);
-      mbar_init(&bar_p[s], 8);
-      mbar_init(&bar_d[s], 1);
-    }
-    fence_barrier_init();
-  }
-  if (warp == 8) {
-    tmem_alloc(tmem_ptr_smem, 512);
-    tmem_relinquish();
-  }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = *tmem_ptr_smem;
-  pdl_launch_dependents();
-  pdl_wait();
-  const uint32_t tm_s = tmem_base, tm_dp = tmem_base + 128, tm_dv = tmem_base + 256, tm_dk = tmem_base + 256 + HD,
-                 tm_dq = tmem_base + 256 + 2 * HD;  // two buffers of HD columns
-
-  if (warp == 8) {
-    // ------------------------------ issue warp ------------------------------
-    if (elect_one()) {
-      constexpr uint32_t idesc_kk = make_idesc_bf16(128, 128, 0, 0);
-      constexpr uint32_t idesc_kn = make_idesc_bf16(128, HD, 0, 1);
-      constexpr uint32_t idesc_nn = make_idesc_bf16(128, HD, 1, 1);
-      auto load_qdo = [&](int it) {
-        const int st = it & 1;
-        mbar_expect_tx(&bar_ld[st], 2 * C::TILE_BYTES);
-        tma_load_2d(sQ + st * C::TILE_BYTES, &tm_q, &bar_ld[st], h * HD, b * T + (jblk + it) * ATT_BLK);
-        tma_load_2d(sDO + st * C::TILE_BYTES, &tm_do, &bar_ld[st], h * HD, b * T + (jblk + it) * ATT_BLK);
-      };
-      auto issue_scores = [&](int it) {  // S = Q_i K_j^T, dP = dO_i V_j^T
-        const int st = it & 1;
-        mbar_wait(&bar_ld[st], (it >> 1) & 1);
-        tc_fence_after();
-        const uint32_t ak = smem_u32(sK), av = smem_u32(sV), aq = smem_u32(sQ + st * C::TILE_BYTES),
-                       ado = smem_u32(sDO + st * C::TILE_BYTES);
-#pragma unroll
-        for (int k = 0; k < HD / 16; ++k)
-          umma_bf16(tm_s, make_smem_desc(aq + k * 32, 16, C::SBO, C::SWZ), make_smem_desc(ak + k * 32, 16, C::SBO, C::SWZ),
-                    idesc_kk, k > 0);
-#pragma unroll
-        for (int k = 0; k < HD / 16; ++k)
-          umma_bf16(tm_dp, make_smem_desc(ado + k * 32, 16, C::SBO, C::SWZ), make_smem_desc(av + k * 32, 16, C::SBO, C::SWZ),
-                    idesc_kk, k > 0);
-        umma_commit(bar_s);
-      };
-      mbar_expect_tx(bar_kv, 2 * C::TILE_BYTES);
-      tma_load_2d(sK, &tm_k, bar_kv, h * HD, kv_row0);
-      tma_load_2d(sV, &tm_v, bar_kv, h * HD, kv_row0);
-      load_qdo(0);
-      if (n_it > 1) load_qdo(1);
-      mbar_wait(bar_kv, 0);
-      issue_scores(0);
-      for (int it = 0; it < n_it; ++it) {
-        const int st = it & 1;
-        const uint32_t ph = (it >> 1) & 1;
-        // S_it / dP_it are in registers everywhere: the tensor cores may start on block it+1 under the exp2 work
-        mbar_wait(bar_c, it & 1);
-        if (it + 1 < n_it) issue_scores(it + 1);
-        // P_it / dS_it are in shared memory (and dQ buffer st was read out two blocks ago)
-        mbar_wait(&bar_p[st], ph);
-        tc_fence_after();
-        const uint32_t apt = smem_u32(sP + st * C::P_BYTES), adst = smem_u32(sDS + st * C::P_BYTES),
-                       aq = smem_u32(sQ + st * C::TILE_BYTES), ado = smem_u32(sDO + st * C::TILE_BYTES), ak = smem_u32(sK);
-        // dV += P^T dO_i ; dK += dS^T Q_i : A = the [q x k] tile read MN-major (M = keys contiguous, 16 query rows per step)
-#pragma unroll
-        for (int k = 0; k < ATT_BLK / 16; ++k)
-          umma_bf16(tm_dv, make_smem_desc(apt + k * 2048, ATT_BLK * 128, 1024, SWZ_128B),
-                    make_smem_desc(ado + k * 16 * C::ROW_BYTES, 16, C::SBO, C::SWZ), idesc_nn, (it > 0 || k > 0) ? 1u : 0u);
-#pragma unroll
-        for (int k = 0; k < ATT_BLK / 16; ++k)
-          umma_bf16(tm_dk, make_smem_desc(adst + k * 2048, ATT_BLK * 128, 1024, SWZ_128B),
-                    make_smem_desc(aq + k * 16 * C::ROW_BYTES, 16, C::SBO, C::SWZ), idesc_nn, (it > 0 || k > 0) ? 1u : 0u);
-        // dQ_i = dS K_j : A = the same tile K-major (two 64-key blocks), B = K_j MN-major
-#pragma unroll
-        for (int k = 0; k < ATT_BLK / 16; ++k) {
-          const uint32_t a_off = (k >> 2) * (ATT_BLK * 128) + (k & 3) * 32;
-          umma_bf16(tm_dq + st * HD, make_smem_desc(adst + a_off, 16, 1024, SWZ_128B),
-                    make_smem_desc(ak + k * 16 * C::ROW_BYTES, 16, C::SBO, C::SWZ), idesc_kn, k > 0);
-        }
-        umma_commit(&bar_d[st]);
-        // Q_it / dO_it were operands of these products: their stage is free once they complete
-        if (it + 2 < n_it) {
-          mbar_wait(&bar_d[st], ph);
-          load_qdo(it + 2);
-        }
-      }
-    }
-  } else {
-    // ------------------------------ softmax warps ------------------------------
-    const int row = (warp & 3) * 32 + lane;  // query row inside the block (TMEM lane)
-    const int gq = warp >> 2;                // key-column half handled by this warp
-    const uint32_t lane_sel = (uint32_t)((warp & 3) * 32) << 16;
-    for (int it = 0; it < n_it; ++it) {
-      const int st = it & 1;
-      const int i = jblk + it;
-      const float lse_r = lse2[stat_base + i * ATT_BLK + row];
-      const float delta_r = delta[stat_base + i * ATT_BLK + row];
-      mbar_wait(bar_s, it & 1);
-      tc_fence_after();
-      uint32_t rs[64], rp[64];
-      tmem_ld_32x32b_x32(tm_s + lane_sel + gq * 64, rs);
-      tmem_ld_32x32b_x32(tm_s + lane_sel + gq * 64 + 32, rs + 32);
-      tmem_ld_32x32b_x32(tm_dp + lane_sel + gq * 64, rp);
-      tmem_ld_32x32b_x32(tm_dp + lane_sel + gq * 64 + 32, rp + 32);
-      tmem_ld_wait();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar_c);
-      if (it == 0) {  // diagonal block (i == j): key column c is visible to query row r iff c <= r
-        const int lim = row - gq * 64;
-#pragma unroll
-        for (int e = 0; e < 64; ++e)
-          if (e > lim) rs[e] = 0xff800000u;  // -inf -> P = 0
-      }
-      uint8_t* pbuf = sP + st * C::P_BYTES;
-      uint8_t* dsbuf = sDS + st * C::P_BYTES;
-#pragma unroll
-      for (int g = 0; g < 8; ++g) {
-        float p[8], ds[8];
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          p[e] = ex2_ftz(fmaf(__uint_as_float(rs[g * 8 + e]), scale_log2, -lse_r));
-          ds[e] = p[e] * (__uint_as_float(rp[g * 8 + e]) - delta_r);
-        }
-        const uint32_t off = p_tile_offset(row, gq * 8 + g);
-        *reinterpret_cast<uint4*>(pbuf + off) =
-            make_uint4(pack_bf16x2(p[0], p[1]), pack_bf16x2(p[2], p[3]), pack_bf16x2(p[4], p[5]), pack_bf16x2(p[6], p[7]));
-        *reinterpret_cast<uint4*>(dsbuf + off) = make_uint4(pack_bf16x2(ds[0], ds[1]), pack_bf16x2(ds[2], ds[3]),
-                                                            pack_bf16x2(ds[4], ds[5]), pack_bf16x2(ds[6], ds[7]));
-      }
-      // dQ of the previous block: its MMAs were issued a whole element-wise pass ago
-      if (it >= 1) {
-        mbar_wait(&bar_d[st ^ 1], ((it - 1) >> 1) & 1);
-        tc_fence_after();
-        uint32_t rq[16];
-        tmem_ld_32x32b_x16(tm_dq + (st ^ 1) * HD + lane_sel + gq * 16, rq);
-        tmem_ld_wait();
-        float* dq_row = dq_accum + (long long)(b * T + (i - 1) * ATT_BLK + row) * lddq + h * HD + gq * 16;
-#pragma unroll
-        for (int e = 0; e < 16; e += 4)
-          red_add_v4_f32_attn(dq_row + e, __uint_as_float(rq[e]) * scale, __uint_as_float(rq[e + 1]) * scale,
-                              __uint_as_float(rq[e + 2]) * scale, __uint_as_float(rq[e + 3]) * scale);
-      }
-      fence_proxy_async_smem();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&bar_p[st]);
-    }
-    {  // tail: dQ of the last block, then the dK / dV accumulators of this key block
-      const int itl = n_it - 1, stl = itl & 1;
-      mbar_wait(&bar_d[stl], (itl >> 1) & 1);
-      tc_fence_after();
-      uint32_t rq[16], rk[16], rv[16];
-      tmem_ld_32x32b_x16(tm_dq + stl * HD + lane_sel + gq * 16, rq);
-      tmem_ld_32x32b_x16(tm_dk + lane_sel + gq * 16, rk);
-      tmem_ld_32x32b_x16(tm_dv + lane_sel + gq * 16, rv);
-      tmem_ld_wait();
-      float* dq_row = dq_accum + (long long)(b * T + (jblk + itl) * ATT_BLK + row) * lddq + h * HD + gq * 16;
-#pragma unroll
-      for (int e = 0; e < 16; e += 4)
-        red_add_v4_f32_attn(dq_row + e, __uint_as_float(rq[e]) * scale, __uint_as_float(rq[e + 1]) * scale,
-                            __uint_as_float(rq[e + 2]) * scale, __uint_as_float(rq[e + 3]) * scale);
-      bf16* dk_row = dk + (long long)(kv_row0 + row) * lddkv + h * HD + gq * 16;
-      bf16* dv_row = dv + (long long)(kv_row0 + row) * lddkv + h * HD + gq * 16;
-#pragma unroll
-      for (int g = 0; g < 2; ++g) {
-        const int e = g * 8;
-        float fk[8], fv[8];
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          fk[u] = __uint_as_float(rk[e + u]) * scale;
-          fv[u] = __uint_as_float(rv[e + u]);
-        }
-        *reinterpret_cast<uint4*>(dk_row + e) =
-            make_uint4(pack_bf16x2(fk[0], fk[1]), pack_bf16x2(fk[2], fk[3]), pack_bf16x2(fk[4], fk[5]), pack_bf16x2(fk[6], fk[7]));
-        *reinterpret_cast<uint4*>(dv_row + e) =
-            make_uint4(pack_bf16x2(fv[0], fv[1]), pack_bf16x2(fv[2], fv[3]), pack_bf16x2(fv[4], fv[5]), pack_bf16x2(fv[6], fv[7]));
-      }
-    }
-  }
-
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 8) {
-    tc_fence_after();
-    tmem_dealloc(tmem_base, 512);
-  }
-}
-
-// Backward, persistent + software-pipelined (head_dim 32, default).  One CTA per SM walks a static list of work items
+// Backward, persistent + software-pipelined (head_dim 32).  One CTA per SM walks a static list of work items
 // (batch, head, 128-key block j), heaviest first; an item loops over the query blocks i >= j.  All (item, i) steps of a
 // CTA form ONE flattened sequence g = 0, 1, 2 ... and every resource is ring-indexed by g (or by the item ordinal k), so
 // the pipeline never drains between items: the issue warp loads K / V / Q / dO of the next item and issues its score
@@ -1354,15 +553,20 @@ DTC_DEVICE void bwd_cursor_next(BwdCursor& c, int stride, int n_items, int BH, i
   bwd_cursor_decode(c, n_items, BH, H, nblk);
 }
 
-template <int HD>
-__global__ void __launch_bounds__(288, 1)
+template <int HD, int NG>
+__global__ void __launch_bounds__(NG * 128 + 32, 1)
 flash_attn_bwd_persist_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
                               const __grid_constant__ CUtensorMap tm_v, const __grid_constant__ CUtensorMap tm_do,
-                              const float* __restrict__ lse2, const float* __restrict__ delta, float* __restrict__ dq_accum,
+                              const float* __restrict__ lse2, const float* __restrict__ delta,
+                              float* __restrict__ dq_accum,
                               long long lddq, bf16* __restrict__ dk, bf16* __restrict__ dv, long long lddkv, int T, int H,
                               int B, float scale, float scale_log2) {
   using C = AttnCfg<HD>;
   static_assert(HD == 32, "the pipelined backward is laid out for head_dim 32");
+  static_assert(NG == 2 || NG == 4, "2 or 4 column groups of softmax warps");
+  constexpr int CW = ATT_BLK / NG;   // key columns of S / dP handled by one softmax warp
+  constexpr int QC = HD / NG;        // columns of dQ / dK / dV read out by one softmax warp
+  constexpr int ISSUE_WARP = 4 * NG;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* sP = smem;                      // 2 buffers of [128 q x 128 k] bf16
@@ -1392,16 +596,16 @@ flash_attn_bwd_persist_kernel(const __grid_constant__ CUtensorMap tm_q, const __
     tma_prefetch_desc(&tm_v);
     tma_prefetch_desc(&tm_do);
     mbar_init(bar_s, 1);
-    mbar_init(bar_c, 8);
+    mbar_init(bar_c, 4 * NG);
     for (int s = 0; s < 2; ++s) {
       mbar_init(&bar_kv[s], 1);
       mbar_init(&bar_ld[s], 1);
-      mbar_init(&bar_p[s], 8);
+      mbar_init(&bar_p[s], 4 * NG);
       mbar_init(&bar_d[s], 1);
     }
     fence_barrier_init();
   }
-  if (warp == 8) {
+  if (warp == ISSUE_WARP) {
     tmem_alloc(tmem_ptr_smem, 512);
     tmem_relinquish();
   }
@@ -1420,7 +624,7 @@ flash_attn_bwd_persist_kernel(const __grid_constant__ CUtensorMap tm_q, const __
   first.k = 0;
   bwd_cursor_decode(first, n_items, BH, H, nblk);
 
-  if (warp == 8) {
+  if (warp == ISSUE_WARP) {
     // ------------------------------ issue warp ------------------------------
     if (elect_one() && first.valid) {
       constexpr uint32_t idesc_kk = make_idesc_bf16(128, 128, 0, 0);
@@ -1516,33 +720,33 @@ flash_attn_bwd_persist_kernel(const __grid_constant__ CUtensorMap tm_q, const __
   } else {
     // ------------------------------ softmax warps ------------------------------
     const int row = (warp & 3) * 32 + lane;  // query row inside the block (TMEM lane)
-    const int gq = warp >> 2;                // key-column half handled by this warp
+    const int gq = warp >> 2;                // key-column group handled by this warp
     const uint32_t lane_sel = (uint32_t)((warp & 3) * 32) << 16;
     // read-outs owed for the previous step: its dQ block and, when it closed an item, that item's dK / dV
     auto flush = [&](const BwdCursor& p, int g) {
       const int st = g & 1;
       mbar_wait(&bar_d[st], (g >> 1) & 1);
       tc_fence_after();
-      uint32_t rq[16];
-      tmem_ld_32x32b_x16(tm_dq + st * HD + lane_sel + gq * 16, rq);
+      uint32_t rq[QC];
+      tmem_ld_cols<QC>(tm_dq + st * HD + lane_sel + gq * QC, rq);
       const bool last = p.it == p.n_it - 1;
-      uint32_t rk[16], rv[16];
+      uint32_t rk[QC], rv[QC];
       if (last) {
-        tmem_ld_32x32b_x16(tm_acc + (p.k & 1) * 2 * HD + lane_sel + gq * 16, rv);
-        tmem_ld_32x32b_x16(tm_acc + (p.k & 1) * 2 * HD + HD + lane_sel + gq * 16, rk);
+        tmem_ld_cols<QC>(tm_acc + (p.k & 1) * 2 * HD + lane_sel + gq * QC, rv);
+        tmem_ld_cols<QC>(tm_acc + (p.k & 1) * 2 * HD + HD + lane_sel + gq * QC, rk);
       }
       tmem_ld_wait();
-      float* dq_row = dq_accum + (long long)(p.b * T + (p.jblk + p.it) * ATT_BLK + row) * lddq + p.h * HD + gq * 16;
+      float* dq_row = dq_accum + (long long)(p.b * T + (p.jblk + p.it) * ATT_BLK + row) * lddq + p.h * HD + gq * QC;
 #pragma unroll
-      for (int e = 0; e < 16; e += 4)
+      for (int e = 0; e < QC; e += 4)
         red_add_v4_f32_attn(dq_row + e, __uint_as_float(rq[e]) * scale, __uint_as_float(rq[e + 1]) * scale,
                             __uint_as_float(rq[e + 2]) * scale, __uint_as_float(rq[e + 3]) * scale);
       if (last) {
         const long long kv_row = (long long)(p.b * T + p.jblk * ATT_BLK + row);
-        bf16* dk_row = dk + kv_row * lddkv + p.h * HD + gq * 16;
-        bf16* dv_row = dv + kv_row * lddkv + p.h * HD + gq * 16;
+        bf16* dk_row = dk + kv_row * lddkv + p.h * HD + gq * QC;
+        bf16* dv_row = dv + kv_row * lddkv + p.h * HD + gq * QC;
 #pragma unroll
-        for (int gg = 0; gg < 2; ++gg) {
+        for (int gg = 0; gg < QC / 8; ++gg) {
           const int e = gg * 8;
           float fk[8], fv[8];
 #pragma unroll
@@ -1564,35 +768,38 @@ flash_attn_bwd_persist_kernel(const __grid_constant__ CUtensorMap tm_q, const __
       const int i = cur.jblk + cur.it;
       const long long stat = ((long long)cur.b * H + cur.h) * T + i * ATT_BLK + row;
       const float lse_r = lse2[stat];
+      // delta = rowsum(dO * O) comes from a pre-pass kernel: computing it in here was measured twice (global row loads:
+      // 45 -> 66 us; from TMA-loaded O / dO tiles in shared memory: 45 -> 50 us) and lost both times
       const float delta_r = delta[stat];
       mbar_wait(bar_s, g & 1);
       tc_fence_after();
-      uint32_t rs[64], rp[64];
-      tmem_ld_32x32b_x32(tm_s + lane_sel + gq * 64, rs);
-      tmem_ld_32x32b_x32(tm_s + lane_sel + gq * 64 + 32, rs + 32);
-      tmem_ld_32x32b_x32(tm_dp + lane_sel + gq * 64, rp);
-      tmem_ld_32x32b_x32(tm_dp + lane_sel + gq * 64 + 32, rp + 32);
+      uint32_t rs[CW], rp[CW];
+#pragma unroll
+      for (int c = 0; c < CW / 32; ++c) {
+        tmem_ld_32x32b_x32(tm_s + lane_sel + gq * CW + c * 32, rs + c * 32);
+        tmem_ld_32x32b_x32(tm_dp + lane_sel + gq * CW + c * 32, rp + c * 32);
+      }
       tmem_ld_wait();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_c);
       if (cur.it == 0) {  // diagonal block (i == j): key column c is visible to query row r iff c <= r
-        const int lim = row - gq * 64;
+        const int lim = row - gq * CW;
 #pragma unroll
-        for (int e = 0; e < 64; ++e)
+        for (int e = 0; e < CW; ++e)
           if (e > lim) rs[e] = 0xff800000u;  // -inf -> P = 0
       }
       uint8_t* pbuf = sP + st * C::P_BYTES;
       uint8_t* dsbuf = sDS + st * C::P_BYTES;
 #pragma unroll
-      for (int gg = 0; gg < 8; ++gg) {
+      for (int gg = 0; gg < CW / 8; ++gg) {
         float p[8], ds[8];
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
           p[e] = ex2_ftz(fmaf(__uint_as_float(rs[gg * 8 + e]), scale_log2, -lse_r));
           ds[e] = p[e] * (__uint_as_float(rp[gg * 8 + e]) - delta_r);
         }
-        const uint32_t off = p_tile_offset(row, gq * 8 + gg);
+        const uint32_t off = p_tile_offset(row, gq * (CW / 8) + gg);
         *reinterpret_cast<uint4*>(pbuf + off) =
             make_uint4(pack_bf16x2(p[0], p[1]), pack_bf16x2(p[2], p[3]), pack_bf16x2(p[4], p[5]), pack_bf16x2(p[6], p[7]));
         *reinterpret_cast<uint4*>(dsbuf + off) = make_uint4(pack_bf16x2(ds[0], ds[1]), pack_bf16x2(ds[2], ds[3]),
@@ -1611,7 +818,7 @@ flash_attn_bwd_persist_kernel(const __grid_constant__ CUtensorMap tm_q, const __
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 8) {
+  if (warp == ISSUE_WARP) {
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);
   }
@@ -1627,47 +834,26 @@ template <int HD>
 static int launch_fwd(const void* q, const void* k, const void* v, long long ld, void* out, long long ldo, float* lse2,
                       int B, int H, int T, cudaStream_t stream) {
   using C = AttnCfg<HD>;
-  CUtensorMap tq, tk, tv;
+  CUtensorMap tq, tk64, tv64;
   int rc;
   const long long M = (long long)B * T;
   if ((rc = attn_tmap<HD>(&tq, q, M, H, ld))) return rc;
-  if ((rc = attn_tmap<HD>(&tk, k, M, H, ld))) return rc;
-  if ((rc = attn_tmap<HD>(&tv, v, M, H, ld))) return rc;
+  const CUtensorMapSwizzle swz = HD == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
+  if ((rc = make_tmap_2d_bf16(&tk64, k, M, (uint64_t)H * HD, ld, 64, HD, swz))) return rc;  // 64-key blocks
+  if ((rc = make_tmap_2d_bf16(&tv64, v, M, (uint64_t)H * HD, ld, 64, HD, swz))) return rc;
   const float scale = 1.f / sqrtf((float)HD);
   dim3 grid(T / ATT_BLK, H, B);
-  static const bool use_kv128 = getenv("DTC_ATTN_FWD_KV128") != nullptr;  // A/B switch: the 128-key-block kernel
-  static const bool use_serial = getenv("DTC_ATTN_FWD_SERIAL") != nullptr;  // A/B switch: the un-pipelined 64-key kernel
-  if (!use_kv128) {
-    CUtensorMap tk64, tv64;
-    const CUtensorMapSwizzle swz = HD == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
-    if ((rc = make_tmap_2d_bf16(&tk64, k, M, (uint64_t)H * HD, ld, 64, HD, swz))) return rc;
-    if ((rc = make_tmap_2d_bf16(&tv64, v, M, (uint64_t)H * HD, ld, 64, HD, swz))) return rc;
-    if (!use_serial) {
-      const int smem_p = C::TILE_BYTES + 2 * ATT_BLK * 128 + 4 * 64 * C::ROW_BYTES + 1024 + 256;
-      auto kern_p = flash_attn_fwd_pipe_kernel<HD>;
-      static dtc::SmemOptIn configured_p;  // per device
-      DTC_CHECK_CUDA(dtc::ensure_dyn_smem(kern_p, smem_p, configured_p));
-      DTC_CHECK_CUDA(dtc::launch(kern_p, grid, 160, smem_p, stream, tq, tk64, tv64, reinterpret_cast<bf16*>(out), ldo, lse2, T,
-                                 H, scale * LOG2E));
-      return 0;
-    }
-    const int smem64 = C::TILE_BYTES + ATT_BLK * 128 + 4 * 64 * C::ROW_BYTES + 1024 + 128;
-    auto kern64 = flash_attn_fwd_kv64_kernel<HD>;
-    static dtc::SmemOptIn configured64;  // per device
-    DTC_CHECK_CUDA(dtc::ensure_dyn_smem(kern64, smem64, configured64));
-    DTC_CHECK_CUDA(dtc::launch(kern64, grid, 128, smem64, stream, tq, tk64, tv64, reinterpret_cast<bf16*>(out), ldo, lse2, T, H,
-                               scale * LOG2E));
-    return 0;
-  }
-  const int smem = 5 * C::TILE_BYTES + C::P_BYTES + 1024 + 128;
-  auto kern = flash_attn_fwd_kernel<HD>;
-  static dtc::SmemOptIn configured;  // per device
-  DTC_CHECK_CUDA(dtc::ensure_dyn_smem(kern, smem, configured));
-  DTC_CHECK_CUDA(dtc::launch(kern, grid, 128, smem, stream, tq, tk, tv, reinterpret_cast<bf16*>(out), ldo, lse2, T, H, scale * LOG2E));
+  const int smem_p = C::TILE_BYTES + 2 * ATT_BLK * 128 + 4 * 64 * C::ROW_BYTES + 1024 + 256;
+  auto kern_p = flash_attn_fwd_pipe_kernel<HD>;
+  static dtc::SmemOptIn configured_p;  // per device
+  DTC_CHECK_CUDA(dtc::ensure_dyn_smem(kern_p, smem_p, configured_p));
+  DTC_CHECK_CUDA(dtc::launch(kern_p, grid, 160, smem_p, stream, tq, tk64, tv64, reinterpret_cast<bf16*>(out), ldo, lse2, T, H,
+                             scale * LOG2E));
   DTC_CHECK_LAUNCH();
   return 0;
 }
 
+// delta pre-pass, then head_dim 32: the persistent pipelined kernel; head_dim 64: the TMEM-accumulator kernel.
 template <int HD>
 static int launch_bwd(const void* q, const void* k, const void* v, long long ld, const void* o, long long ldo,
                       const void* d_o, long long lddo, const float* lse2, float* delta, float* dq_accum, long long lddq,
@@ -1680,64 +866,39 @@ static int launch_bwd(const void* q, const void* k, const void* v, long long ld,
   if ((rc = attn_tmap<HD>(&tk, k, M, H, ld))) return rc;
   if ((rc = attn_tmap<HD>(&tv, v, M, H, ld))) return rc;
   if ((rc = attn_tmap<HD>(&tdo, d_o, M, H, lddo))) return rc;
-  {
+  const float scale = 1.f / sqrtf((float)HD);
+  {  // delta[b, h, t] = rowsum(dO * O)
     const long long threads = M * H * (HD / 8);
-    DTC_CHECK_CUDA(dtc::launch(attn_bwd_prep_kernel<HD>, (int)((threads + 255) / 256), 256, 0, stream, 
+    DTC_CHECK_CUDA(dtc::launch(attn_bwd_prep_kernel<HD>, (int)((threads + 255) / 256), 256, 0, stream,
         reinterpret_cast<const bf16*>(o), ldo, reinterpret_cast<const bf16*>(d_o), lddo, delta, (int)M, T, H));
     DTC_CHECK_LAUNCH();
   }
-  const float scale_ = 1.f / sqrtf((float)HD);
-  static const bool use_v1 = getenv("DTC_ATTN_BWD_V1") != nullptr;  // A/B switch: TMEM-accumulator kernel
-  static const bool use_regacc = getenv("DTC_ATTN_BWD_REGACC") != nullptr;  // A/B switch: the un-pipelined register-accumulator kernel
   if constexpr (HD == 32) {
-    static const bool use_persist = getenv("DTC_ATTN_BWD_PERSIST") != nullptr;  // opt-in until validated on hardware
-    if (!use_v1 && !use_regacc && use_persist) {
-      const int smem4 = 4 * C::P_BYTES + 8 * C::TILE_BYTES + 1024 + 256;
-      auto kern4 = flash_attn_bwd_persist_kernel<HD>;
-      static dtc::SmemOptIn configured4;  // per device
-      DTC_CHECK_CUDA(dtc::ensure_dyn_smem(kern4, smem4, configured4));
-      int dev = 0, sms = 148;
-      if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-      const int n_items = B * H * (T / ATT_BLK);
-      const int grid4 = n_items < sms ? n_items : sms;
-      DTC_CHECK_CUDA(dtc::launch(kern4, grid4, 288, smem4, stream, tq, tk, tv, tdo, lse2, delta, dq_accum, lddq,
-                                 reinterpret_cast<bf16*>(dk), reinterpret_cast<bf16*>(dv), lddkv, T, H, B, scale_,
-                                 scale_ * LOG2E));
-      return 0;
-    }
-    if (!use_v1 && !use_regacc) {
-      const int smem3 = 4 * C::P_BYTES + 6 * C::TILE_BYTES + 1024 + 256;
-      auto kern3 = flash_attn_bwd_pipe_kernel<HD>;
-      static dtc::SmemOptIn configured3;  // per device
-      DTC_CHECK_CUDA(dtc::ensure_dyn_smem(kern3, smem3, configured3));
-      dim3 grid3(T / ATT_BLK, H, B);
-      DTC_CHECK_CUDA(dtc::launch(kern3, grid3, 288, smem3, stream, tq, tk, tv, tdo, lse2, delta, dq_accum, lddq,
-                                 reinterpret_cast<bf16*>(dk), reinterpret_cast<bf16*>(dv), lddkv, T, H, scale_,
-                                 scale_ * LOG2E));
-      return 0;
-    }
-    if (!use_v1) {
-      const int smem2 = 5 * C::TILE_BYTES + 2 * C::P_BYTES + 2 * ATT_BLK * 4 + 1024 + 128;
-      auto kern2 = flash_attn_bwd_regacc_kernel<HD>;
-      static dtc::SmemOptIn configured2;  // per device
-      DTC_CHECK_CUDA(dtc::ensure_dyn_smem(kern2, smem2, configured2));
-      dim3 grid2(T / ATT_BLK, H, B);
-      DTC_CHECK_CUDA(dtc::launch(kern2, grid2, 128, smem2, stream, tq, tk, tv, tdo, lse2, delta, dq_accum, lddq,
-                                 reinterpret_cast<bf16*>(dk), reinterpret_cast<bf16*>(dv), lddkv, T, H, scale_,
-                                 scale_ * LOG2E));
-      return 0;
-    }
+    static const bool ng2 = getenv("DTC_ATTN_BWD_NG2") != nullptr;  // A/B: 8 softmax warps per CTA instead of 16
+    const int smem4 = 4 * C::P_BYTES + 8 * C::TILE_BYTES + 1024 + 256;
+    auto kern4 = ng2 ? flash_attn_bwd_persist_kernel<HD, 2> : flash_attn_bwd_persist_kernel<HD, 4>;
+    static dtc::SmemOptIn configured4[2];  // per instantiation, per device
+    DTC_CHECK_CUDA(dtc::ensure_dyn_smem(kern4, smem4, configured4[ng2 ? 0 : 1]));
+    int dev = 0, sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int n_items = B * H * (T / ATT_BLK);
+    const int grid4 = n_items < sms ? n_items : sms;
+    DTC_CHECK_CUDA(dtc::launch(kern4, grid4, ng2 ? 288 : 544, smem4, stream, tq, tk, tv, tdo, lse2, delta, dq_accum, lddq,
+                               reinterpret_cast<bf16*>(dk), reinterpret_cast<bf16*>(dv), lddkv, T, H, B, scale,
+                               scale * LOG2E));
+    DTC_CHECK_LAUNCH();
+    return 0;
+  } else {
+    const int smem = 6 * C::TILE_BYTES + 2 * C::P_BYTES + 4 * ATT_BLK * 4 + 1024 + 128;
+    auto kern = flash_attn_bwd_kernel<HD>;
+    static dtc::SmemOptIn configured;  // per device
+    DTC_CHECK_CUDA(dtc::ensure_dyn_smem(kern, smem, configured));
+    dim3 grid(T / ATT_BLK, H, B);
+    DTC_CHECK_CUDA(dtc::launch(kern, grid, 128, smem, stream, tq, tk, tv, tdo, lse2, delta, dq_accum, lddq,
+                               reinterpret_cast<bf16*>(dk), reinterpret_cast<bf16*>(dv), lddkv, T, H, scale, scale * LOG2E));
+    DTC_CHECK_LAUNCH();
+    return 0;
   }
-  const int smem = 6 * C::TILE_BYTES + 2 * C::P_BYTES + 4 * ATT_BLK * 4 + 1024 + 128;
-  auto kern = flash_attn_bwd_kernel<HD>;
-  static dtc::SmemOptIn configured;  // per device
-  DTC_CHECK_CUDA(dtc::ensure_dyn_smem(kern, smem, configured));
-  const float scale = 1.f / sqrtf((float)HD);
-  dim3 grid(T / ATT_BLK, H, B);
-  DTC_CHECK_CUDA(dtc::launch(kern, grid, 128, smem, stream, tq, tk, tv, tdo, lse2, delta, dq_accum, lddq, reinterpret_cast<bf16*>(dk),
-                                    reinterpret_cast<bf16*>(dv), lddkv, T, H, scale, scale * LOG2E));
-  DTC_CHECK_LAUNCH();
-  return 0;
 }
 
 }  // namespace dtc

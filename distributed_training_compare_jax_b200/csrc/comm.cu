@@ -340,6 +340,75 @@ static int fill_peers(PeerPtrs* out, const unsigned long long* ptrs, int world) 
   return 0;
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Small all-gather / all-reduce through symmetric memory (tensor-parallel step: cross-entropy statistics X7, partial
+// gradients of the replicated LayerNorm / row-bias leaves).  Messages of a few 10-100 KB: latency, not bandwidth.
+//   push : dst[slot_off + i] = src[i] on EVERY rank (multimem.st through the switch, or one store per peer)
+//   sum  : out[i] (+)= sum_r slots[r * stride + i]                      (local, after a flag barrier)
+// all-gather = push into slot `rank` + barrier;  all-reduce = push + barrier + sum.
+// ---------------------------------------------------------------------------------------------------------
+namespace dtc {
+__global__ void symm_push_f32_kernel(const float* __restrict__ src, float* mc_dst, PeerPtrs peers, int world,
+                                     long long dst_off, long long n4) {
+  pdl_launch_dependents();
+  pdl_wait();
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+    const float4 v = reinterpret_cast<const float4*>(src)[i];
+    if (mc_dst != nullptr) {
+      asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc_dst + dst_off + i * 4), "f"(v.x),
+                   "f"(v.y), "f"(v.z), "f"(v.w)
+                   : "memory");
+    } else {
+      for (int r = 0; r < world; ++r) reinterpret_cast<float4*>(reinterpret_cast<float*>(peers.p[r]) + dst_off)[i] = v;
+    }
+  }
+}
+__global__ void sum_slots_f32_kernel(const float* __restrict__ slots, long long stride, int world, float* __restrict__ out,
+                                     long long n4, int accumulate) {
+  pdl_launch_dependents();
+  pdl_wait();
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+    float4 a = accumulate ? reinterpret_cast<const float4*>(out)[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int r = 0; r < world; ++r) {
+      const float4 v = __ldcg(reinterpret_cast<const float4*>(slots + r * stride) + i);  // written by peers: L2-coherent path
+      a.x += v.x;
+      a.y += v.y;
+      a.z += v.z;
+      a.w += v.w;
+    }
+    reinterpret_cast<float4*>(out)[i] = a;
+  }
+}
+}  // namespace dtc
+
+// dst_ptrs: HOST array of `world` device addresses of the symmetric destination buffer; mc_dst: its multicast address or 0.
+// n and dst_off in floats, multiples of 4; src / destinations 16-byte aligned.
+extern "C" int dtc_symm_push_f32(const float* src, unsigned long long mc_dst, const unsigned long long* dst_ptrs, int world,
+                                 long long dst_off, long long n, cudaStream_t stream) {
+  DTC_CHECK_ARG(n > 0 && n % 4 == 0 && dst_off % 4 == 0, "symm_push: n=%lld dst_off=%lld must be multiples of 4", n, dst_off);
+  dtc::PeerPtrs peers;
+  int rc = fill_peers(&peers, dst_ptrs, world);
+  if (rc) return rc;
+  const long long n4 = n / 4;
+  int blocks = (int)((n4 + 255) / 256);
+  if (blocks > 296) blocks = 296;
+  DTC_CHECK_CUDA(dtc::launch(dtc::symm_push_f32_kernel, blocks, 256, 0, stream, src, reinterpret_cast<float*>(mc_dst), peers, world,
+                             dst_off, n4));
+  DTC_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int dtc_sum_slots_f32(const float* slots, long long stride, int world, float* out, long long n, int accumulate,
+                                 cudaStream_t stream) {
+  DTC_CHECK_ARG(n > 0 && n % 4 == 0 && stride % 4 == 0 && world >= 1, "sum_slots: n=%lld stride=%lld world=%d", n, stride, world);
+  const long long n4 = n / 4;
+  int blocks = (int)((n4 + 255) / 256);
+  if (blocks > 296) blocks = 296;
+  DTC_CHECK_CUDA(dtc::launch(dtc::sum_slots_f32_kernel, blocks, 256, 0, stream, slots, stride, world, out, n4, accumulate));
+  DTC_CHECK_LAUNCH();
+  return 0;
+}
+
 // flag_ptrs: HOST array of `world` device addresses (each rank's symmetric flag buffer, n_slots*world ints, zeroed).
 extern "C" int dtc_symm_barrier(const unsigned long long* flag_ptrs, int rank, int world, int slot, cudaStream_t stream) {
   PeerPtrs f;

@@ -329,6 +329,19 @@ DTC_DEVICE void tmem_ld_32x32b_x16(uint32_t taddr, uint32_t* r) {
       : "r"(taddr)
       : "memory");
 }
+DTC_DEVICE void tmem_ld_32x32b_x8(uint32_t taddr, uint32_t* r) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(taddr)
+               : "memory");
+}
+template <int N>
+DTC_DEVICE void tmem_ld_cols(uint32_t taddr, uint32_t* r) {  // N = 8, 16 or 32 consecutive fp32 columns of this warp's lanes
+  static_assert(N == 8 || N == 16 || N == 32, "tmem_ld_cols: 8, 16 or 32 columns");
+  if constexpr (N == 8) tmem_ld_32x32b_x8(taddr, r);
+  else if constexpr (N == 16) tmem_ld_32x32b_x16(taddr, r);
+  else tmem_ld_32x32b_x32(taddr, r);
+}
 DTC_DEVICE void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // ----------------------------------------------------------------------------------------------

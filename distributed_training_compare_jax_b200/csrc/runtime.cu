@@ -60,8 +60,10 @@ __global__ void cast_f32_to_bf16_kernel(const float* __restrict__ in, bf16* __re
 }
 
 // dst_bf16[m, dst_col0 + c] = bf16(src_f32[m, c])   (attention-backward dQ accumulator -> dqkv slice)
-__global__ void cast_f32_to_bf16_2d_kernel(const float* __restrict__ in, long long ld_in, bf16* __restrict__ out,
-                                           long long ld_out, int rows, int cols) {
+// clear_src != 0: the source is zeroed behind the read (the attention backward's dQ accumulator is then clean for the
+// next layer without a separate fill kernel).
+__global__ void cast_f32_to_bf16_2d_kernel(float* __restrict__ in, long long ld_in, bf16* __restrict__ out,
+                                           long long ld_out, int rows, int cols, int clear_src) {
   pdl_launch_dependents();  // PDL: let the next kernel's prologue overlap this kernel
   pdl_wait();               // ... and do not touch global memory before the previous kernel has completed
   const int cpr = cols / 8;
@@ -73,6 +75,10 @@ __global__ void cast_f32_to_bf16_2d_kernel(const float* __restrict__ in, long lo
     const float4 b = *reinterpret_cast<const float4*>(in + r * ld_in + c + 4);
     *reinterpret_cast<uint4*>(out + r * ld_out + c) =
         make_uint4(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w), pack_bf16x2(b.x, b.y), pack_bf16x2(b.z, b.w));
+    if (clear_src) {
+      *reinterpret_cast<float4*>(in + r * ld_in + c) = make_float4(0.f, 0.f, 0.f, 0.f);
+      *reinterpret_cast<float4*>(in + r * ld_in + c + 4) = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
   }
 }
 
@@ -117,14 +123,26 @@ extern "C" int dtc_cast_f32_to_bf16(const float* in, void* out, long long n, cud
   return 0;
 }
 
-extern "C" int dtc_cast_f32_to_bf16_2d(const float* in, long long ld_in, void* out, long long ld_out, int rows, int cols,
-                                       cudaStream_t stream) {
+static int cast2d(float* in, long long ld_in, void* out, long long ld_out, int rows, int cols, int clear_src,
+                  cudaStream_t stream) {
   DTC_CHECK_ARG(cols % 8 == 0 && ld_in % 4 == 0 && ld_out % 8 == 0, "cast2d: cols/ld alignment");
   long long total = (long long)rows * (cols / 8);
   if (total == 0) return 0;
   int blocks = (int)((total + 255) / 256);
   if (blocks > 148 * 8) blocks = 148 * 8;
-  DTC_CHECK_CUDA(dtc::launch(dtc::cast_f32_to_bf16_2d_kernel, blocks, 256, 0, stream, in, ld_in, reinterpret_cast<bf16*>(out), ld_out, rows, cols));
+  DTC_CHECK_CUDA(dtc::launch(dtc::cast_f32_to_bf16_2d_kernel, blocks, 256, 0, stream, in, ld_in, reinterpret_cast<bf16*>(out), ld_out, rows, cols,
+                             clear_src));
   DTC_CHECK_LAUNCH();
   return 0;
+}
+
+extern "C" int dtc_cast_f32_to_bf16_2d(const float* in, long long ld_in, void* out, long long ld_out, int rows, int cols,
+                                       cudaStream_t stream) {
+  return cast2d(const_cast<float*>(in), ld_in, out, ld_out, rows, cols, 0, stream);
+}
+
+// Same, and the fp32 source is set to zero behind the read.
+extern "C" int dtc_cast_f32_to_bf16_2d_clear(float* in, long long ld_in, void* out, long long ld_out, int rows, int cols,
+                                             cudaStream_t stream) {
+  return cast2d(in, ld_in, out, ld_out, rows, cols, 1, stream);
 }

@@ -58,6 +58,6 @@ class CausalSelfAttention:
         eng.side_work(out_param_grads, layer=l)
         Fn.gemm(dh, c["wo"][l], out=ws.dattn)
         Fn.flash_attn_bwd(ws.qkv[l], ws.attn[l], ws.dattn, ws.lse2[l], ws.B, self.local.heads_local, ws.T,
-                          self.config.head_dim, dqkv=ws.dqkv, dq_accum=ws.dq_accum, delta=ws.delta)
+                          self.config.head_dim, dqkv=ws.dqkv, dq_accum=ws.dq_accum, delta=ws.delta, dq_clean=True)
         eng.side_work(qkv_param_grads, layer=l)
         ws.dln_cur = eng.tp_reduced_gemm(ws.dqkv, c["wqkv"][l], out=ws.dln)

@@ -205,20 +205,24 @@ def flash_attn_fwd(qkv: torch.Tensor, B: int, H: int, T: int, hd: int, out=None,
     return out, lse2
 
 
-def flash_attn_bwd(qkv, o, d_o, lse2, B: int, H: int, T: int, hd: int, dqkv=None, dq_accum=None, delta=None):
-    """Returns dqkv [B*T, 3*H*hd] bf16.  ``dq_accum`` (fp32 [B*T, H*hd]) is zeroed here unless provided zeroed."""
+def flash_attn_bwd(qkv, o, d_o, lse2, B: int, H: int, T: int, hd: int, dqkv=None, dq_accum=None, delta=None,
+                   dq_clean: bool = False):
+    """Returns dqkv [B*T, 3*H*hd] bf16.  ``dq_accum`` (fp32 [B*T, H*hd]) must be zero when the kernel starts: it is zeroed
+    here, unless ``dq_clean`` — then the caller guarantees a zero buffer on entry and gets a zero buffer back (the final
+    cast clears it behind its read: no fill kernel per layer)."""
     M, Dl = B * T, H * hd
     dqkv = torch.empty((M, 3 * Dl), device=qkv.device, dtype=BF16) if dqkv is None else dqkv
     if dq_accum is None:
         dq_accum = torch.zeros((M, Dl), device=qkv.device, dtype=F32)
-    else:
+    elif not dq_clean:
         dq_accum.zero_()
     delta = torch.empty((B, H, T), device=qkv.device, dtype=F32) if delta is None else delta
     q, k, v = qkv[:, :Dl], qkv[:, Dl:2 * Dl], qkv[:, 2 * Dl:]
     dk, dv = dqkv[:, Dl:2 * Dl], dqkv[:, 2 * Dl:]
     native.call("dtc_flash_attn_bwd", q, k, v, qkv.stride(0), o, o.stride(0), d_o, d_o.stride(0), lse2, delta, dq_accum,
                 dq_accum.stride(0), dk, dv, dqkv.stride(0), B, H, T, hd)
-    native.call("dtc_cast_f32_to_bf16_2d", dq_accum, dq_accum.stride(0), dqkv, dqkv.stride(0), M, Dl)
+    native.call("dtc_cast_f32_to_bf16_2d_clear" if dq_clean else "dtc_cast_f32_to_bf16_2d", dq_accum, dq_accum.stride(0),
+                dqkv, dqkv.stride(0), M, Dl)
     return dqkv
 
 

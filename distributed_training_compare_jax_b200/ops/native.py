@@ -25,6 +25,7 @@ P, I, L, F, U64, U32 = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_ulonglo
 _PROTOS: dict[str, list[Any]] = {
     "dtc_cast_f32_to_bf16": [P, P, L],
     "dtc_cast_f32_to_bf16_2d": [P, L, P, L, I, I],
+    "dtc_cast_f32_to_bf16_2d_clear": [P, L, P, L, I, I],
     "dtc_gemm_bf16": [P, L, I, P, L, I, I, I, I, I, F, P, P, L, P, L, P, L, I, I, I],
     "dtc_flash_attn_fwd": [P, P, P, L, P, L, P, I, I, I, I],
     "dtc_flash_attn_bwd": [P, P, P, L, P, L, P, L, P, P, P, L, P, P, L, I, I, I, I],
@@ -43,6 +44,8 @@ _PROTOS: dict[str, list[Any]] = {
     "dtc_colsum": [P, L, I, I, P],
     "dtc_symm_barrier": [P, I, I, I],
     "dtc_jitter": [U32, U32, P],
+    "dtc_symm_push_f32": [P, U64, P, I, L, L],
+    "dtc_sum_slots_f32": [P, L, I, P, L, I],
     "dtc_gemm_bf16_scatter": [P, L, P, L, I, I, I, I, P, I, I, L, I, I],
     "dtc_gemm_wgrad_grouped": [I, P, P, P, P, P, P, I, P, P, F, I, I],
     "dtc_colsum_grouped": [I, P, P, P, P, P],

@@ -91,6 +91,15 @@ class SeqParallelState:
         self.mean2, self.rstd2 = e(L, Ms, dtype=F32), e(L, Ms, dtype=F32)
         self.meanf, self.rstdf = e(Ms, dtype=F32), e(Ms, dtype=F32)
         self.part_ptrs = self._peer_array(self.part)
+        # small fp32 exchanges (cross-entropy statistics, partial gradients of replicated leaves): one slot per rank on
+        # every rank, filled by dtc_symm_push_f32 — no NCCL call is left inside the step graph
+        st = engine.store
+        self.pg_off, self.pg_n = st.offsets["ln1_g"][0], st.rep_numel - st.offsets["ln1_g"][0]
+        self.ce_n = M * 3
+        if n > 1:
+            self.small = SymmBuffer(n * (self.ce_n + self.pg_n), F32, dev, tp.group)
+            self.ce_slots = self.small.tensor[:n * self.ce_n].view(n, M, 3)
+            self.pg_slots = self.small.tensor[n * self.ce_n:]
         # Experimental (DTC_SP_FOLD=1, not yet run on hardware): no barrier kernels between producers and consumers — the
         # last CTA of a scatter GEMM / LayerNorm kernel publishes a sequence number to every rank, the LayerNorm kernels wait
         # in their prologue and a one-CTA wait kernel sits in front of the stock GEMMs that read a gathered operand.
@@ -163,6 +172,23 @@ class SeqParallelState:
         else:
             Fn.sp_ln_bwd(self.part, self.n, x, mean, rstd, gamma, dres, dgamma, dbeta, mc, peers, n, self.row0)
 
+    def all_gather_small(self, local: torch.Tensor) -> torch.Tensor:
+        """[M, 3] fp32 statistics of every rank -> [n, M, 3] (push into slot `rank` everywhere + flag barrier)."""
+        from ..ops import native
+        native.call("dtc_symm_push_f32", local, self.small.mc_ptr if self.use_mc else 0, self.small.ptr_array, self.n,
+                    self.rank * self.ce_n, self.ce_n)
+        self.barrier()
+        return self.ce_slots
+
+    def all_reduce_partial_grads(self, flat_grad: torch.Tensor) -> None:
+        """Sum over the TP group of the partial-gradient range (LayerNorm scale / bias, out_proj / fc2 bias), in place."""
+        from ..ops import native
+        mine = flat_grad[self.pg_off:self.pg_off + self.pg_n]
+        native.call("dtc_symm_push_f32", mine, self.small.mc_ptr if self.use_mc else 0, self.small.ptr_array, self.n,
+                    self.n * self.ce_n + self.rank * self.pg_n, self.pg_n)
+        self.barrier()
+        native.call("dtc_sum_slots_f32", self.pg_slots, self.pg_n, self.n, mine, self.pg_n, 0)
+
     def own(self, full: torch.Tensor) -> torch.Tensor:
         return full[self.row0:self.row0 + self.Ms]
 
@@ -229,8 +255,7 @@ class SeqParallelEngine(NativeStageEngine):
             Fn.ce_fwd_bwd(ws.logits, ws.labels, nv, gscale, loss_rows=ws.loss_rows)
         else:
             Fn.ce_stats(ws.logits, ws.labels, nv, lo.vocab_start, ws.ce_stats_local)
-            tp.all_gather_into(ws.ce_stats_all, ws.ce_stats_local)
-            Fn.ce_combine(ws.ce_stats_all, n, ws.M, ws.lse, ws.loss_rows)
+            Fn.ce_combine(sp.all_gather_small(ws.ce_stats_local), n, ws.M, ws.lse, ws.loss_rows)
             Fn.ce_grad(ws.logits, ws.labels, ws.lse, nv, lo.vocab_start, gscale)
 
         def head_param_grads():   # logits now hold dlogits (pad columns are zero)
@@ -292,7 +317,7 @@ class SeqParallelEngine(NativeStageEngine):
                 self.side_work(out_param_grads)
                 Fn.gemm(sp.dMID, c["wo"][l], out=ws.dattn)
                 Fn.flash_attn_bwd(ws.qkv[l], ws.attn[l], ws.dattn, ws.lse2[l], ws.B, Hl, ws.T, hd, dqkv=ws.dqkv,
-                                  dq_accum=ws.dq_accum, delta=ws.delta)
+                                  dq_accum=ws.dq_accum, delta=ws.delta, dq_clean=True)
                 self.side_work(qkv_param_grads)
                 sp.gemm_scatter(ws.dqkv, c["wqkv"][l], b_mn=False)
                 sp.scattered()
@@ -304,5 +329,5 @@ class SeqParallelEngine(NativeStageEngine):
         Fn.embed_bwd(ws.ids, cur, g["wte"], g["wpe"], ws.T, cfg.dropout, self.seed, self.store.step,
                      stream_id=ws.stream_id, row_offset=ws.row_offset)
         if sp.n > 1:
-            self.mesh.tp.all_reduce(self._partial_grads)
+            sp.all_reduce_partial_grads(self.store.flat_grad)
         return None

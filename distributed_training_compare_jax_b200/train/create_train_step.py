@@ -99,7 +99,13 @@ class _GraphedBody:
         torch.cuda.synchronize()
         g = torch.cuda.CUDAGraph()
         before = native.launches()
-        with torch.cuda.graph(g):
+        # The step is captured on a HIGH-priority stream: kernel nodes inherit the priority of the stream they were
+        # captured on, the engine's side streams (weight gradients, bucketed DP reduction) keep the default (lowest)
+        # priority, so whenever both have thread blocks waiting for an SM the dependent chain goes first.
+        import os
+        prio = os.environ.get("DTC_GRAPH_PRIO", "1") != "0"
+        cap = torch.cuda.Stream(priority=-1) if prio else None
+        with torch.cuda.graph(g, stream=cap):
             self.body()
         self.launches_per_replay = native.launches() - before  # captured, not executed
         native.add_launches(-self.launches_per_replay)

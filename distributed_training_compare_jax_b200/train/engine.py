@@ -52,7 +52,8 @@ class Workspace:
         # backward scratch (shared by all layers)
         self.dh_a, self.dh_b, self.dh_mid, self.dln = e(M, D), e(M, D), e(M, D), e(M, D)
         self.dqkv, self.dattn, self.df1 = e(M, 3 * Dl), e(M, Dl), e(M, Fl)
-        self.dq_accum, self.delta = e(M, Dl, dtype=F32), e(B, Hl, T, dtype=F32)
+        # zero on entry of every attention backward and zero again when it returns (Fn.flash_attn_bwd(dq_clean=True))
+        self.dq_accum, self.delta = torch.zeros(M, Dl, device=device, dtype=F32), e(B, Hl, T, dtype=F32)
         if local.has_head:
             self.lnf, self.meanf, self.rstdf = e(M, D), e(M, dtype=F32), e(M, dtype=F32)
             self.logits = e(M, Vl)
@@ -95,7 +96,7 @@ class NativeStageEngine(StageEngineBase):
         # Weight-gradient work (wgrad GEMMs + bias column sums) does not feed the backward chain: it runs on a side
         # stream concurrently with the dgrad / attention / LayerNorm chain.  Both streams use the light (two CTAs per SM)
         # configuration of the persistent GEMM, so a CTA of each stream fits on one SM.
-        self.overlap_wgrad = overlap_wgrad
+        self.overlap_wgrad = overlap_wgrad and __import__('os').environ.get('DTC_WGRAD_OVERLAP', '1') != '0'
         self.bwd_gemm_impl = int(__import__('os').environ.get('DTC_BWD_GEMM_IMPL', '0'))
         # One grouped wgrad launch + one grouped bias-grad launch per layer (default; measured on B200: 5.43 -> 5.21 ms per
         # step on one GPU, profiles/r2/).  DTC_WGRAD_GROUPED=0 restores the four split-K launches + four column sums.

@@ -24,6 +24,8 @@ int dtc_version(void);
 int dtc_set_pdl(int enabled); /* programmatic dependent launch for all kernels: 0 (default) / 1; env DTC_PDL=1 */
 int dtc_device_arch(void); /* compute capability major*10+minor of the current device, <0 on error */
 int dtc_cast_f32_to_bf16(const float* in, void* out, long long n, cudaStream_t stream);
+int dtc_cast_f32_to_bf16_2d_clear(float* in, long long ld_in, void* out, long long ld_out, int rows, int cols,
+                                  cudaStream_t stream); /* same, and `in` is zeroed behind the read */
 int dtc_cast_f32_to_bf16_2d(const float* in, long long ld_in, void* out, long long ld_out, int rows, int cols,
                             cudaStream_t stream);
 
@@ -107,6 +109,14 @@ int dtc_symm_barrier(const unsigned long long* flag_ptrs, int rank, int world, i
 /* Protocol stress aid (the reference has no race tooling): stalls the stream for
  * hash(seed, *step) % max_ns nanoseconds, max_ns <= 1e6; `step` = device int that changes between graph replays (or NULL). */
 int dtc_jitter(unsigned seed, unsigned max_ns, const int* step, cudaStream_t stream);
+/* small all-gather / all-reduce through symmetric memory (vocab-parallel CE statistics X7, partial LayerNorm / row-bias
+ * gradients of the tensor-parallel step; ref: the max / sum exchanges GSPMD derives for train/create_train_step.py:32
+ * over parallel/sharding.py:33-39): push a local fp32 range into slot `dst_off` of EVERY rank's buffer, then (after a
+ * dtc_symm_barrier) sum the `world` slots locally. */
+int dtc_symm_push_f32(const float* src, unsigned long long mc_dst, const unsigned long long* dst_ptrs, int world,
+                      long long dst_off, long long n, cudaStream_t stream);
+int dtc_sum_slots_f32(const float* slots, long long stride, int world, float* out, long long n, int accumulate,
+                      cudaStream_t stream);
 int dtc_dp_num_partials(long long n);
 int dtc_dp_reduce_scatter(float* local_grad, unsigned long long mc_grad, const unsigned long long* grad_ptrs, int rank,
                           int world, long long off, long long n, float* partials, cudaStream_t stream);
