@@ -14,6 +14,7 @@ Prints one JSON line with device-timed (CUDA events, max over ranks) tokens/s.
 import argparse
 import json
 import os
+import sys
 
 import torch
 import torch.distributed as dist
@@ -57,18 +58,29 @@ def main():
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--batch", type=int, default=8)
-    ap.add_argument("--graph", action="store_true", help="capture the whole training step into one CUDA graph (1 GPU)")
+    ap.add_argument("--graph", action="store_true", help="capture the whole training step into one CUDA graph (with DDP: the "
+                    "PyTorch recipe — DDP built and warmed up for 11 iterations on a side stream, NCCL async error "
+                    "handling off; falls back to eager launches if the capture fails)")
     args = ap.parse_args()
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     local_rank = int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    use_graph = args.graph
     if world > 1:
+        if use_graph:
+            os.environ["TORCH_NCCL_ASYNC_ERROR_HANDLING"] = "0"
         dist.init_process_group("nccl", device_id=dev)
     torch.manual_seed(0)
     model = GPT().to(dev)
-    net = nn.parallel.DistributedDataParallel(model, device_ids=[dev.index]) if world > 1 else model
-    use_graph = args.graph and world == 1
+    if world > 1:
+        ddp_stream = torch.cuda.Stream()
+        ddp_stream.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(ddp_stream):   # (graph recipe: DDP must be constructed on a side stream)
+            net = nn.parallel.DistributedDataParallel(model, device_ids=[dev.index])
+        torch.cuda.current_stream().wait_stream(ddp_stream)
+    else:
+        net = model
     opt = torch.optim.AdamW(model.parameters(), lr=3e-4, weight_decay=0.1, eps=1e-8, fused=True, capturable=use_graph)
     T = 512
     g = torch.Generator(device=dev).manual_seed(rank)
@@ -105,17 +117,25 @@ def main():
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
-            for _ in range(3):
+            for _ in range(11 if world > 1 else 3):
                 opt.zero_grad(set_to_none=True)
                 body()
         torch.cuda.current_stream().wait_stream(side)
         opt.zero_grad(set_to_none=True)
-        graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(graph):
-            static_loss = body()
-        for _ in range(3):
-            step()
-        torch.cuda.synchronize()
+        try:
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                static_loss = body()
+            for _ in range(3):
+                step()
+            torch.cuda.synchronize()
+        except Exception as e:   # report the eager number rather than nothing
+            graph, static_loss = None, None
+            if rank == 0:
+                print(f"[torch_baseline] CUDA-graph capture failed ({type(e).__name__}: {str(e)[:200]}); timing eager launches",
+                      file=sys.stderr, flush=True)
+            torch.cuda.synchronize()
+            opt.zero_grad(set_to_none=True)
     if world > 1:
         dist.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
