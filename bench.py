@@ -100,7 +100,7 @@ def run_arm(args, arm: str) -> dict:
         raise ValueError(f"global batch {global_batch} is not divisible by {dp} data-parallel ranks")
     mesh = build_mesh(dp, tp, pp)
     if strategy == "pp":
-        layers = stage_layers(mc.n_layers, pp, False)[mesh.pp.rank]
+        layers = stage_layers(mc.n_layers, pp, False, 3.5 if args.pp_balanced else 0.0)[mesh.pp.rank]
         local = LocalShape(mc, layer_start=layers.start, layer_end=layers.stop, has_embed=mesh.pp.rank == 0,
                            has_head=mesh.pp.rank == pp - 1)
         M = tc.pp_microbatches
@@ -210,6 +210,8 @@ def run_arm(args, arm: str) -> dict:
     if strategy == "pp":
         res["config"]["pp_microbatches"] = tc.pp_microbatches
         res["config"]["pp_schedule"] = tc.pp_schedule
+        res["config"]["pp_layers_per_stage"] = [len(r) for r in stage_layers(mc.n_layers, pp, False,
+                                                                             3.5 if args.pp_balanced else 0.0)]
         res["config"]["bubble_fraction"] = bubble_fraction(pp, tc.pp_microbatches)
     # release the arm: graphs first (they reference NCCL work), then the engine / symmetric buffers
     del train_step, state, opt, eng, dev_batches, pinned
@@ -263,6 +265,8 @@ def main() -> int:
     ap.add_argument("--arm-timeout", type=float, default=240.0, help="seconds per arm before the watchdog gives up")
     ap.add_argument("--pp-microbatches", type=int, default=2)
     ap.add_argument("--pp-schedule", default="gpipe")
+    ap.add_argument("--pp-balanced", action="store_true", help="PP: fewer layers on the last stage (it also runs lm_head + "
+                    "CE); default: the reference's equal layer counts")
     ap.add_argument("--model-config", default="configs/model_config.yaml")
     ap.add_argument("--backend", default="auto")
     ap.add_argument("--no-fused-comm", action="store_true")

@@ -67,6 +67,8 @@ class TrainConfig:
     pp_schedule: str = "gpipe"        # "gpipe" (reference schedule) | "1f1b"
     pp_clip: str = "stage"            # "stage" = per-stage local norm (reference quirk Q3) | "global"
     pp_grad_scale_by_stages: bool = True   # reference quirk Q4: psum inside the differentiated fn scales grads by S
+    pp_layer_split: str = "even"      # "even" (reference: same number of layers per stage) | "balanced" (fewer layers on the last stage, which also runs lm_head + cross-entropy)
+    pp_head_cost: float = 3.5         # cost of final LayerNorm + lm_head + CE in transformer-layer units (pp_layer_split: balanced)
     pp_reference_truncate: bool = False    # reference quirk Q2: n_layers // n_stages layers per stage, rest dropped
     pp_init: str = "reference"        # "reference" = per-stage keys (Q6) | "shared" = same weights as DP/TP
     synthetic_data: bool = True       # offline token stream (no HF hub access on the box)

@@ -935,6 +935,177 @@ gemm_grouped_wgrad_kernel(const __grid_constant__ GemmGroup grp, int K, int spli
 }
 
 // =========================================================================================================
+// Grouped weight gradients on CTA pairs: the same problem list as gemm_grouped_wgrad_kernel, but every work item is a
+// 256 x 256 output tile computed by two CTAs (tcgen05.mma.cta_group::2, UMMA M = 256) and a K slice (split-K).  Per
+// k-block a CTA loads 128 x 64 of Xᵀ and 128 x 64 of dY (32 KB) for 2 x 128 x 256 x 64 FLOP — twice the arithmetic
+// intensity of the 128 x 128 tiles, which is what the 48 B/clk L2 -> SM port of an SM asks for (the 1-CTA grouped kernel
+// runs two CTAs per SM that share that port: 39 us per layer, profiles/r2/step_budget_ncu.md).  Both operands are
+// MN-major (X is [K, M_p], dY is [K, N_p] row-major); fp32 reduce-add epilogue straight from registers; six 32 KB stages.
+// =========================================================================================================
+template <int BN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(PG_THREADS, 1)
+gemm_grouped_wgrad_2cta_kernel(const __grid_constant__ GemmGroup grp, int K, int splits, int kb_per_split, int num_stages,
+                               float alpha) {
+  constexpr int A_BYTES = BM * BK * 2, B_BYTES = (BN / 2) * BK * 2, STAGE_BYTES = A_BYTES + B_BYTES;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + num_stages * STAGE_BYTES);
+  uint64_t* full_bar = bars;                       // [PG_STAGE_MAX]  (leader's copy counts both CTAs' bytes)
+  uint64_t* empty_bar = bars + PG_STAGE_MAX;       // [PG_STAGE_MAX]
+  uint64_t* tmem_full = bars + 2 * PG_STAGE_MAX;   // [2]
+  uint64_t* tmem_empty = tmem_full + 2;            // [2]  (leader's copy: 16 arrivals)
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t cta = cluster_ctarank();
+  const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+  const int total_kb = (K + BK - 1) / BK;
+  const int tiles_mn = grp.tile_start[grp.count];
+  const int total_tiles = tiles_mn * splits;
+
+  if (warp == 0 && lane == 0) {
+    for (int p = 0; p < grp.count; ++p) {
+      tma_prefetch_desc(&grp.a[p]);
+      tma_prefetch_desc(&grp.b[p]);
+    }
+    for (int s = 0; s < num_stages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&tmem_full[b], 1);
+      mbar_init(&tmem_empty[b], 16);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc_2sm(tmem_ptr_smem, 2 * BN);
+    tmem_relinquish_2sm();
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+  pdl_launch_dependents();
+  pdl_wait();
+
+  if (warp == 0) {
+    // ------------------------------ TMA producer (both CTAs) ------------------------------
+    if (elect_one()) {
+      uint32_t kit = 0;
+      for (int tile = pair; tile < total_tiles; tile += num_pairs) {
+        const int split = tile / tiles_mn;
+        int p, m_blk, n_blk;
+        group_decode(grp, tile % tiles_mn, p, m_blk, n_blk);
+        const CUtensorMap* ta = &grp.a[p];
+        const CUtensorMap* tb = &grp.b[p];
+        const int row0 = m_blk * 256 + (int)cta * BM;        // this CTA's 128 rows of the output (columns of X)
+        const int bcol0 = n_blk * BN + (int)cta * (BN / 2);  // this CTA's half of the dY columns
+        const int kb_begin = split * kb_per_split;
+        const int nkb = min(total_kb, kb_begin + kb_per_split) - kb_begin;
+        for (int i = 0; i < nkb; ++i, ++kit) {
+          const int s = kit % num_stages;
+          const uint32_t ph = (kit / num_stages) & 1;
+          mbar_wait(&empty_bar[s], ph ^ 1);
+          uint8_t* sa = smem + s * STAGE_BYTES;
+          uint8_t* sb = sa + A_BYTES;
+          const uint32_t full_leader = mapa_shared(smem_u32(&full_bar[s]), 0);
+          if (cta == 0) mbar_expect_tx(&full_bar[s], 2 * STAGE_BYTES);
+          const int k0 = (kb_begin + i) * BK;
+#pragma unroll
+          for (int j = 0; j < BM / 64; ++j) tma_load_2d_2sm(sa + j * (BK * 128), ta, full_leader, row0 + j * 64, k0);
+#pragma unroll
+          for (int j = 0; j < BN / 128; ++j) tma_load_2d_2sm(sb + j * (BK * 128), tb, full_leader, bcol0 + j * 64, k0);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------ MMA issuer (leader CTA only) ------------------------------
+    if (cta == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(256, BN, 1, 1);
+      uint32_t kit = 0;
+      int it = 0;
+      for (int tile = pair; tile < total_tiles; tile += num_pairs, ++it) {
+        const int split = tile / tiles_mn;
+        const int kb_begin = split * kb_per_split;
+        const int nkb = min(total_kb, kb_begin + kb_per_split) - kb_begin;
+        const int buf = it & 1;
+        mbar_wait(&tmem_empty[buf], ((it >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + buf * BN;
+        for (int i = 0; i < nkb; ++i, ++kit) {
+          const int s = kit % num_stages;
+          const uint32_t ph = (kit / num_stages) & 1;
+          mbar_wait(&full_bar[s], ph);
+          tc_fence_after();
+          if (elect_one()) {
+            const uint32_t sa = smem_u32(smem + s * STAGE_BYTES);
+            const uint32_t sb = sa + A_BYTES;
+#pragma unroll
+            for (int k = 0; k < BK / 16; ++k) {
+              const uint64_t da = make_smem_desc(sa + k * 2048, BK * 128, 1024, SWZ_128B);
+              const uint64_t db = make_smem_desc(sb + k * 2048, BK * 128, 1024, SWZ_128B);
+              umma_bf16_2sm(tmem_d, da, db, idesc, (i > 0 || k > 0) ? 1u : 0u);
+            }
+            umma_commit_2sm(&empty_bar[s], 0x3);
+            if (i == nkb - 1) umma_commit_2sm(&tmem_full[buf], 0x3);
+          }
+          __syncwarp();
+        }
+      }
+    }
+  } else {
+    // ------------------------------ epilogue (warps 2..9 of both CTAs): fp32 reduce-add ------------------------------
+    const int q = warp & 3;
+    const int g = (warp - 2) >> 2;      // column half of the tile
+    const int row = q * 32 + lane;
+    const int gcol = g * (BN / 2);
+    int it = 0;
+    for (int tile = pair; tile < total_tiles; tile += num_pairs, ++it) {
+      int p, m_blk, n_blk;
+      group_decode(grp, tile % tiles_mn, p, m_blk, n_blk);
+      const int buf = it & 1;
+      const long long gm = (long long)m_blk * 256 + (int)cta * BM + row;
+      const bool row_ok = gm < grp.M[p];
+      const int Np = grp.N[p];
+      float* obase = grp.out[p] + gm * grp.ldo[p];
+      mbar_wait(&tmem_full[buf], (it >> 1) & 1);
+      tc_fence_after();
+      const uint32_t tmem_d = tmem_base + buf * BN + ((uint32_t)(q * 32) << 16) + gcol;
+#pragma unroll 1
+      for (int c = 0; c < BN / 64; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(tmem_d + c * 32, r);
+        tmem_ld_wait();
+        if (c == BN / 64 - 1) {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(mapa_shared(smem_u32(&tmem_empty[buf]), 0));
+        }
+        const int n0 = n_blk * BN + gcol + c * 32;
+#pragma unroll
+        for (int c4 = 0; c4 < 8; ++c4) {
+          const int n = n0 + c4 * 4;
+          if (row_ok && n < Np)
+            red_add_v4_f32(obase + n, __uint_as_float(r[c4 * 4]) * alpha, __uint_as_float(r[c4 * 4 + 1]) * alpha,
+                           __uint_as_float(r[c4 * 4 + 2]) * alpha, __uint_as_float(r[c4 * 4 + 3]) * alpha);
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc_2sm(tmem_base, 2 * BN);
+  }
+}
+
+// =========================================================================================================
 // CTA-pair variant (cta_group::2): two CTAs on the two SMs of a TPC share one 256 x BN output tile.
 // Each CTA TMA-loads its own 128 rows of A and HALF of the B tile; the leader CTA's elected thread issues
 // tcgen05.mma.cta_group::2 (UMMA M = 256), which reads both CTAs' shared memory and writes 128 accumulator rows
@@ -1600,6 +1771,60 @@ extern "C" int dtc_gemm_wgrad_grouped(int count, const unsigned long long* A, co
   const int max_ctas = 2 * num_sms();
   const int grid = total_tiles < max_ctas ? total_tiles : max_ctas;
   DTC_CHECK_CUDA(dtc::launch(kern, grid, PG_THREADS, smem_of(stages), stream, grp, K, splits, kb_per_split, stages, alpha));
+  DTC_CHECK_LAUNCH();
+  return 0;
+}
+
+// Same contract as dtc_gemm_wgrad_grouped, computed by CTA pairs on 256 x 256 tiles (gemm_grouped_wgrad_2cta_kernel).
+// `splits` slices the reduction so that (number of 256 x 256 tiles) x splits fills the 74 CTA pairs about twice.
+extern "C" int dtc_gemm_wgrad_grouped_pair(int count, const unsigned long long* A, const long long* lda,
+                                           const unsigned long long* B, const long long* ldb, const int* Ms, const int* Ns,
+                                           int K, const unsigned long long* out, const long long* ldo, float alpha,
+                                           int splits, int stages, cudaStream_t stream) {
+  DTC_CHECK_ARG(count >= 1 && count <= GG_MAX && K > 0, "wgrad_grouped_pair: count=%d (1..%d), K=%d", count, GG_MAX, K);
+  constexpr int BN = 256;
+  GemmGroup grp;
+  memset(&grp, 0, sizeof(grp));
+  grp.count = count;
+  int tiles = 0;
+  for (int p = 0; p < count; ++p) {
+    DTC_CHECK_ARG(Ms[p] > 0 && Ns[p] > 0 && Ms[p] % 8 == 0 && Ns[p] % 8 == 0 && lda[p] % 8 == 0 && ldb[p] % 8 == 0 &&
+                      ldo[p] % 4 == 0,
+                  "wgrad_grouped_pair: problem %d: M=%d N=%d lda=%lld ldb=%lld ldo=%lld", p, Ms[p], Ns[p], lda[p], ldb[p],
+                  ldo[p]);
+    DTC_CHECK_ARG((A[p] & 15) == 0 && (B[p] & 15) == 0 && (out[p] & 15) == 0 && A[p] && B[p] && out[p],
+                  "wgrad_grouped_pair: problem %d: pointers must be non-null and 16-byte aligned", p);
+    int rc;
+    if ((rc = make_tmap_2d_bf16(&grp.a[p], reinterpret_cast<const void*>(A[p]), K, Ms[p], lda[p], BK, 64,
+                                CU_TENSOR_MAP_SWIZZLE_128B)))
+      return rc;
+    if ((rc = make_tmap_2d_bf16(&grp.b[p], reinterpret_cast<const void*>(B[p]), K, Ns[p], ldb[p], BK, 64,
+                                CU_TENSOR_MAP_SWIZZLE_128B)))
+      return rc;
+    grp.out[p] = reinterpret_cast<float*>(out[p]);
+    grp.ldo[p] = ldo[p];
+    grp.M[p] = Ms[p];
+    grp.N[p] = Ns[p];
+    grp.m_blocks[p] = (Ms[p] + 255) / 256;
+    grp.tile_start[p] = tiles;
+    tiles += grp.m_blocks[p] * ((Ns[p] + BN - 1) / BN);
+  }
+  for (int p = count; p <= GG_MAX; ++p) grp.tile_start[p] = tiles;
+  const int total_kb = (K + BK - 1) / BK;
+  if (splits < 1) splits = 1;
+  if (splits > total_kb) splits = total_kb;
+  const int kb_per_split = (total_kb + splits - 1) / splits;
+  splits = (total_kb + kb_per_split - 1) / kb_per_split;
+  if (stages < 2 || stages > PG_STAGE_MAX) stages = PG_STAGE_MAX;
+  auto smem_of = [](int st) { return st * (BM * BK * 2 + (BN / 2) * BK * 2) + 1024 + 512; };
+  while (stages > 2 && smem_of(stages) > 227 * 1024) --stages;
+  auto kern = gemm_grouped_wgrad_2cta_kernel<BN>;
+  static dtc::SmemOptIn configured;  // per device
+  DTC_CHECK_CUDA(dtc::ensure_dyn_smem(kern, 227 * 1024, configured));
+  const int total_tiles = tiles * splits;
+  const int max_pairs = num_sms() / 2;
+  const int pairs = total_tiles < max_pairs ? total_tiles : max_pairs;
+  DTC_CHECK_CUDA(dtc::launch(kern, 2 * pairs, PG_THREADS, smem_of(stages), stream, grp, K, splits, kb_per_split, stages, alpha));
   DTC_CHECK_LAUNCH();
   return 0;
 }

@@ -263,9 +263,10 @@ def wgrad_group_args(xs, dys, outs) -> GroupArgs:
     return args
 
 
-def wgrad_grouped(args: GroupArgs, alpha: float = 1.0, splits: int = 1, stages: int = 0) -> None:
-    """The weight gradients of one layer (<= 4 GEMMs sharing K = tokens) as ONE persistent tcgen05 launch."""
-    native.call("dtc_gemm_wgrad_grouped", args.count, args.a, args.lda, args.b, args.ldb, args.m, args.n, args.K, args.out,
+def wgrad_grouped(args: GroupArgs, alpha: float = 1.0, splits: int = 1, stages: int = 0, pair: bool = False) -> None:
+    """The weight gradients of one layer (<= 4 GEMMs sharing K = tokens) as ONE persistent tcgen05 launch.
+    ``pair``: 256 x 256 tiles on CTA pairs (cta_group::2) instead of 128 x 128 tiles on single CTAs."""
+    native.call("dtc_gemm_wgrad_grouped_pair" if pair else "dtc_gemm_wgrad_grouped", args.count, args.a, args.lda, args.b, args.ldb, args.m, args.n, args.K, args.out,
                 args.ldo, float(alpha), splits, stages)
 
 

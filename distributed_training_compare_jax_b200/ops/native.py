@@ -48,6 +48,7 @@ _PROTOS: dict[str, list[Any]] = {
     "dtc_sum_slots_f32": [P, L, I, P, L, I],
     "dtc_gemm_bf16_scatter": [P, L, P, L, I, I, I, I, P, I, I, L, I, I],
     "dtc_gemm_wgrad_grouped": [I, P, P, P, P, P, P, I, P, P, F, I, I],
+    "dtc_gemm_wgrad_grouped_pair": [I, P, P, P, P, P, P, I, P, P, F, I, I],
     "dtc_colsum_grouped": [I, P, P, P, P, P],
     "dtc_sp_ln_fwd": [P, P, P, I, P, P, P, P, P, U64, P, I, L, I, I, F],
     "dtc_sp_ln_bwd": [P, I, P, P, P, P, P, P, P, U64, P, I, L, I, I],

@@ -32,13 +32,30 @@ class Action:
     mb: int
 
 
-def stage_layers(n_layers: int, n_stages: int, reference_truncate: bool = False) -> list[range]:
+def stage_layers(n_layers: int, n_stages: int, reference_truncate: bool = False, head_cost: float = 0.0) -> list[range]:
     """Contiguous layer ranges per stage.  ``reference_truncate`` reproduces the reference's
     ``layers_per_stage = n_layers // n_stages`` (train/train.py:118), which silently drops the remainder
-    (12 layers on 8 stages → an 8-layer model, quirk Q2); the default spreads all layers (e.g. 2,2,2,2,1,1,1,1)."""
+    (12 layers on 8 stages → an 8-layer model, quirk Q2); the default spreads all layers (e.g. 2,2,2,2,1,1,1,1).
+    ``head_cost`` > 0 (``pp_layer_split: balanced``): the last stage also runs LayerNorm + lm_head + cross-entropy, which
+    cost about ``head_cost`` transformer layers (3.5 for the reference model: 0.95 ms against 0.27 ms per layer); layers are
+    then assigned so that the stage COSTS are as equal as contiguous ranges allow."""
     if reference_truncate:
         per = n_layers // n_stages
         return [range(s * per, (s + 1) * per) for s in range(n_stages)]
+    if head_cost > 0 and n_stages > 1:
+        total = n_layers + head_cost
+        counts, used = [], 0
+        for s in range(n_stages - 1):
+            cum = int(round((s + 1) * total / n_stages))            # layers that should lie at or before this boundary
+            n = max(1, min(cum - used, n_layers - used - (n_stages - 1 - s)))   # >= 1 here, >= 1 left for every later stage
+            counts.append(n)
+            used += n
+        counts.append(n_layers - used)
+        out, start = [], 0
+        for n in counts:
+            out.append(range(start, start + n))
+            start += n
+        return out
     base, extra = divmod(n_layers, n_stages)
     out, start = [], 0
     for s in range(n_stages):

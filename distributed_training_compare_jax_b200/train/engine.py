@@ -106,6 +106,7 @@ class NativeStageEngine(StageEngineBase):
         lo = self.local
         self.wgrad_grouped = bool(wgrad_grouped and self.cfg.d_model % 64 == 0 and lo.ff_local % 64 == 0
                                   and (3 * lo.d_local) % 64 == 0 and lo.d_local % 8 == 0)
+        self.wgrad_pair = __import__('os').environ.get('DTC_WGRAD_PAIR', '1') != '0'   # CTA-pair grouped wgrad kernel
         self.side = None  # side stream of the workspace currently being processed (set in forward / backward)
         self._forked: set[int] = set()  # side streams that carry work not yet joined into the main stream
         if self.device.type != "cuda":
@@ -258,16 +259,21 @@ def _grouped_backward_impl(self, ws, top: torch.Tensor) -> torch.Tensor:
             ws.group_args[key] = (Fn.colsum_group_args(dys, [g["b2"][l], g["b1"][l], g["bo"][l], g["bqkv"][l]]),
                                   Fn.wgrad_group_args(xs, dys, [g["w2"][l], g["w1"][l], g["wo"][l], g["wqkv"][l]]))
             tiles = sum(-(-x.shape[1] // 128) * -(-d.shape[1] // 128) for x, d in zip(xs, dys))
+            ws.group_tiles256 = sum(-(-x.shape[1] // 256) * -(-d.shape[1] // 256) for x, d in zip(xs, dys))
         cs_args, wg_args = ws.group_args[key]
         splits = getattr(ws, "group_splits", None)
-        if splits is None:   # fill 2 CTAs per SM when the layer is small (tensor-parallel shards)
-            splits = ws.group_splits = max(1, min(8, 296 // max(tiles, 1)))
+        if splits is None:
+            if self.wgrad_pair:   # 256 x 256 tiles on the 74 CTA pairs: slice the token reduction until they are busy ~twice
+                kb = max(1, self.micro_batch * self.seq_len // 64)
+                splits = ws.group_splits = max(1, min(8, kb // 8, 74 // max(ws.group_tiles256, 1)))
+            else:                 # fill 2 CTAs per SM when the layer is small (tensor-parallel shards)
+                splits = ws.group_splits = max(1, min(8, 296 // max(tiles, 1)))
         side = self.side if self.side is not None else main
         if side is not main:
             side.wait_stream(main)
         with torch.cuda.stream(side):
             Fn.colsum_grouped(cs_args)
-            Fn.wgrad_grouped(wg_args, splits=splits)
+            Fn.wgrad_grouped(wg_args, splits=splits, pair=self.wgrad_pair)
             ev = torch.cuda.Event()
             ev.record(side)
         events[l] = ev

@@ -49,9 +49,9 @@ def build_state(train_config: TrainConfig, model_config: ModelConfig, opt_config
                        symm_group=mesh.dp.group if fused_dp else None)
     init_params(store, train_config.seed, pp_stage_keys=pp_stage_keys, stage_index=mesh.pp.rank)
     engine = None
-    # (hybrid DP×TP keeps the replicated-activation TP path until the combination has run on hardware: DTC_SP_HYBRID=1)
+    # (hybrid DP×TP uses it too — validated on 4 and 8 GPUs, profiles/r2; DTC_SP_HYBRID=0 selects GEMM + NCCL all-reduce)
     if (backend == "native" and train_config.tp_seq_parallel and mesh.tp.size > 1 and mesh.pp.size == 1 and n_micro == 1
-            and train_config.fused_comm and (mesh.dp.size == 1 or os.environ.get("DTC_SP_HYBRID") == "1")):
+            and train_config.fused_comm and (mesh.dp.size == 1 or os.environ.get("DTC_SP_HYBRID", "1") != "0")):
         from ..parallel.tp_sp import SeqParallelEngine
         try:   # the conditions checked inside are the same on every rank, so all ranks fall back together
             engine = SeqParallelEngine(model_config, local, mesh, store, micro_batch, model_config.max_seq_len, n_micro,
@@ -181,7 +181,8 @@ def train_pp(train_config: TrainConfig, model_config: ModelConfig, opt_config: O
     validate(model_config, train_config, num_devices)
     mesh = mesh or build_mesh(1, 1, num_devices)
     S, stage = num_devices, mesh.pp.rank
-    layers = stage_layers(model_config.n_layers, S, train_config.pp_reference_truncate)[stage]
+    head_cost = train_config.pp_head_cost if train_config.pp_layer_split == "balanced" else 0.0
+    layers = stage_layers(model_config.n_layers, S, train_config.pp_reference_truncate, head_cost)[stage]
     local = LocalShape(model_config, layer_start=layers.start, layer_end=layers.stop, has_embed=(stage == 0),
                        has_head=(stage == S - 1))
     M = train_config.pp_microbatches

@@ -161,6 +161,10 @@ int dtc_sp_ln_bwd(const void* part, int n_part, const void* x, const float* mean
 int dtc_gemm_wgrad_grouped(int count, const unsigned long long* A, const long long* lda, const unsigned long long* B,
                            const long long* ldb, const int* Ms, const int* Ns, int K, const unsigned long long* out,
                            const long long* ldo, float alpha, int splits, int stages, cudaStream_t stream);
+/* same contract on CTA pairs (cta_group::2), 256 x 256 output tiles; `splits` slices the token reduction */
+int dtc_gemm_wgrad_grouped_pair(int count, const unsigned long long* A, const long long* lda, const unsigned long long* B,
+                           const long long* ldb, const int* Ms, const int* Ns, int K, const unsigned long long* out,
+                           const long long* ldo, float alpha, int splits, int stages, cudaStream_t stream);
 int dtc_colsum_grouped(int count, const unsigned long long* x, const long long* ld, const int* M, const int* N,
                        const unsigned long long* out, cudaStream_t stream);
 /* folded-barrier variants (experimental, `DTC_SP_FOLD=1`): same operations with the cross-rank synchronisation inside the

@@ -1,9 +1,8 @@
-"""Kernels and engine modes written after the round's GPU budget was spent: they compile for sm_100a and are wired behind
-opt-in switches, but have NOT run on a B200 yet.  They are skipped unless ``DTC_EXPERIMENTAL=1`` so that the default GPU
-suite only contains validated paths; running this file is the first item of the next round.
+"""Grouped per-layer gradient kernels (validated on B200 in round 2; the grouped backward is the engine's default):
 
-  * ``dtc_gemm_wgrad_grouped`` / ``dtc_colsum_grouped`` — the four weight / bias gradients of a layer as one launch each
-  * ``NativeStageEngine(wgrad_grouped=True)`` (``DTC_WGRAD_GROUPED=1``) — backward pass that uses them
+  * ``dtc_gemm_wgrad_grouped`` / ``dtc_gemm_wgrad_grouped_pair`` / ``dtc_colsum_grouped`` — the four weight / bias gradients
+    of a layer as one launch each (128 x 128 tiles on single CTAs, or 256 x 256 tiles on CTA pairs)
+  * ``NativeStageEngine(wgrad_grouped=True)`` against the per-GEMM backward (``wgrad_grouped=False``)
 """
 import os
 
@@ -12,8 +11,7 @@ import torch
 
 from distributed_training_compare_jax_b200.ops import functional as Fn
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get("DTC_EXPERIMENTAL") != "1", reason="unvalidated: set DTC_EXPERIMENTAL=1")]
+pytestmark = pytest.mark.gpu
 BF16, F32 = torch.bfloat16, torch.float32
 
 
@@ -26,15 +24,16 @@ def randn(*shape, scale=1.0):
     return (torch.randn(*shape, device="cuda") * scale).to(BF16)
 
 
+@pytest.mark.parametrize("pair", [False, True])
 @pytest.mark.parametrize("splits", [1, 3])
 @pytest.mark.parametrize("K,shapes", [(4096, [(2048, 512), (512, 2048), (512, 512), (512, 1536)]),
                                       (512, [(256, 768), (200, 264)]), (1000, [(128, 128)])])
-def test_wgrad_grouped_matches_fp32_reference(K, shapes, splits):
+def test_wgrad_grouped_matches_fp32_reference(K, shapes, splits, pair):
     torch.manual_seed(7)
     xs = [randn(K, m) for m, _ in shapes]
     dys = [randn(K, n, scale=K ** -0.5) for _, n in shapes]
     outs = [torch.full((m, n), 0.25, device="cuda", dtype=F32) for m, n in shapes]     # accumulated into
-    Fn.wgrad_grouped(Fn.wgrad_group_args(xs, dys, outs), splits=splits)
+    Fn.wgrad_grouped(Fn.wgrad_group_args(xs, dys, outs), splits=splits, pair=pair)
     torch.cuda.synchronize()
     for x, dy, o in zip(xs, dys, outs):
         want = x.float().t() @ dy.float() + 0.25

@@ -68,7 +68,8 @@ def test_pp2_native(single, tmp_path, schedule):
 
 @pytest.mark.skipif(NGPU < 4, reason="needs >= 4 GPUs")
 def test_dp2_tp2_native(single, tmp_path):
-    loss = _run(tmp_path, "dptp", "dp_tp", 4, dp_size=2, tp_size=2)
+    # replicated-activation TP inside the hybrid mesh (GEMM + NCCL all-reduce)
+    loss = _run(tmp_path, "dptp", "dp_tp", 4, dp_size=2, tp_size=2, tp_seq_parallel=False)
     np.testing.assert_allclose(loss, single, rtol=5e-3, atol=5e-3)
 
 
@@ -129,11 +130,11 @@ def test_pp8_native(tmp_path):
     np.testing.assert_allclose(loss, ref, rtol=5e-3, atol=5e-3)
 
 
-@pytest.mark.skipif(NGPU < 4 or os.environ.get("DTC_EXPERIMENTAL") != "1",
-                    reason="needs >= 4 GPUs; unvalidated: set DTC_EXPERIMENTAL=1")
-def test_dp2_tp2_sequence_parallel_native(single, tmp_path, monkeypatch):
-    monkeypatch.setenv("DTC_SP_HYBRID", "1")   # hybrid DP×TP uses the sequence-parallel engine only on request for now
+@pytest.mark.skipif(NGPU < 4, reason="needs >= 4 GPUs")
+def test_dp2_tp2_sequence_parallel_native(single, tmp_path):
+    """Hybrid DP x TP on the sequence-parallel engine (the default for dp_tp; BASELINE config 5 at small scale)."""
     loss = _run(tmp_path, "dptp_sp", "dp_tp", 4, dp_size=2, tp_size=2, tp_seq_parallel=True)
+    assert _run.last_metrics["tp_seq_parallel"] is True
     np.testing.assert_allclose(loss, single, rtol=5e-3, atol=5e-3)
 
 

@@ -144,3 +144,17 @@ def test_per_action_cuda_graphs_are_only_used_with_the_native_engine():
         [t.join(30) for t in ts]
     assert all(not e.graphs and e.steps_run == 4 for e in execs)
     assert torch.equal(engines[1].final[0], torch.full((2,), 2.0))
+
+
+def test_balanced_layer_split_moves_layers_off_the_head_stage():
+    """pp_layer_split: balanced — the last stage also runs lm_head + CE (~3.5 layers of work for the reference model)."""
+    from distributed_training_compare_jax_b200.parallel.pp import stage_layers
+    assert [len(r) for r in stage_layers(12, 2)] == [6, 6]                      # reference: equal layer counts
+    assert [len(r) for r in stage_layers(12, 2, False, 3.5)] == [8, 4]          # 8 vs 4 + 3.5
+    for S in (2, 3, 4, 8, 12):
+        rs = stage_layers(12, S, False, 3.5)
+        assert sum(len(r) for r in rs) == 12 and all(len(r) >= 1 for r in rs)
+        assert [r.start for r in rs] == [sum(len(q) for q in rs[:i]) for i in range(S)]   # contiguous, in order
+        even = stage_layers(12, S)
+        cost = lambda split: max(len(r) + (3.5 if i == S - 1 else 0) for i, r in enumerate(split))
+        assert cost(rs) <= cost(even)

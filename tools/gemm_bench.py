@@ -111,5 +111,39 @@ def main():
     native.load().dtc_gemm_set_impl(0)
 
 
-if __name__ == "__main__":
+if __name__ == "__main__" and "--grouped" not in sys.argv:
     main()
+
+
+def bench_grouped():
+    """The four weight gradients of one layer as ONE launch: 1-CTA 128x128 tiles vs CTA-pair 256x256 tiles (+ split-K)."""
+    K, D, F = 4096, 512, 2048
+    n = 6
+    sets = []
+    for _ in range(n):
+        xs = [torch.randn(K, m, device="cuda").to(torch.bfloat16) for m in (F, D, D, D)]
+        dys = [(torch.randn(K, c, device="cuda") * 0.02).to(torch.bfloat16) for c in (D, F, D, 3 * D)]
+        outs = [torch.zeros(x.shape[1], d.shape[1], device="cuda") for x, d in zip(xs, dys)]
+        sets.append((Fn.wgrad_group_args(xs, dys, outs), xs, dys, outs))
+    flops = 2.0 * K * (F * D + D * F + D * D + D * 3 * D)
+    for pair, splits in ((False, 1), (False, 2), (True, 1), (True, 2), (True, 3), (True, 4)):
+        for s in sets[:2]:
+            Fn.wgrad_grouped(s[0], splits=splits, pair=pair)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            for s in sets:
+                Fn.wgrad_grouped(s[0], splits=splits, pair=pair)
+        g.replay()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        g.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        us = e0.elapsed_time(e1) * 1e3 / n
+        print(f"grouped wgrad (4 GEMMs of a layer) pair={pair!s:5s} splits={splits}: {us:7.1f} us  {flops / us / 1e6:7.1f} TFLOP/s", flush=True)
+
+
+if "--grouped" in sys.argv:
+    bench_grouped()
