@@ -40,8 +40,8 @@ EXCERPTS = {
     "flash_attn_fwd_pipe_kernel<32>": (
         "Flash attention forward, pipelined: issue warp (TMA + tcgen05.mma) and softmax warps (LDTM, MUFU.EX2)",
         [r"UTCHMMA", r"MUFU\.EX2", r"LDTM"], 3),
-    "flash_attn_bwd_pipe_kernel<32>": (
-        "Flash attention backward, pipelined: S / dP, dV / dK / dQ products on tcgen05, dQ via fp32 red.add",
+    "flash_attn_bwd_persist_kernel<32, 4>": (
+        "Flash attention backward, persistent + pipelined: S / dP, dV / dK / dQ products on tcgen05, dQ via fp32 red.add",
         [r"UTCHMMA", r"REDG", r"LDTM"], 3),
     "symm_barrier_kernel": ("Cross-rank flag barrier (signal pads in symmetric memory)", [r"SYS"], 6),
 }
