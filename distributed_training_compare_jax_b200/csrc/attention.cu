@@ -194,13 +194,16 @@ flash_attn_fwd_pipe_kernel(const __grid_constant__ CUtensorMap tm_q, const __gri
         for (int i = 0; i < 64; ++i)
           if (i > lim) r[i] = 0xff800000u;  // -inf
       }
-      float mx = __uint_as_float(r[0]);
+      // four independent partial maxima / sums: a single 64-long dependent FMNMX (or FADD) chain costs ~250 cycles of pure
+      // latency per block, which the two warps per scheduler cannot hide
+      float mx4[4] = {__uint_as_float(r[0]), __uint_as_float(r[1]), __uint_as_float(r[2]), __uint_as_float(r[3])};
 #pragma unroll
-      for (int i = 1; i < 64; ++i) mx = fmaxf(mx, __uint_as_float(r[i]));
+      for (int i = 4; i < 64; ++i) mx4[i & 3] = fmaxf(mx4[i & 3], __uint_as_float(r[i]));
+      const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
       // m_run is finite from block 0 on (key 0 is visible to every query); a fully masked block leaves it unchanged
       const float m_new = fmaxf(m_run, mx * scale_log2);
       const float alpha = ex2_ftz(m_run - m_new);
-      float l_blk = 0.f;
+      float l4[4] = {0.f, 0.f, 0.f, 0.f};
       uint8_t* prow = sP + st * P64_BYTES;
 #pragma unroll
       for (int g = 0; g < 8; ++g) {
@@ -208,12 +211,12 @@ flash_attn_fwd_pipe_kernel(const __grid_constant__ CUtensorMap tm_q, const __gri
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           p[i] = ex2_ftz(fmaf(__uint_as_float(r[g * 8 + i]), scale_log2, -m_new));
-          l_blk += p[i];
+          l4[i & 3] += p[i];
         }
         *reinterpret_cast<uint4*>(prow + swizzle_offset<3>(tid * 128 + g * 16)) =
             make_uint4(pack_bf16x2(p[0], p[1]), pack_bf16x2(p[2], p[3]), pack_bf16x2(p[4], p[5]), pack_bf16x2(p[6], p[7]));
       }
-      l_run = l_run * alpha + l_blk;
+      l_run = l_run * alpha + ((l4[0] + l4[1]) + (l4[2] + l4[3]));
       m_run = m_new;
       // fold the product of the PREVIOUS block (its MMA was issued a whole softmax ago) before P_j is published:
       // bar_p also tells the issue warp that PV[(j-1)&1] may be overwritten by block j+1

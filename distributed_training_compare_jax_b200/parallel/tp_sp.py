@@ -76,7 +76,7 @@ class SeqParallelState:
         self.part = full[2 * L + 4]                            # viewed by the kernels as [n, Ms, D]
         self.barrier_flags = FlagBarrier(dev, tp.group) if n > 1 else None
         if self.barrier_flags is not None:
-            self.barrier_flags.step_counter = engine.store.step
+            self.barrier_flags.step_counter = engine.store.step   # (jitter stress test: a device int that changes per step)
         self._slot = 0
         self._ptr_cache: dict[int, tuple] = {}
         # ---- local: owned rows of the residual stream and the LayerNorm statistics
@@ -93,10 +93,10 @@ class SeqParallelState:
         self.part_ptrs = self._peer_array(self.part)
         # small fp32 exchanges (cross-entropy statistics, partial gradients of replicated leaves): one slot per rank on
         # every rank, filled by dtc_symm_push_f32 — no NCCL call is left inside the step graph
-        st = engine.store
-        self.pg_off, self.pg_n = st.offsets["ln1_g"][0], st.rep_numel - st.offsets["ln1_g"][0]
         self.ce_n = M * 3
         if n > 1:
+            st = engine.store
+            self.pg_off, self.pg_n = st.offsets["ln1_g"][0], st.rep_numel - st.offsets["ln1_g"][0]
             self.small = SymmBuffer(n * (self.ce_n + self.pg_n), F32, dev, tp.group)
             self.ce_slots = self.small.tensor[:n * self.ce_n].view(n, M, 3)
             self.pg_slots = self.small.tensor[n * self.ce_n:]
