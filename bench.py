@@ -84,6 +84,9 @@ def run_arm(args, arm: str) -> dict:
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     strategy = ARM_STRATEGY[arm]
+    fault = os.environ.get("DTC_BENCH_FAULT", "")   # test hook "<arm>:<rank>": that rank raises at the start of that arm
+    if fault and fault.split(":")[0] == arm and int(fault.split(":")[1]) == int(os.environ.get("RANK", "0")):
+        raise RuntimeError(f"injected fault in arm `{arm}` (DTC_BENCH_FAULT)")
     weak = arm == "dp_weak" or (arm == "dp_tp")          # batch is per data-parallel rank
     tc = TrainConfig(seed=0, parallel=strategy, batch=args.batch, steps=args.steps, log_every=10 ** 9,
                      output_dir="outputs/bench", pp_microbatches=args.pp_microbatches, warmup_steps=args.warmup,

@@ -1531,7 +1531,7 @@ extern "C" int dtc_gemm_set_trace(unsigned long long* buf) {
 }
 
 static int g_gemm_impl = 0;  // 0 = persistent 1-CTA kernel, 1 = one-tile-per-CTA kernel, 2 = CTA-pair 256x128, 3 = CTA-pair, 256x256 where it fits
-// Tuning / A-B switch used by tools/gemm_bench.py.
+// Process-wide default variant of dtc_gemm_bf16 (tools / C callers); the Python layer passes the variant per call (dtc_gemm_bf16_ex).
 extern "C" int dtc_gemm_set_impl(int impl) {
   g_gemm_impl = impl;
   return 0;
@@ -1542,10 +1542,10 @@ extern "C" int dtc_gemm_set_impl(int impl) {
 // B: b_mn_major == 0 -> [N, K] row-major;                             == 1 -> [K, N] row-major.
 // Requirements: all leading dimensions and base pointers 16-byte aligned; N % 8 == 0.
 // block_n: 64 / 128 / 256 (0 = choose); splits > 1 requires epi_mode == EPI_ATOMIC_F32.
-extern "C" int dtc_gemm_bf16(const void* A, long long lda, int a_mn_major, const void* B, long long ldb, int b_mn_major,
+static int gemm_bf16_dispatch(const void* A, long long lda, int a_mn_major, const void* B, long long ldb, int b_mn_major,
                              int M, int N, int K, int epi_mode, float alpha, const void* bias, const void* aux,
                              long long ld_aux, void* out, long long ldo, void* out2, long long ldo2, int splits,
-                             int stages, int block_n, cudaStream_t stream) {
+                             int stages, int block_n, int impl, cudaStream_t stream) {
   DTC_CHECK_ARG(M > 0 && N > 0 && K > 0, "gemm: empty problem M=%d N=%d K=%d", M, N, K);
   DTC_CHECK_ARG(N % 8 == 0, "gemm: N=%d must be a multiple of 8", N);
   DTC_CHECK_ARG(lda % 8 == 0 && ldb % 8 == 0, "gemm: lda=%lld ldb=%lld must be multiples of 8 elements", lda, ldb);
@@ -1579,7 +1579,7 @@ extern "C" int dtc_gemm_bf16(const void* A, long long lda, int a_mn_major, const
       block_n = 64;
   }
   static const bool env_v1 = getenv("DTC_GEMM_V1") != nullptr;  // A/B switch: one-tile-per-CTA kernel
-  const bool use_v1 = env_v1 || g_gemm_impl == 1;
+  const bool use_v1 = env_v1 || impl == 1;
   // CTA-pair kernel: needs >= 256 rows; 256-wide tiles when that still leaves enough pair-tiles to fill the GPU.
   // Default policy (impl 0), from profiles/r2/gemm_microbench.txt (device time, this kernel vs the 1-CTA persistent one):
   //   * big GEMMs (lm_head, >= 1e11 FLOP): always pairs — forward 251 -> 183 us, wgrad 234 -> 188 us;
@@ -1591,13 +1591,13 @@ extern "C" int dtc_gemm_bf16(const void* A, long long lda, int a_mn_major, const
   const bool big = flops >= 1e11 || (flops >= 2e10 && splits > 1);  // (split-K: the lm_head dgrad of a small local batch)
   const bool mid = pair_layers && flops >= 6e9 && !a_mn_major && splits <= 1 &&
                    (epi_mode == EPI_STORE_BF16 || epi_mode == EPI_BIAS_GELU || epi_mode == EPI_BIAS_RESIDUAL);
-  const bool want_2cta = (g_gemm_impl == 2 || g_gemm_impl == 3 || (g_gemm_impl == 0 && (big || mid) && !env_v1)) &&
+  const bool want_2cta = (impl == 2 || impl == 3 || (impl == 0 && (big || mid) && !env_v1)) &&
                          M >= 256 && N >= 128;  // impl 4 forces the 1-CTA persistent kernel
   if (want_2cta) {
     const long long tiles256 = (long long)((M + 255) / 256) * ((N + 255) / 256) * (splits > 1 ? splits : 1);
     // 256-wide pair tiles (half the operand bytes per MMA cycle again) whenever they still fill all 74 CTA pairs;
     // ragged N is fine: TMA zero-fills the loads and clips the stores
-    const bool wide = (block_n_arg == 256) || ((g_gemm_impl == 3 || g_gemm_impl == 0) && block_n_arg == 0 && tiles256 >= 56);  // >= 3/4 of the 74 CTA pairs busy
+    const bool wide = (block_n_arg == 256) || ((impl == 3 || impl == 0) && block_n_arg == 0 && tiles256 >= 56);  // >= 3/4 of the 74 CTA pairs busy
     if (stages == 0) stages = PG_STAGE_MAX;
 #define DTC_2CTA_DISPATCH(AMN, BMN)                                                                               \
   if (wide) return launch_gemm_2cta<AMN, BMN, 256, 4>(A, lda, B, ldb, M, N, K, splits, stages, epi, stream);      \
@@ -1642,6 +1642,25 @@ extern "C" int dtc_gemm_bf16(const void* A, long long lda, int a_mn_major, const
   if (a_mn_major && !b_mn_major) { DTC_GEMM_DISPATCH(true, false) }
   DTC_GEMM_DISPATCH(true, true)
 #undef DTC_GEMM_DISPATCH
+}
+
+extern "C" int dtc_gemm_bf16(const void* A, long long lda, int a_mn_major, const void* B, long long ldb, int b_mn_major,
+                             int M, int N, int K, int epi_mode, float alpha, const void* bias, const void* aux,
+                             long long ld_aux, void* out, long long ldo, void* out2, long long ldo2, int splits,
+                             int stages, int block_n, cudaStream_t stream) {
+  return gemm_bf16_dispatch(A, lda, a_mn_major, B, ldb, b_mn_major, M, N, K, epi_mode, alpha, bias, aux, ld_aux, out, ldo, out2,
+                            ldo2, splits, stages, block_n, g_gemm_impl, stream);
+}
+
+// Same with the kernel variant chosen PER CALL (no process-global state: safe with several host threads / engines that
+// want different policies).  impl: 0 default policy, 1 one-tile-per-CTA, 2 CTA pair 256x128, 3 CTA pair 256x256 where it
+// fits, 4 the 1-CTA persistent kernel.
+extern "C" int dtc_gemm_bf16_ex(const void* A, long long lda, int a_mn_major, const void* B, long long ldb, int b_mn_major,
+                                int M, int N, int K, int epi_mode, float alpha, const void* bias, const void* aux,
+                                long long ld_aux, void* out, long long ldo, void* out2, long long ldo2, int splits,
+                                int stages, int block_n, int impl, cudaStream_t stream) {
+  return gemm_bf16_dispatch(A, lda, a_mn_major, B, ldb, b_mn_major, M, N, K, epi_mode, alpha, bias, aux, ld_aux, out, ldo, out2,
+                            ldo2, splits, stages, block_n, impl, stream);
 }
 
 // Fused GEMM -> reduce-scatter (sequence-parallel tensor parallelism; SURVEY.md §8 row R4, collectives X3/X4/X5/X8).

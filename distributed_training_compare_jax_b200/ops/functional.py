@@ -6,6 +6,8 @@ replay never allocates) and enqueues exactly the kernels named in ``include/dtc_
 """
 from __future__ import annotations
 
+import threading
+
 import torch
 
 from . import native
@@ -16,23 +18,24 @@ F32 = torch.float32
 
 
 class gemm_impl:
-    """Context manager selecting the GEMM kernel variant for the calls issued inside it (host-side dispatch, so it
-    also works while a CUDA graph is being captured): 0 persistent 1-CTA (default policy), 1 one-tile-per-CTA
-    (98 KB smem, 128 TMEM columns: two of them fit on one SM, which lets GEMMs from two streams overlap),
-    2 / 3 CTA-pair kernels."""
-    current = 0
+    """Context manager selecting the GEMM kernel variant for the calls issued inside it by THIS host thread (the variant
+    travels with every call — ``dtc_gemm_bf16_ex`` — so two threads or two engines with different policies do not
+    interfere): 0 default policy, 1 one-tile-per-CTA, 2 / 3 CTA-pair kernels, 4 the 1-CTA persistent kernel."""
+    _tls = threading.local()
 
     def __init__(self, impl: int):
         self.impl, self.prev = impl, 0
 
+    @staticmethod
+    def get() -> int:
+        return getattr(gemm_impl._tls, "current", 0)
+
     def __enter__(self):
-        self.prev = gemm_impl.current
-        gemm_impl.current = self.impl
-        native.load().dtc_gemm_set_impl(self.impl)
+        self.prev = gemm_impl.get()
+        gemm_impl._tls.current = self.impl
 
     def __exit__(self, *exc):
-        gemm_impl.current = self.prev
-        native.load().dtc_gemm_set_impl(self.prev)
+        gemm_impl._tls.current = self.prev
 
 
 def _check_rowmajor(t: torch.Tensor, name: str) -> None:
@@ -61,9 +64,9 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
     _check_rowmajor(out, "out")
     if mode == 1 and out2 is None:
         out2 = torch.empty((M, N), device=a.device, dtype=BF16)
-    native.call("dtc_gemm_bf16", a, a.stride(0), int(a_mn), b, b.stride(0), int(b_mn), M, N, K, mode, float(alpha),
+    native.call("dtc_gemm_bf16_ex", a, a.stride(0), int(a_mn), b, b.stride(0), int(b_mn), M, N, K, mode, float(alpha),
                 bias, aux, aux.stride(0) if aux is not None else 0, out, out.stride(0), out2,
-                out2.stride(0) if out2 is not None else 0, splits, stages, block_n)
+                out2.stride(0) if out2 is not None else 0, splits, stages, block_n, gemm_impl.get())
     return out if mode != 1 else (out, out2)
 
 

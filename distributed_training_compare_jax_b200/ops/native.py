@@ -27,6 +27,7 @@ _PROTOS: dict[str, list[Any]] = {
     "dtc_cast_f32_to_bf16_2d": [P, L, P, L, I, I],
     "dtc_cast_f32_to_bf16_2d_clear": [P, L, P, L, I, I],
     "dtc_gemm_bf16": [P, L, I, P, L, I, I, I, I, I, F, P, P, L, P, L, P, L, I, I, I],
+    "dtc_gemm_bf16_ex": [P, L, I, P, L, I, I, I, I, I, F, P, P, L, P, L, P, L, I, I, I, I],
     "dtc_flash_attn_fwd": [P, P, P, L, P, L, P, I, I, I, I],
     "dtc_flash_attn_bwd": [P, P, P, L, P, L, P, L, P, P, P, L, P, P, L, I, I, I, I],
     "dtc_layernorm_fwd": [P, P, P, P, P, P, I, I, F],

@@ -42,6 +42,12 @@ int dtc_gemm_bf16(const void* A, long long lda, int a_mn_major, const void* B, l
                   int N, int K, int epi_mode, float alpha, const void* bias, const void* aux, long long ld_aux,
                   void* out, long long ldo, void* out2, long long ldo2, int splits, int stages, int block_n,
                   cudaStream_t stream);
+/* same, kernel variant chosen per call instead of through dtc_gemm_set_impl (0 default policy, 1 one tile per CTA,
+ * 2 / 3 CTA pairs 256x128 / 256x256, 4 persistent 1-CTA) */
+int dtc_gemm_bf16_ex(const void* A, long long lda, int a_mn_major, const void* B, long long ldb, int b_mn_major, int M,
+                  int N, int K, int epi_mode, float alpha, const void* bias, const void* aux, long long ld_aux,
+                  void* out, long long ldo, void* out2, long long ldo2, int splits, int stages, int block_n, int impl,
+                     cudaStream_t stream);
 
 int dtc_gemm_set_impl(int impl); /* 0 = persistent kernel (default), 1 = one-tile-per-CTA kernel (A/B tuning) */
 

@@ -36,3 +36,26 @@ def test_bench_json_line_has_the_contract_keys():
 def test_reference_arm_reports_unavailable_and_exits_zero():
     d = _run("--impl", "reference", "--gpus", "1", "--steps", "2", "--warmup", "1")
     assert d["impl"] == "reference" and "unavailable" in d and len(d["unavailable"]) > 20
+
+
+def test_a_failing_arm_does_not_lose_the_headline():
+    """Two gloo ranks, arms dp + tp: rank 1 raises inside the TP arm.  Its peer is stuck in a collective; the per-arm
+    watchdog sees the failure marker, rank 0 still prints ONE line with the DP headline and `extra.tp.error`, and the
+    launcher exits without waiting for a collective timeout."""
+    import socket
+    import time
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="", OMP_NUM_THREADS="2", DTC_BENCH_FAULT="tp:1", DTC_DIST_TIMEOUT="300")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", str(port), os.path.join(ROOT, "bench.py"), "--gpus", "2", "--steps", "2", "--warmup", "1",
+           "--backend", "torch", "--batch", "2", "--model-config", "configs/model_config_tiny.yaml", "--arms", "dp,tp"]
+    t0 = time.time()
+    r = subprocess.run(cmd, cwd=ROOT, env=env, capture_output=True, text=True, timeout=600)
+    lines = [l for l in r.stdout.splitlines() if l.startswith("{")]
+    assert len(lines) == 1, r.stdout[-2000:] + r.stderr[-3000:]
+    d = json.loads(lines[0])
+    assert d["value"] and d["value"] > 0 and d["config"]["parallelism"] == "dp2"
+    assert "error" in d["extra"]["tp"]
+    assert time.time() - t0 < 250

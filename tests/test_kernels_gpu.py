@@ -93,9 +93,7 @@ def test_gemm_strided_views_and_vocab_shape():
 @pytest.mark.parametrize("impl", [1, 2, 3])
 def test_gemm_kernel_variants_agree(impl):
     """one-tile-per-CTA (1), CTA-pair 256x128 (2) and CTA-pair 256x256 (3) kernels against the fp32 reference."""
-    lib = native.load()
-    try:
-        lib.dtc_gemm_set_impl(impl)
+    with Fn.gemm_impl(impl):
         M, K, N = 1024, 320, 768
         x, w, bias, res = randn(M, K), randn(K, N, scale=0.1), randn(N), randn(M, N)
         assert rel_err(Fn.gemm(x, w, b_mn=True, bias=bias), R.gemm(x, w, b_mn=True, bias=bias)) < 1e-2
@@ -124,8 +122,6 @@ def test_gemm_kernel_variants_agree(impl):
         # ragged edges: M, N not multiples of the pair tile
         a2, b2 = randn(600, 200), randn(200, 392, scale=0.1)
         assert rel_err(Fn.gemm(a2, b2, b_mn=True), R.gemm(a2, b2, b_mn=True)) < 1e-2
-    finally:
-        lib.dtc_gemm_set_impl(0)
 
 
 # ------------------------------------------------------------------------------------------- attention

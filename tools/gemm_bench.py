@@ -28,7 +28,7 @@ SHAPES = [  # name, a shape, b shape, a_mn, b_mn, epi, out shape / dtype, splits
 
 
 def run(name, ash, bsh, a_mn, b_mn, epi, splits, impl, iters=20):
-    native.load().dtc_gemm_set_impl(impl)
+    Fn.gemm_impl._tls.current = impl   # (single-threaded tool: set the per-thread variant directly)
     Kd, Md = (ash[0], ash[1]) if a_mn else (ash[1], ash[0])
     Nd = bsh[1] if b_mn else bsh[0]
     bytes_per_set = (ash[0] * ash[1] + bsh[0] * bsh[1] + 2 * Md * Nd) * 2
@@ -108,7 +108,7 @@ def main():
             torch.cuda.synchronize()
             line += f" | cuBLAS {e0.elapsed_time(e1) * 50:.1f} us (graph, L2-warm)"
         print(line, flush=True)
-    native.load().dtc_gemm_set_impl(0)
+    Fn.gemm_impl._tls.current = 0
 
 
 if __name__ == "__main__" and "--grouped" not in sys.argv:

@@ -19,8 +19,7 @@ def r(*s, scale=1.0):
 
 impl = int(os.environ.get("DTC_PROFILE_IMPL", "0"))   # GEMM variant (tools/gemm_bench.py: 0 default, 2 / 3 CTA pair)
 if impl:
-    from distributed_training_compare_jax_b200.ops import native
-    native.load().dtc_gemm_set_impl(impl)
+    Fn.gemm_impl._tls.current = impl
 if what in ("gemm", "all"):
     x, wqkv, bq = r(M, D), r(D, 3 * D, scale=0.05), r(3 * D)
     w1, b1 = r(D, F, scale=0.05), r(F)
