@@ -25,7 +25,8 @@
 
 namespace dtc {
 
-constexpr int SP_WARPS = 8;
+constexpr int SP_WARPS = 8;      // backward: rows per CTA (its column partials are reduced per CTA)
+constexpr int SPF_WARPS = 4;     // forward: rows per CTA — at TP = 8 a rank owns 512 rows: 128 CTAs instead of 64
 
 struct SpPeers {
   bf16* p[SP_MAX_RANKS];
@@ -60,6 +61,20 @@ DTC_DEVICE uint4 sp_load16(const bf16* p) {
   return *reinterpret_cast<const uint4*>(p);
 }
 
+// acc += sum over the n_part (<= SP_MAX_RANKS) partial-sum slots of one 16-byte chunk.  All loads are issued before the first
+// add: a load -> add loop over a run-time slot count serialises n_part DRAM / NVLink round trips per chunk (ncu: 60 % of the
+// stall samples of sp_ln_fwd were long-scoreboard waits on exactly that loop at TP = 8).
+template <bool L2_COHERENT>
+DTC_DEVICE void add_slots_bf16x8(float* acc, const bf16* part, int n_part, long long part_stride, long long off) {
+  uint4 v[SP_MAX_RANKS];
+#pragma unroll
+  for (int p = 0; p < SP_MAX_RANKS; ++p)
+    if (p < n_part) v[p] = sp_load16<L2_COHERENT>(part + p * part_stride + off);
+#pragma unroll
+  for (int p = 0; p < SP_MAX_RANKS; ++p)
+    if (p < n_part) add_bf16x8(acc, v[p]);
+}
+
 // one warp per owned row; D = NCH * 256, the row lives in registers (shared by both kernel variants)
 template <int NCH, bool L2_COHERENT>
 DTC_DEVICE void sp_ln_fwd_row(const bf16* __restrict__ res, const bf16* __restrict__ bias, const bf16* __restrict__ part,
@@ -79,7 +94,7 @@ DTC_DEVICE void sp_ln_fwd_row(const bf16* __restrict__ res, const bf16* __restri
     for (int j = 0; j < 8; ++j) xk[j] = 0.f;
     add_bf16x8(xk, *reinterpret_cast<const uint4*>(res + off));
     if (bias != nullptr) add_bf16x8(xk, *reinterpret_cast<const uint4*>(bias + c));
-    for (int p = 0; p < n_part; ++p) add_bf16x8(xk, sp_load16<L2_COHERENT>(part + p * part_stride + off));
+    add_slots_bf16x8<L2_COHERENT>(xk, part, n_part, part_stride, off);
     // the residual stream is stored in bf16: normalise exactly what the backward pass will read back
     const uint4 packed = make_uint4(pack_bf16x2(xk[0], xk[1]), pack_bf16x2(xk[2], xk[3]), pack_bf16x2(xk[4], xk[5]),
                                     pack_bf16x2(xk[6], xk[7]));
@@ -122,7 +137,7 @@ DTC_DEVICE void sp_ln_fwd_row(const bf16* __restrict__ res, const bf16* __restri
 // Barrier-kernel variant (default): the partial-sum slots were completed before this kernel started (flag barrier in
 // front of it), so the plain read-only load path is safe.
 template <int NCH>
-__global__ void __launch_bounds__(SP_WARPS * 32)
+__global__ void __launch_bounds__(SPF_WARPS * 32)
 sp_ln_fwd_kernel(const bf16* __restrict__ res, const bf16* __restrict__ bias, const bf16* __restrict__ part, int n_part,
                  long long part_stride, const bf16* __restrict__ gamma, const bf16* __restrict__ beta,
                  bf16* __restrict__ hsum, float* __restrict__ mean_out, float* __restrict__ rstd_out, bf16* mc_out,
@@ -130,7 +145,7 @@ sp_ln_fwd_kernel(const bf16* __restrict__ res, const bf16* __restrict__ bias, co
   pdl_launch_dependents();  // PDL: let the next kernel's prologue overlap this kernel
   pdl_wait();               // ... and do not touch global memory before the previous kernel has completed
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const long long row = (long long)blockIdx.x * SP_WARPS + warp;
+  const long long row = (long long)blockIdx.x * SPF_WARPS + warp;
   if (row >= Ms) return;
   sp_ln_fwd_row<NCH, false>(res, bias, part, n_part, part_stride, gamma, beta, hsum, mean_out, rstd_out, mc_out, peers,
                             n_out, out_row0, eps, row, lane);
@@ -139,7 +154,7 @@ sp_ln_fwd_kernel(const bf16* __restrict__ res, const bf16* __restrict__ bias, co
 // Folded-barrier variant: optionally waits for the partial-sum slots of every rank in its prologue (wait_in) and
 // publishes its own pushes to every rank from its last CTA (signal_out) — no separate barrier kernels around it.
 template <int NCH>
-__global__ void __launch_bounds__(SP_WARPS * 32)
+__global__ void __launch_bounds__(SPF_WARPS * 32)
 sp_ln_fwd_sync_kernel(const bf16* __restrict__ res, const bf16* __restrict__ bias, const bf16* __restrict__ part, int n_part,
                       long long part_stride, const bf16* __restrict__ gamma, const bf16* __restrict__ beta,
                       bf16* __restrict__ hsum, float* __restrict__ mean_out, float* __restrict__ rstd_out, bf16* mc_out,
@@ -153,7 +168,7 @@ sp_ln_fwd_sync_kernel(const bf16* __restrict__ res, const bf16* __restrict__ bia
     if (threadIdx.x == 0) sp_wait_done(sync, gridDim.x);
   }
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const long long row = (long long)blockIdx.x * SP_WARPS + warp;
+  const long long row = (long long)blockIdx.x * SPF_WARPS + warp;
   if (row < Ms)
     sp_ln_fwd_row<NCH, true>(res, bias, part, n_part, part_stride, gamma, beta, hsum, mean_out, rstd_out, mc_out, peers,
                              n_out, out_row0, eps, row, lane);
@@ -203,7 +218,7 @@ DTC_DEVICE void sp_ln_bwd_body(const bf16* __restrict__ part, int n_part, long l
         dy[j] = 0.f;
         xv[j] = 0.f;
       }
-      for (int p = 0; p < n_part; ++p) add_bf16x8(dy, sp_load16<L2_COHERENT>(part + p * part_stride + off));
+      add_slots_bf16x8<L2_COHERENT>(dy, part, n_part, part_stride, off);
       add_bf16x8(xv, *reinterpret_cast<const uint4*>(x + off));
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
@@ -244,6 +259,7 @@ DTC_DEVICE void sp_ln_bwd_body(const bf16* __restrict__ part, int n_part, long l
   }
 }
 
+// Barrier-kernel variant (default): the slots were completed before this kernel started, plain read-only loads are safe.
 template <int NCH>
 __global__ void __launch_bounds__(SP_WARPS * 32)
 sp_ln_bwd_kernel(const bf16* __restrict__ part, int n_part, long long part_stride, const bf16* __restrict__ x,
@@ -252,78 +268,8 @@ sp_ln_bwd_kernel(const bf16* __restrict__ part, int n_part, long long part_strid
                  SpPeers peers, int n_out, long long out_row0, int Ms) {
   pdl_launch_dependents();
   pdl_wait();
-  constexpr int D = NCH * 256;
-  __shared__ float s_dg[D];
-  __shared__ float s_db[D];
-  for (int i = threadIdx.x; i < D; i += blockDim.x) {
-    s_dg[i] = 0.f;
-    s_db[i] = 0.f;
-  }
-  __syncthreads();
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  float acc_dg[NCH * 8], acc_db[NCH * 8], gam[NCH * 8];
-#pragma unroll
-  for (int k = 0; k < NCH; ++k) {
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      acc_dg[k * 8 + j] = 0.f;
-      acc_db[k * 8 + j] = 0.f;
-      gam[k * 8 + j] = 0.f;
-    }
-    add_bf16x8(gam + k * 8, *reinterpret_cast<const uint4*>(gamma + k * 256 + lane * 8));
-  }
-  for (long long row = (long long)blockIdx.x * SP_WARPS + warp; row < Ms; row += (long long)gridDim.x * SP_WARPS) {
-    const float mu = mean[row], rs = rstd[row];
-    float xhat[NCH * 8], wdy[NCH * 8];
-    float c1 = 0.f, c2 = 0.f;
-#pragma unroll
-    for (int k = 0; k < NCH; ++k) {
-      const long long off = row * D + k * 256 + lane * 8;
-      float dy[8], xv[8];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        dy[j] = 0.f;
-        xv[j] = 0.f;
-      }
-      for (int p = 0; p < n_part; ++p) add_bf16x8(dy, *reinterpret_cast<const uint4*>(part + p * part_stride + off));
-      add_bf16x8(xv, *reinterpret_cast<const uint4*>(x + off));
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const int i = k * 8 + j;
-        xhat[i] = (xv[j] - mu) * rs;
-        acc_dg[i] += dy[j] * xhat[i];
-        acc_db[i] += dy[j];
-        wdy[i] = dy[j] * gam[i];
-        c1 += wdy[i];
-        c2 += wdy[i] * xhat[i];
-      }
-    }
-    c1 = warp_sum(c1) * (1.f / D);
-    c2 = warp_sum(c2) * (1.f / D);
-#pragma unroll
-    for (int k = 0; k < NCH; ++k) {
-      const long long off = row * D + k * 256 + lane * 8;
-      float r[8];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) r[j] = rs * (wdy[k * 8 + j] - c1 - xhat[k * 8 + j] * c2);
-      if (dres != nullptr) add_bf16x8(r, *reinterpret_cast<const uint4*>(dres + off));
-      sp_push16(mc_out, peers, n_out, (out_row0 + row) * D + k * 256 + lane * 8,
-                make_uint4(pack_bf16x2(r[0], r[1]), pack_bf16x2(r[2], r[3]), pack_bf16x2(r[4], r[5]), pack_bf16x2(r[6], r[7])));
-    }
-  }
-#pragma unroll
-  for (int k = 0; k < NCH; ++k) {
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      atomicAdd(&s_dg[k * 256 + lane * 8 + j], acc_dg[k * 8 + j]);
-      atomicAdd(&s_db[k * 256 + lane * 8 + j], acc_db[k * 8 + j]);
-    }
-  }
-  __syncthreads();
-  for (int i = threadIdx.x; i < D; i += blockDim.x) {
-    atomicAdd(&dgamma[i], s_dg[i]);
-    atomicAdd(&dbeta[i], s_db[i]);
-  }
+  sp_ln_bwd_body<NCH, false>(part, n_part, part_stride, x, mean, rstd, gamma, dres, dgamma, dbeta, mc_out, peers, n_out,
+                             out_row0, Ms);
 }
 
 // Folded-barrier variant (see sp_ln_fwd_sync_kernel).
@@ -411,11 +357,11 @@ extern "C" int dtc_sp_ln_fwd(const void* res, const void* bias, const void* part
   DTC_CHECK_ARG(res != nullptr && out_row0 >= 0, "sp_ln_fwd: residual rows missing");
   SpPeers peers;
   if (sp_fill_peers(&peers, mc_out, peer_out, n_out, "sp_ln_fwd")) return -1;
-  const int blocks = (Ms + SP_WARPS - 1) / SP_WARPS;
+  const int blocks = (Ms + SPF_WARPS - 1) / SPF_WARPS;
   const long long stride = (long long)Ms * D;
 #define DTC_SP_FWD(NCH)                                                                                              \
   case NCH:                                                                                                          \
-    DTC_CHECK_CUDA(dtc::launch(sp_ln_fwd_kernel<NCH>, blocks, SP_WARPS * 32, 0, stream,                              \
+    DTC_CHECK_CUDA(dtc::launch(sp_ln_fwd_kernel<NCH>, blocks, SPF_WARPS * 32, 0, stream,                              \
         reinterpret_cast<const bf16*>(res), reinterpret_cast<const bf16*>(bias), reinterpret_cast<const bf16*>(part), \
         n_part, stride, reinterpret_cast<const bf16*>(gamma), reinterpret_cast<const bf16*>(beta),                   \
         reinterpret_cast<bf16*>(hsum), mean, rstd, reinterpret_cast<bf16*>(mc_out), peers, n_out, out_row0, Ms, eps)); \
@@ -477,11 +423,11 @@ extern "C" int dtc_sp_ln_fwd_sync(const void* res, const void* bias, const void*
   SpSync sync;
   if (sp_fill_peers(&peers, mc_out, peer_out, n_out, "sp_ln_fwd_sync")) return -1;
   if (sp_fill_sync(&sync, sig_ptrs, counters, rank, world, "sp_ln_fwd_sync")) return -1;
-  const int blocks = (Ms + SP_WARPS - 1) / SP_WARPS;
+  const int blocks = (Ms + SPF_WARPS - 1) / SPF_WARPS;
   const long long stride = (long long)Ms * D;
 #define DTC_SP_FWD(NCH)                                                                                              \
   case NCH:                                                                                                          \
-    DTC_CHECK_CUDA(dtc::launch(sp_ln_fwd_sync_kernel<NCH>, blocks, SP_WARPS * 32, 0, stream,                         \
+    DTC_CHECK_CUDA(dtc::launch(sp_ln_fwd_sync_kernel<NCH>, blocks, SPF_WARPS * 32, 0, stream,                         \
         reinterpret_cast<const bf16*>(res), reinterpret_cast<const bf16*>(bias), reinterpret_cast<const bf16*>(part), \
         n_part, stride, reinterpret_cast<const bf16*>(gamma), reinterpret_cast<const bf16*>(beta),                   \
         reinterpret_cast<bf16*>(hsum), mean, rstd, reinterpret_cast<bf16*>(mc_out), peers, n_out, out_row0, Ms, eps,  \

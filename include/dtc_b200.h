@@ -49,7 +49,7 @@ int dtc_gemm_bf16_ex(const void* A, long long lda, int a_mn_major, const void* B
                   void* out, long long ldo, void* out2, long long ldo2, int splits, int stages, int block_n, int impl,
                      cudaStream_t stream);
 
-int dtc_gemm_set_impl(int impl); /* 0 = persistent kernel (default), 1 = one-tile-per-CTA kernel (A/B tuning) */
+int dtc_gemm_set_impl(int impl); /* process-wide default variant of dtc_gemm_bf16 (same codes as `impl` above; tools) */
 
 /* ---- causal flash attention (K3 K6; ref: model/CausalSelfAttention.py:34-42, model/GPTModel.py:50-51) ---- */
 int dtc_flash_attn_fwd(const void* q, const void* k, const void* v, long long ld, void* out, long long ldo,

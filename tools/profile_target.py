@@ -40,3 +40,26 @@ if what in ("attn", "all"):
         Fn.flash_attn_bwd(qkv, out, d_o, lse2, B, H, T, hd)
 torch.cuda.synchronize()
 print("profile target done")
+if what == "seqpar":
+    # One rank's share of the sequence-parallel TP = 8 sublayer boundary, with the 8 "peers" emulated by 8 local buffers
+    # (same kernels, same addresses-per-owner logic; the stores stay on this GPU instead of crossing NVLink):
+    #   fc2-like scatter GEMM [4096 x 256] x [256 x 512] -> slot `rank` of every owner's partial-sum buffer
+    #   reduce (8 slots) + bias + residual + LayerNorm on the 512 owned rows, pushed to the 8 gathered buffers; its backward
+    import ctypes as C
+    n, rank = 8, 3
+    Ms = M // n
+    x, w = r(M, F // n), r(F // n, D, scale=0.05)
+    parts = torch.zeros(n, n, Ms, D, device="cuda", dtype=bf)            # parts[o] = owner o's [n, Ms, D] slots
+    part_ptrs = (C.c_ulonglong * n)(*[parts[o].data_ptr() for o in range(n)])
+    gathered = torch.zeros(n, M, D, device="cuda", dtype=bf)              # every "rank"'s gathered operand buffer
+    out_ptrs = (C.c_ulonglong * n)(*[gathered[o].data_ptr() for o in range(n)])
+    res, bias, gamma, beta = r(Ms, D), r(D), r(D), r(D)
+    hsum = torch.empty(Ms, D, device="cuda", dtype=bf)
+    mean, rstd = torch.empty(Ms, device="cuda"), torch.empty(Ms, device="cuda")
+    dgamma, dbeta = torch.zeros(D, device="cuda"), torch.zeros(D, device="cuda")
+    for _ in range(3):
+        Fn.gemm_scatter(x, w, part_ptrs, n, rank, D, b_mn=True)
+        Fn.sp_ln_fwd(res, bias, parts[rank], n, gamma, beta, hsum, mean, rstd, 0, out_ptrs, n, rank * Ms, 1e-6)
+        Fn.sp_ln_bwd(parts[rank], n, hsum, mean, rstd, gamma, res, dgamma, dbeta, 0, out_ptrs, n, rank * Ms)
+    torch.cuda.synchronize()
+    print("profile target done")
