@@ -53,11 +53,6 @@ DTC_DEVICE uint32_t p_tile_offset(int row, int col8 /* 16-byte chunk index 0..15
 // __syncthreads in the loop).  Softmax inner loop: FMNMX, FFMA, MUFU.EX2, FADD and half a CVT per element; the causal
 // predicate is evaluated on the (at most two) diagonal blocks only.
 // TMEM: S 2 x 64 columns, PV 2 x HD columns -> 256 allocated -> two CTAs per SM.
-DTC_DEVICE float ex2_ftz(float x) {
-  float y;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
 
 template <int HD>
 __global__ void __launch_bounds__(160, HD == 32 ? 2 : 1)

@@ -116,6 +116,12 @@ DTC_DEVICE float tanh_fast(float x) {
   asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+// 2^x, single MUFU.EX2 (no range fix-ups; flush-to-zero; exp2(-inf) = +0)
+DTC_DEVICE float ex2_ftz(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 DTC_DEVICE float gelu_tanh(float x) {
   const float k0 = 0.7978845608028654f, k1 = 0.044715f;
   const float t = tanh_fast(k0 * (x + k1 * x * x * x));

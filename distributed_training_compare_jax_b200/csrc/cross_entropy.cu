@@ -25,40 +25,8 @@ DTC_DEVICE RowStat stat_merge(RowStat a, RowStat b) {
   return r;
 }
 
-DTC_DEVICE RowStat block_row_stats(const bf16* __restrict__ row, int V, float* s_red) {
-  RowStat st;
-  st.m = -INFINITY;
-  st.s = 0.f;
-  const int V8 = V & ~7;
-  for (int c = threadIdx.x * 8; c < V8; c += CE_THREADS * 8) {
-    const uint4 u = *reinterpret_cast<const uint4*>(row + c);
-    const uint32_t w[4] = {u.x, u.y, u.z, u.w};
-    float f[8];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const float2 t = unpack_bf16x2(w[j]);
-      f[2 * j] = t.x;
-      f[2 * j + 1] = t.y;
-    }
-    float cm = f[0];
-#pragma unroll
-    for (int j = 1; j < 8; ++j) cm = fmaxf(cm, f[j]);
-    if (cm > st.m) {
-      st.s = (st.m == -INFINITY) ? 0.f : st.s * __expf(st.m - cm);
-      st.m = cm;
-    }
-#pragma unroll
-    for (int j = 0; j < 8; ++j) st.s += __expf(f[j] - st.m);
-  }
-  for (int c = V8 + threadIdx.x; c < V; c += CE_THREADS) {
-    const float f = __bfloat162float(row[c]);
-    if (f > st.m) {
-      st.s = (st.m == -INFINITY) ? 0.f : st.s * __expf(st.m - f);
-      st.m = f;
-    }
-    st.s += __expf(f - st.m);
-  }
-  // warp then CTA reduction of (m, s) pairs
+// warp then CTA reduction of (m, s) pairs; every thread returns the merged statistics (s_red: 34 floats of shared memory)
+DTC_DEVICE RowStat block_merge_stats(RowStat st, float* s_red) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     RowStat other;
@@ -92,6 +60,42 @@ DTC_DEVICE RowStat block_row_stats(const bf16* __restrict__ row, int V, float* s
   st.m = s_red[32];
   st.s = s_red[33];
   return st;
+}
+
+DTC_DEVICE RowStat block_row_stats(const bf16* __restrict__ row, int V, float* s_red) {
+  RowStat st;
+  st.m = -INFINITY;
+  st.s = 0.f;
+  const int V8 = V & ~7;
+  for (int c = threadIdx.x * 8; c < V8; c += CE_THREADS * 8) {
+    const uint4 u = *reinterpret_cast<const uint4*>(row + c);
+    const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+    float f[8];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 t = unpack_bf16x2(w[j]);
+      f[2 * j] = t.x;
+      f[2 * j + 1] = t.y;
+    }
+    float cm = f[0];
+#pragma unroll
+    for (int j = 1; j < 8; ++j) cm = fmaxf(cm, f[j]);
+    if (cm > st.m) {
+      st.s = (st.m == -INFINITY) ? 0.f : st.s * __expf(st.m - cm);
+      st.m = cm;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) st.s += __expf(f[j] - st.m);
+  }
+  for (int c = V8 + threadIdx.x; c < V; c += CE_THREADS) {
+    const float f = __bfloat162float(row[c]);
+    if (f > st.m) {
+      st.s = (st.m == -INFINITY) ? 0.f : st.s * __expf(st.m - f);
+      st.m = f;
+    }
+    st.s += __expf(f - st.m);
+  }
+  return block_merge_stats(st, s_red);
 }
 
 // dlogits[c] = (exp(x - lse) - [c == y_local]) * gscale for c < V ; 0 for pad columns [V, ld)
@@ -136,6 +140,35 @@ ce_fwd_bwd_kernel(bf16* __restrict__ logits, long long ld, const int* __restrict
   const float lse = st.m + __logf(st.s);
   if (threadIdx.x == 0) loss_rows[blockIdx.x] = lse - target;
   __syncthreads();  // all reads of row[y] / stats done before the in-place overwrite
+  block_row_grad(row, V, (int)ld, lse, y, gscale);
+}
+
+// Loss + gradient from per-part statistics that the lm_head GEMM epilogue already produced (EPI_STORE_STATS):
+// parts[row * n_parts + p] = {max, sum exp(x - max)} of part p of the row.  One pass over the logits instead of two.
+__global__ void __launch_bounds__(CE_THREADS)
+ce_bwd_from_parts_kernel(bf16* __restrict__ logits, long long ld, const int* __restrict__ labels,
+                         const float2* __restrict__ parts, int n_parts, float* __restrict__ loss_rows, int V, float gscale) {
+  pdl_launch_dependents();
+  pdl_wait();
+  __shared__ float s_red[34];
+  bf16* row = logits + (long long)blockIdx.x * ld;
+  int y = labels[blockIdx.x];
+  y = y < 0 ? 0 : (y >= V ? V - 1 : y);
+  const float target = __bfloat162float(row[y]);
+  RowStat st;
+  st.m = -INFINITY;
+  st.s = 0.f;
+  for (int p = threadIdx.x; p < n_parts; p += CE_THREADS) {
+    const float2 v = parts[(long long)blockIdx.x * n_parts + p];
+    RowStat o;
+    o.m = v.x;
+    o.s = v.y;
+    st = stat_merge(st, o);
+  }
+  st = block_merge_stats(st, s_red);
+  const float lse = st.m + __logf(st.s);
+  if (threadIdx.x == 0) loss_rows[blockIdx.x] = lse - target;
+  __syncthreads();  // the read of row[y] is done before the in-place overwrite
   block_row_grad(row, V, (int)ld, lse, y, gscale);
 }
 
@@ -247,6 +280,18 @@ extern "C" int dtc_ce_grad(void* logits, long long ld, const int* labels, const 
 extern "C" int dtc_reduce_sum(const float* in, int n, float scale, float* out, int accumulate, cudaStream_t stream) {
   DTC_CHECK_ARG(n > 0, "reduce_sum: empty input");
   DTC_CHECK_CUDA(dtc::launch(reduce_sum_kernel, 1, 1024, 0, stream, in, n, scale, out, accumulate));
+  DTC_CHECK_LAUNCH();
+  return 0;
+}
+
+// Loss and in-place gradient from the per-part statistics written by the lm_head GEMM (epilogue mode 8, see dtc_gemm_bf16_ex):
+// parts = float2 [M, n_parts].  Same outputs as dtc_ce_fwd_bwd with one pass over the logits less.
+extern "C" int dtc_ce_bwd_from_parts(void* logits, long long ld, const int* labels, const void* parts, int n_parts,
+                                     float* loss_rows, int M, int V, float gscale, cudaStream_t stream) {
+  DTC_CHECK_ARG(M > 0 && V > 0 && ld >= V && ld % 8 == 0 && n_parts > 0 && parts != nullptr,
+                "ce_bwd_from_parts: bad shape M=%d V=%d ld=%lld n_parts=%d", M, V, ld, n_parts);
+  DTC_CHECK_CUDA(dtc::launch(ce_bwd_from_parts_kernel, M, CE_THREADS, 0, stream, reinterpret_cast<bf16*>(logits), ld, labels,
+                             reinterpret_cast<const float2*>(parts), n_parts, loss_rows, V, gscale));
   DTC_CHECK_LAUNCH();
   return 0;
 }

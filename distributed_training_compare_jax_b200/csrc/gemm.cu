@@ -45,6 +45,12 @@ enum GemmEpiMode : int {
   // (peer_out[o] + (sp_rank*sp_rows + row - o*sp_rows)*ldo), tile by tile while later tiles are still in the tensor
   // cores.  The owner sums the n slots in fp32 inside its next kernel (csrc/seqpar.cu).  Persistent kernel only.
   EPI_SCATTER_BF16 = 7,
+  // out_bf16 = alpha*acc + bias, and per-row softmax statistics of what was stored: for every (row, 128-column part of a
+  // tile) one float2 {max, sum exp(x - max)} over the part's VALID columns (n < n_valid; vocab padding excluded), written
+  // to stats[row * n_parts + 2*n_blk + half] (`out2` carries the float2 array, `ldo2` the number of valid columns).  The
+  // lm_head GEMM computes them while the accumulator is in registers anyway, which saves the cross-entropy kernel one full
+  // pass over the 412 MB of logits.  CTA-pair kernel only.
+  EPI_STORE_STATS = 8,
 };
 
 struct GemmEpi {
@@ -1167,7 +1173,7 @@ gemm_2cta_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
   const int tiles_mn = m_blocks * n_blocks;
   const int total_tiles = tiles_mn * splits;
   const int mode = epi.mode;
-  const bool bf16_out = mode <= EPI_DGELU;
+  const bool bf16_out = mode <= EPI_DGELU || mode == EPI_STORE_STATS;
   const bool use_aux = (mode == EPI_BIAS_RESIDUAL || mode == EPI_DGELU);
 
   if (warp == 0 && lane == 0) {
@@ -1363,6 +1369,7 @@ gemm_2cta_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
         mbar_wait(&tmem_full[buf], (it >> 1) & 1);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + buf * BN + ((uint32_t)(q * 32) << 16) + gcol;
+        float run_m = -INFINITY, run_s = 0.f;  // EPI_STORE_STATS: this row's (max, sum exp) over the group's columns of the tile
 #pragma unroll 1
         for (int sl = 0; sl < SPG; ++sl) {
           uint32_t r[64];
@@ -1388,6 +1395,44 @@ gemm_2cta_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
             }
           }
           const int col0 = n_blk * BN + gcol + sl * 64;
+          if (mode == EPI_STORE_STATS) {
+            // statistics of the ROUNDED values (the loss kernel re-reads the bf16 logits), pad columns masked out
+            const int n_valid = (int)epi.ldo2;
+            // (two passes over the registers, rounding twice, instead of keeping 64 rounded values alive)
+            auto rounded = [&](int c2, float& x, float& y) {
+              const float2 f = unpack_bf16x2(pack_bf16x2(__uint_as_float(r[2 * c2]), __uint_as_float(r[2 * c2 + 1])));
+              x = (col0 + 2 * c2 < n_valid) ? f.x : -INFINITY;
+              y = (col0 + 2 * c2 + 1 < n_valid) ? f.y : -INFINITY;
+            };
+            float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+            for (int c2 = 0; c2 < 32; ++c2) {
+              float x, y;
+              rounded(c2, x, y);
+              m4[c2 & 3] = fmaxf(m4[c2 & 3], fmaxf(x, y));
+            }
+            const float m_slab = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
+            if (m_slab > -INFINITY) {
+              constexpr float L2E = 1.4426950408889634f;
+              if (m_slab > run_m) {
+                run_s *= ex2_ftz((run_m - m_slab) * L2E);  // run_m = -inf: 0 * 0
+                run_m = m_slab;
+              }
+              const float mb = run_m * L2E;
+              float s4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+              for (int c2 = 0; c2 < 32; ++c2) {
+                float x, y;
+                rounded(c2, x, y);
+                s4[c2 & 3] += ex2_ftz(fmaf(x, L2E, -mb)) + ex2_ftz(fmaf(y, L2E, -mb));  // exp2(-inf) = 0 for masked columns
+              }
+              run_s += (s4[0] + s4[1]) + (s4[2] + s4[3]);
+            }
+            if (sl == SPG - 1 && (long long)row0 + row < M) {
+              const int n_parts = 2 * n_blocks;
+              reinterpret_cast<float2*>(epi.out2)[((long long)row0 + row) * n_parts + 2 * n_blk + g] = make_float2(run_m, run_s);
+            }
+          }
 #pragma unroll 1
           for (int o = 0; o < n_out; ++o, ++jc) {
             const int b = jc % GB;
@@ -1479,7 +1524,7 @@ static int launch_gemm_2cta(const void* A, long long lda, const void* B, long lo
   tout = ta;
   tout2 = ta;
   taux = ta;
-  if (epi.mode <= EPI_DGELU) {
+  if (epi.mode <= EPI_DGELU || epi.mode == EPI_STORE_STATS) {
     if ((rc = make_tmap_2d_bf16(&tout, epi.out, M, N, epi.ldo, BM, 64, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
     if (epi.mode == EPI_BIAS_GELU &&
         (rc = make_tmap_2d_bf16(&tout2, epi.out2, M, N, epi.ldo2, BM, 64, CU_TENSOR_MAP_SWIZZLE_128B)))
@@ -1551,12 +1596,17 @@ static int gemm_bf16_dispatch(const void* A, long long lda, int a_mn_major, cons
   DTC_CHECK_ARG(lda % 8 == 0 && ldb % 8 == 0, "gemm: lda=%lld ldb=%lld must be multiples of 8 elements", lda, ldb);
   DTC_CHECK_ARG(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0 && ((uintptr_t)out & 15) == 0,
                 "gemm: operand pointers must be 16-byte aligned");
-  DTC_CHECK_ARG(epi_mode >= 0 && epi_mode <= 5, "gemm: bad epilogue mode %d (the scatter epilogue has its own entry point)", epi_mode);
+  DTC_CHECK_ARG((epi_mode >= 0 && epi_mode <= 5) || epi_mode == EPI_STORE_STATS, "gemm: bad epilogue mode %d (the scatter epilogue has its own entry point)", epi_mode);
   DTC_CHECK_ARG(splits <= 1 || epi_mode == EPI_ATOMIC_F32, "gemm: split-K needs the fp32 reduce-add epilogue");
   DTC_CHECK_ARG(!(epi_mode == EPI_BIAS_RESIDUAL || epi_mode == EPI_DGELU) || aux != nullptr, "gemm: aux missing");
   DTC_CHECK_ARG(epi_mode != EPI_BIAS_GELU || out2 != nullptr, "gemm: out2 missing");
-  DTC_CHECK_ARG(ldo % 8 == 0 && (aux == nullptr || ld_aux % 8 == 0) && (out2 == nullptr || ldo2 % 8 == 0),
+  DTC_CHECK_ARG(ldo % 8 == 0 && (aux == nullptr || ld_aux % 8 == 0) &&
+                    (out2 == nullptr || ldo2 % 8 == 0 || epi_mode == EPI_STORE_STATS),
                 "gemm: output/aux leading dimensions must be multiples of 8");
+  DTC_CHECK_ARG(epi_mode != EPI_STORE_STATS || (out2 != nullptr && M >= 256 && N >= 128 && !a_mn_major && splits <= 1 &&
+                                                ldo2 > 0 && ldo2 <= N && (block_n == 128 || block_n == 256)),
+                "gemm: the statistics epilogue needs out2 = float2 stats, ldo2 = valid columns (1..N), an explicit block_n of "
+                "128 or 256 (it fixes the number of parts per row: 2 * ceil(N / block_n)), M >= 256, N >= 128, no split-K");
   GemmEpi epi;
   epi.mode = epi_mode;
   epi.alpha = alpha;
@@ -1591,8 +1641,8 @@ static int gemm_bf16_dispatch(const void* A, long long lda, int a_mn_major, cons
   const bool big = flops >= 1e11 || (flops >= 2e10 && splits > 1);  // (split-K: the lm_head dgrad of a small local batch)
   const bool mid = pair_layers && flops >= 6e9 && !a_mn_major && splits <= 1 &&
                    (epi_mode == EPI_STORE_BF16 || epi_mode == EPI_BIAS_GELU || epi_mode == EPI_BIAS_RESIDUAL);
-  const bool want_2cta = (impl == 2 || impl == 3 || (impl == 0 && (big || mid) && !env_v1)) &&
-                         M >= 256 && N >= 128;  // impl 4 forces the 1-CTA persistent kernel
+  const bool want_2cta = ((impl == 2 || impl == 3 || (impl == 0 && (big || mid) && !env_v1)) &&
+                          M >= 256 && N >= 128) || epi_mode == EPI_STORE_STATS;  // impl 4 forces the 1-CTA persistent kernel
   if (want_2cta) {
     const long long tiles256 = (long long)((M + 255) / 256) * ((N + 255) / 256) * (splits > 1 ? splits : 1);
     // 256-wide pair tiles (half the operand bytes per MMA cycle again) whenever they still fill all 74 CTA pairs;

@@ -14,6 +14,8 @@ dict of physical parameter views of a :class:`~.param_tree.ParamStore`.
 """
 from __future__ import annotations
 
+import os
+
 import torch
 
 from ..ops import functional as Fn
@@ -103,10 +105,19 @@ class GPTModel:
         L, eps = lo.L, self.config.layernorm_eps
         nv = lo.vocab_valid
         Fn.layernorm_fwd(ws.h[L], c["lnf_g"], c["lnf_b"], eps, out=ws.lnf, mean=ws.meanf, rstd=ws.rstdf)
-        Fn.gemm(ws.lnf, c["wlm"], b_mn=True, bias=c["blm"], out=ws.logits)
-        if tp.size == 1:
+        # Opt-in (DTC_CE_FUSED_STATS=1): the lm_head GEMM leaves per-part softmax statistics behind and the loss kernel makes
+        # ONE pass over the logits.  Measured on B200: the extra epilogue work (rounding, masking, exp2 on 206 M elements in
+        # the 8 epilogue warps) costs more than the saved 412 MB read: 4.47 vs 4.41 ms per step — so it is not the default.
+        fused_stats = tp.size == 1 and ws.M >= 256 and os.environ.get("DTC_CE_FUSED_STATS", "0") == "1"
+        if fused_stats:
+            Fn.gemm(ws.lnf, c["wlm"], b_mn=True, bias=c["blm"], out=ws.logits, epi="store_stats", block_n=256,
+                    stats=ws.ce_parts, n_valid=nv)
+            Fn.ce_bwd_from_parts(ws.logits, ws.labels, ws.ce_parts, ws.ce_n_parts, nv, gscale, loss_rows=ws.loss_rows)
+        elif tp.size == 1:
+            Fn.gemm(ws.lnf, c["wlm"], b_mn=True, bias=c["blm"], out=ws.logits)
             Fn.ce_fwd_bwd(ws.logits, ws.labels, nv, gscale, loss_rows=ws.loss_rows)
         else:
+            Fn.gemm(ws.lnf, c["wlm"], b_mn=True, bias=c["blm"], out=ws.logits)
             Fn.ce_stats(ws.logits, ws.labels, nv, lo.vocab_start, ws.ce_stats_local)
             tp.all_gather_into(ws.ce_stats_all, ws.ce_stats_local)
             Fn.ce_combine(ws.ce_stats_all, tp.size, ws.M, ws.lse, ws.loss_rows)

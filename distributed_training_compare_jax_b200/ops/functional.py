@@ -12,7 +12,7 @@ import torch
 
 from . import native
 
-EPI = {"store": 0, "bias_gelu": 1, "bias_residual": 2, "dgelu": 3, "atomic_f32": 4, "store_f32": 5}
+EPI = {"store": 0, "bias_gelu": 1, "bias_residual": 2, "dgelu": 3, "atomic_f32": 4, "store_f32": 5, "store_stats": 8}
 BF16 = torch.bfloat16
 F32 = torch.float32
 
@@ -47,9 +47,11 @@ def _check_rowmajor(t: torch.Tensor, name: str) -> None:
 def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = False, epi: str = "store",
          alpha: float = 1.0, bias: torch.Tensor | None = None, aux: torch.Tensor | None = None,
          out: torch.Tensor | None = None, out2: torch.Tensor | None = None, splits: int = 0, stages: int = 0,
-         block_n: int = 0) -> torch.Tensor:
+         block_n: int = 0, stats: torch.Tensor | None = None, n_valid: int = 0) -> torch.Tensor:
     """D[M,N] = A·Bᵀ on the tcgen05 GEMM.  ``a`` is [M,K] (or [K,M] when ``a_mn``), ``b`` is [N,K]
-    (or [K,N] when ``b_mn``).  See ``dtc_gemm_bf16`` for the epilogues."""
+    (or [K,N] when ``b_mn``).  See ``dtc_gemm_bf16`` for the epilogues.  ``epi="store_stats"``: besides the bf16 output,
+    ``stats`` (fp32 [M, 2·ceil(N / block_n), 2]) receives {max, Σ exp(x − max)} of every 128- (block_n 256) or 64-column
+    (block_n 128) part of each row over the columns < ``n_valid`` (see :func:`ce_bwd_from_parts`)."""
     _check_rowmajor(a, "a")
     _check_rowmajor(b, "b")
     K, M = (a.shape[0], a.shape[1]) if a_mn else (a.shape[1], a.shape[0])
@@ -64,6 +66,14 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
     _check_rowmajor(out, "out")
     if mode == 1 and out2 is None:
         out2 = torch.empty((M, N), device=a.device, dtype=BF16)
+    if mode == 8:
+        block_n = block_n or 256
+        n_parts = 2 * (-(-N // block_n))
+        if stats is None or stats.dtype != F32 or stats.numel() < M * n_parts * 2 or not stats.is_contiguous():
+            raise ValueError(f"gemm: store_stats needs a contiguous fp32 stats tensor of at least [{M}, {n_parts}, 2]")
+        native.call("dtc_gemm_bf16_ex", a, a.stride(0), int(a_mn), b, b.stride(0), int(b_mn), M, N, K, mode, float(alpha),
+                    bias, None, 0, out, out.stride(0), stats, int(n_valid or N), 0, stages, block_n, gemm_impl.get())
+        return out
     native.call("dtc_gemm_bf16_ex", a, a.stride(0), int(a_mn), b, b.stride(0), int(b_mn), M, N, K, mode, float(alpha),
                 bias, aux, aux.stride(0) if aux is not None else 0, out, out.stride(0), out2,
                 out2.stride(0) if out2 is not None else 0, splits, stages, block_n, gemm_impl.get())
@@ -175,6 +185,15 @@ def ce_fwd_bwd(logits, labels, V: int, gscale: float, loss_rows=None):
     M = logits.shape[0]
     loss_rows = torch.empty(M, device=logits.device, dtype=F32) if loss_rows is None else loss_rows
     native.call("dtc_ce_fwd_bwd", logits, logits.stride(0), labels, loss_rows, M, V, float(gscale))
+    return loss_rows
+
+
+def ce_bwd_from_parts(logits, labels, parts, n_parts: int, V: int, gscale: float, loss_rows=None):
+    """Like :func:`ce_fwd_bwd`, with the row statistics taken from ``parts`` (written by ``gemm(epi="store_stats")``): one
+    pass over the logits instead of two."""
+    M = logits.shape[0]
+    loss_rows = torch.empty(M, device=logits.device, dtype=F32) if loss_rows is None else loss_rows
+    native.call("dtc_ce_bwd_from_parts", logits, logits.stride(0), labels, parts, n_parts, loss_rows, M, V, float(gscale))
     return loss_rows
 
 

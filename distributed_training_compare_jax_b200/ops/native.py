@@ -36,6 +36,7 @@ _PROTOS: dict[str, list[Any]] = {
     "dtc_embed_bwd": [P, P, P, P, I, I, I, I, F, U64, P, U32, L],
     "dtc_ce_fwd_bwd": [P, L, P, P, I, I, F],
     "dtc_ce_stats": [P, L, P, P, I, I, I],
+    "dtc_ce_bwd_from_parts": [P, L, P, P, I, P, I, I, F],
     "dtc_ce_combine": [P, I, I, P, P],
     "dtc_ce_grad": [P, L, P, P, I, I, I, F],
     "dtc_reduce_sum": [P, I, F, P, I],

@@ -58,6 +58,8 @@ class Workspace:
             self.lnf, self.meanf, self.rstdf = e(M, D), e(M, dtype=F32), e(M, dtype=F32)
             self.logits = e(M, Vl)
             self.dln_f32 = e(M, D, dtype=F32)   # split-K accumulator of the lm_head dgrad (few output tiles, K = vocab)
+            self.ce_n_parts = 2 * (-(-Vl // 256))   # softmax statistics per 128-column part, from the lm_head GEMM epilogue
+            self.ce_parts = e(M, self.ce_n_parts, 2, dtype=F32)
             self.loss_rows, self.lse = e(M, dtype=F32), e(M, dtype=F32)
             if tp_size > 1:
                 self.ce_stats_local, self.ce_stats_all = e(M, 3, dtype=F32), e(tp_size, M, 3, dtype=F32)

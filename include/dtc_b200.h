@@ -89,6 +89,11 @@ int dtc_embed_bwd(const int* ids, const void* dh, float* dwte, float* dwpe, int 
 /* ---- softmax cross-entropy (K12 X7; ref: train/create_train_step.py:32-34,148) --------------------- */
 int dtc_ce_fwd_bwd(void* logits, long long ld, const int* labels, float* loss_rows, int M, int V, float gscale,
                    cudaStream_t stream);
+/* loss + in-place gradient from the {max, sum exp} parts written by the lm_head GEMM (dtc_gemm_bf16_ex, epi_mode 8:
+ * out2 = float2 parts [M, 2*ceil(N/block_n)], ldo2 = number of valid columns, block_n 128 or 256 given explicitly) —
+ * one pass over the logits instead of two (K11 + K12 fused at the statistics level; ref: train/create_train_step.py:31-34). */
+int dtc_ce_bwd_from_parts(void* logits, long long ld, const int* labels, const void* parts, int n_parts, float* loss_rows,
+                          int M, int V, float gscale, cudaStream_t stream);
 int dtc_ce_stats(const void* logits, long long ld, const int* labels, float* stats, int M, int V_local,
                  int vocab_start, cudaStream_t stream);
 int dtc_ce_combine(const float* stats, int n_shards, int M, float* lse, float* loss_rows, cudaStream_t stream);

@@ -205,6 +205,33 @@ def test_cross_entropy_fused(M, V, ld):
     assert logits[:, V:].abs().max().item() == 0.0 if ld > V else True
 
 
+@pytest.mark.parametrize("M,K,V,block_n", [(256, 128, 50258, 256), (512, 64, 1000, 128), (384, 64, 4000, 256)])
+def test_lm_head_statistics_epilogue_feeds_the_loss_kernel(M, K, V, block_n):
+    """lm_head GEMM with the statistics epilogue + single-pass loss kernel == plain GEMM + two-pass fused CE kernel, and
+    both match the fp32 reference (vocabulary not a multiple of anything: pad columns must not enter the statistics)."""
+    torch.manual_seed(5)
+    Vp = -(-V // 64) * 64
+    x, w, bias = randn(M, K), randn(K, Vp, scale=0.3), randn(Vp)
+    labels = torch.randint(0, V, (M,), device="cuda", dtype=torch.int32)
+    plain = Fn.gemm(x, w, b_mn=True, bias=bias)
+    ref_in = plain[:, :V].float()
+    n_parts = 2 * (-(-Vp // block_n))
+    parts = torch.full((M, n_parts, 2), float("nan"), device="cuda", dtype=F32)
+    logits = torch.zeros(M, Vp, device="cuda", dtype=BF16)
+    Fn.gemm(x, w, b_mn=True, bias=bias, out=logits, epi="store_stats", block_n=block_n, stats=parts, n_valid=V)
+    assert torch.equal(logits, plain)                       # same tiles, same rounding
+    # the parts merge to the row's logsumexp over the VALID columns
+    m, s = parts[..., 0], parts[..., 1]
+    lse = torch.logsumexp(torch.where(s > 0, m + torch.log(s.clamp_min(1e-30)), torch.full_like(m, -float("inf"))), dim=1)
+    assert torch.allclose(lse, torch.logsumexp(ref_in, dim=1), atol=2e-3, rtol=1e-4)
+    loss_a = Fn.ce_bwd_from_parts(logits, labels, parts, n_parts, V, 1.0 / M)
+    loss_b = Fn.ce_fwd_bwd(plain, labels, V, 1.0 / M)
+    assert torch.allclose(loss_a, loss_b, atol=1e-3, rtol=1e-4)
+    assert torch.allclose(loss_a, R.cross_entropy_rows(ref_in, labels), atol=2e-3, rtol=1e-3)
+    assert rel_err(logits[:, :V], R.cross_entropy_grad(ref_in, labels, 1.0 / M)) < 1e-2
+    assert logits[:, V:].abs().max().item() == 0.0           # pad columns carry no gradient
+
+
 def test_cross_entropy_vocab_parallel_matches_fused():
     M, V, n = 48, 1024, 4
     Vl = V // n
