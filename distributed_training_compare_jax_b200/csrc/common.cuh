@@ -226,6 +226,22 @@ DTC_DEVICE void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
   asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
+// Execution-only cluster barrier (no memory ordering of its own): the arrive.release form compiles to MEMBAR + ERRBAR, which
+// a kernel pays for at entry and again at exit.  Use it where the data handed over is already ordered by other means
+// (barrier initialisation: fence.mbarrier_init.release.cluster) or where only "my peer has got this far" is needed.
+DTC_DEVICE void cluster_sync_relaxed() {
+  asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.aligned;" ::: "memory");
+}
+// 16-byte shared-memory accesses by 32-bit shared address (a pointer that went through uintptr_t arithmetic compiles to generic LD / ST)
+DTC_DEVICE void sts_v4(uint32_t addr, uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
+}
+DTC_DEVICE uint4 lds_v4(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+  return v;
+}
 // shared::cluster address of the same smem location in CTA `rank` of the cluster
 DTC_DEVICE uint32_t mapa_shared(uint32_t smem_addr, uint32_t rank) {
   uint32_t r;

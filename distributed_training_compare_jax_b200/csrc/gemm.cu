@@ -991,7 +991,7 @@ gemm_grouped_wgrad_2cta_kernel(const __grid_constant__ GemmGroup grp, int K, int
   }
   tc_fence_before();
   __syncthreads();
-  cluster_sync_all();
+  cluster_sync_relaxed();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
   pdl_launch_dependents();
@@ -1104,7 +1104,7 @@ gemm_grouped_wgrad_2cta_kernel(const __grid_constant__ GemmGroup grp, int K, int
 
   tc_fence_before();
   __syncthreads();
-  cluster_sync_all();
+  cluster_sync_relaxed();
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc_2sm(tmem_base, 2 * BN);
@@ -1139,13 +1139,34 @@ struct P2Smem {
   static constexpr int bytes(int stages) { return stages * STAGE_BYTES + NSLAB * SLAB_BYTES + 1024 + TAIL_BYTES; }
 };
 
+// Debug trace of the pair kernel (compiled in with -DDTC_GEMM_TRACE only; tools/gemm_pair_trace.py): the leader CTA of the first
+// and of the last pair of every launch stamp clock64 at the phase boundaries of their first tile into a record of 16 words.
+#ifdef DTC_GEMM_TRACE
+__device__ unsigned long long* g_pair_trace = nullptr;  // [0] launch counter, records from word 16
+#define GT_STAMP(i)                                    \
+  do {                                                 \
+    if (s_trace_rec) s_trace_rec[i] = clock64();       \
+  } while (0)
+DTC_DEVICE unsigned long long gt_globaltimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+#else
+#define GT_STAMP(i) do { } while (0)
+#endif
+
 template <int N>
 DTC_DEVICE void tma_store_wait_read_n() {
   asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
 }
 DTC_DEVICE void epi_group_sync(int g) { asm volatile("bar.sync %0, 128;" ::"r"(g + 1) : "memory"); }
 
-template <bool A_MN, bool B_MN, int BN, int NSLAB>
+// MODE >= 0: the epilogue mode is a compile-time constant (the launch's epi.mode must equal it); MODE < 0: read at run time.
+// A run-time mode makes the compiler if-convert the mode branches: every slab then ISSUES the GELU / residual / statistics
+// instructions of all modes predicated off — 700 instructions per warp and slab for a plain store, and with two epilogue
+// warps per scheduler that issue time was the 1.5 us per slab the clock trace shows (profiles/r2/gemm_pair_trace.md).
+template <bool A_MN, bool B_MN, int BN, int NSLAB, int MODE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(PG_THREADS, NSLAB == 2 ? 2 : 1)
 gemm_2cta_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                  const __grid_constant__ CUtensorMap tma_out, const __grid_constant__ CUtensorMap tma_out2,
@@ -1172,9 +1193,38 @@ gemm_2cta_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
   const int total_kb = (K + BK - 1) / BK;
   const int tiles_mn = m_blocks * n_blocks;
   const int total_tiles = tiles_mn * splits;
-  const int mode = epi.mode;
+  const int mode = MODE >= 0 ? MODE : epi.mode;
   const bool bf16_out = mode <= EPI_DGELU || mode == EPI_STORE_STATS;
   const bool use_aux = (mode == EPI_BIAS_RESIDUAL || mode == EPI_DGELU);
+#ifdef DTC_GEMM_TRACE
+  unsigned long long*& s_trace_rec = *reinterpret_cast<unsigned long long**>(bars + 62);  // (spare word of the barrier block)
+  if (threadIdx.x == 0) {
+    unsigned long long* rec = nullptr;
+    if (g_pair_trace != nullptr && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 2)) {
+      const unsigned long long slot = atomicAdd(g_pair_trace, 1ull);
+      if (slot < 4096) {
+        rec = g_pair_trace + 16 + slot * 16;
+        rec[0] = gt_globaltimer();
+        rec[1] = clock64();
+        rec[15] = ((unsigned long long)gridDim.x << 32) | blockIdx.x;
+      }
+    }
+    s_trace_rec = rec;
+  }
+#endif
+
+  // This CTA's share of a tile, decoded for the FIRST tile ahead of the prologue barriers: the integer divisions and the
+  // cold kernel-parameter loads cost ~0.5 us when they sat between the cluster barrier and the first TMA issue (clock trace).
+  auto decode_tile = [&](int tile, int& row0, int& bcol0, int& kb_begin, int& nkb) {
+    const int split = tile / tiles_mn, mn = tile % tiles_mn;
+    const int m_blk = mn % m_blocks, n_blk = mn / m_blocks;
+    row0 = m_blk * 256 + (int)cta * BM;        // this CTA's rows of A / of the output
+    bcol0 = n_blk * BN + (int)cta * (BN / 2);  // this CTA's half of the B tile
+    kb_begin = split * kb_per_split;
+    nkb = min(total_kb, kb_begin + kb_per_split) - kb_begin;
+  };
+  int f_row0 = 0, f_bcol0 = 0, f_kb_begin = 0, f_nkb = 0;
+  if (pair < total_tiles) decode_tile(pair, f_row0, f_bcol0, f_kb_begin, f_nkb);
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tma_a);
@@ -1199,26 +1249,23 @@ gemm_2cta_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
   }
   tc_fence_before();
   __syncthreads();
-  cluster_sync_all();  // the peer's barriers are initialised before anything may arrive on them remotely
+  cluster_sync_relaxed();  // the peer's barriers are initialised (and fenced: fence_barrier_init) before anything may arrive on them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
   pdl_launch_dependents();  // PDL: only after this CTA owns its TMEM (a dependent may not allocate first)
   pdl_wait();               // inputs come from the previous kernel: no global access before it has completed
+  if (threadIdx.x == 0) GT_STAMP(2);
 
   if (warp == 0) {
     // ------------------------------ TMA producer (both CTAs) ------------------------------
     if (elect_one()) {
       uint32_t kit = 0;
+      int s = 0;
+      uint32_t ph = 0;  // ring position: stage s, lap parity ph
       for (int tile = pair; tile < total_tiles; tile += num_pairs) {
-        const int split = tile / tiles_mn, mn = tile % tiles_mn;
-        const int m_blk = mn % m_blocks, n_blk = mn / m_blocks;
-        const int row0 = m_blk * 256 + (int)cta * BM;       // this CTA's rows of A / of the output
-        const int bcol0 = n_blk * BN + (int)cta * (BN / 2);  // this CTA's half of the B tile
-        const int kb_begin = split * kb_per_split;
-        const int nkb = min(total_kb, kb_begin + kb_per_split) - kb_begin;
+        int row0 = f_row0, bcol0 = f_bcol0, kb_begin = f_kb_begin, nkb = f_nkb;
+        if (tile != pair) decode_tile(tile, row0, bcol0, kb_begin, nkb);
         for (int i = 0; i < nkb; ++i, ++kit) {
-          const int s = kit % num_stages;
-          const uint32_t ph = (kit / num_stages) & 1;
           mbar_wait(&empty_bar[s], ph ^ 1);
           uint8_t* sa = smem + s * S::STAGE_BYTES;
           uint8_t* sb = sa + S::A_BYTES;
@@ -1237,6 +1284,11 @@ gemm_2cta_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
           } else {
             tma_load_2d_2sm(sb, &tma_b, full_leader, k0, bcol0);
           }
+          if (kit == 0) GT_STAMP(3);
+          if (++s == num_stages) {
+            s = 0;
+            ph ^= 1;
+          }
         }
       }
     }
@@ -1247,21 +1299,24 @@ gemm_2cta_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
       constexpr uint32_t A_LBO = A_MN ? BK * 128 : 16, A_STEP = A_MN ? 2048 : 32;
       constexpr uint32_t B_LBO = B_MN ? BK * 128 : 16, B_STEP = B_MN ? 2048 : 32;
       uint32_t kit = 0;
+      int s = 0;
+      uint32_t ph = 0;
       int it = 0;
       for (int tile = pair; tile < total_tiles; tile += num_pairs, ++it) {
-        const int split = tile / tiles_mn;
-        const int kb_begin = split * kb_per_split;
-        const int nkb = min(total_kb, kb_begin + kb_per_split) - kb_begin;
+        int nkb = f_nkb;
+        if (tile != pair) {
+          const int kb_begin = (tile / tiles_mn) * kb_per_split;
+          nkb = min(total_kb, kb_begin + kb_per_split) - kb_begin;
+        }
         const int buf = it & 1;
         mbar_wait(&tmem_empty[buf], ((it >> 1) & 1) ^ 1);  // both CTAs' epilogues have drained this buffer
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + buf * BN;
         for (int i = 0; i < nkb; ++i, ++kit) {
-          const int s = kit % num_stages;
-          const uint32_t ph = (kit / num_stages) & 1;
           mbar_wait(&full_bar[s], ph);
           tc_fence_after();
           if (elect_one()) {
+            if (kit == 0) GT_STAMP(4);
             const uint32_t sa = smem_u32(smem + s * S::STAGE_BYTES);
             const uint32_t sb = sa + S::A_BYTES;
 #pragma unroll
@@ -1272,8 +1327,13 @@ gemm_2cta_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
             }
             umma_commit_2sm(&empty_bar[s], 0x3);
             if (i == nkb - 1) umma_commit_2sm(&tmem_full[buf], 0x3);
+            if (i == nkb - 1 && it == 0) GT_STAMP(5);
           }
           __syncwarp();
+          if (++s == num_stages) {
+            s = 0;
+            ph ^= 1;
+          }
         }
       }
     }
@@ -1368,6 +1428,7 @@ gemm_2cta_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
         }
         mbar_wait(&tmem_full[buf], (it >> 1) & 1);
         tc_fence_after();
+        if (it == 0 && threadIdx.x == 64) GT_STAMP(6);
         const uint32_t tmem_d = tmem_base + buf * BN + ((uint32_t)(q * 32) << 16) + gcol;
         float run_m = -INFINITY, run_s = 0.f;  // EPI_STORE_STATS: this row's (max, sum exp) over the group's columns of the tile
 #pragma unroll 1
@@ -1376,23 +1437,29 @@ gemm_2cta_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
           tmem_ld_32x32b_x32(tmem_d + sl * 64, r);
           tmem_ld_32x32b_x32(tmem_d + sl * 64 + 32, r + 32);
           tmem_ld_wait();
+          if (it == 0 && sl == 0 && threadIdx.x == 64) GT_STAMP(12);
           if (sl == SPG - 1) {  // this warp has read its whole share of the accumulator: hand the buffer back early
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive_cluster(mapa_shared(smem_u32(&tmem_empty[buf]), 0));
           }
           // v = alpha * acc + bias, kept in r as float bits
+          if (has_bias) {
+            const uint32_t bias_u32 = smem_u32(tbias + sl * 64);
 #pragma unroll
-          for (int c8 = 0; c8 < 8; ++c8) {
-            uint4 bb = make_uint4(0, 0, 0, 0);
-            if (has_bias) bb = *reinterpret_cast<const uint4*>(tbias + sl * 64 + c8 * 8);
-            const uint32_t bw[4] = {bb.x, bb.y, bb.z, bb.w};
+            for (int c8 = 0; c8 < 8; ++c8) {
+              const uint4 bb = lds_v4(bias_u32 + c8 * 16);
+              const uint32_t bw[4] = {bb.x, bb.y, bb.z, bb.w};
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const float2 f = unpack_bf16x2(bw[j]);
-              r[c8 * 8 + 2 * j] = __float_as_uint(__uint_as_float(r[c8 * 8 + 2 * j]) * alpha + f.x);
-              r[c8 * 8 + 2 * j + 1] = __float_as_uint(__uint_as_float(r[c8 * 8 + 2 * j + 1]) * alpha + f.y);
+              for (int j = 0; j < 4; ++j) {
+                const float2 f = unpack_bf16x2(bw[j]);
+                r[c8 * 8 + 2 * j] = __float_as_uint(fmaf(__uint_as_float(r[c8 * 8 + 2 * j]), alpha, f.x));
+                r[c8 * 8 + 2 * j + 1] = __float_as_uint(fmaf(__uint_as_float(r[c8 * 8 + 2 * j + 1]), alpha, f.y));
+              }
             }
+          } else if (alpha != 1.f) {
+#pragma unroll
+            for (int j = 0; j < 64; ++j) r[j] = __float_as_uint(__uint_as_float(r[j]) * alpha);
           }
           const int col0 = n_blk * BN + gcol + sl * 64;
           if (mode == EPI_STORE_STATS) {
@@ -1437,12 +1504,14 @@ gemm_2cta_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
           for (int o = 0; o < n_out; ++o, ++jc) {
             const int b = jc % GB;
             uint8_t* sbuf = gslab + b * S::SLAB_BYTES;
+            const uint32_t sbuf_u32 = smem_u32(sbuf);
             if (use_aux) {
               mbar_wait(&gaux[b], (jc / GB) & 1);  // the aux slab has landed (it was requested once the buffer was free)
             } else {
               if (leader) tma_store_wait_read_n<GB - 1>();  // the store that last used this buffer has read it
               epi_group_sync(g);
             }
+            if (it == 0 && sl == 0 && o == 0 && threadIdx.x == 64) GT_STAMP(13);
 #pragma unroll
             for (int c8 = 0; c8 < 8; ++c8) {
               const uint32_t off = swizzle_offset<3>(row * 128 + c8 * 16);
@@ -1450,7 +1519,7 @@ gemm_2cta_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
 #pragma unroll
               for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[c8 * 8 + j]);
               if (use_aux) {
-                const uint4 a = *reinterpret_cast<const uint4*>(sbuf + off);
+                const uint4 a = lds_v4(sbuf_u32 + off);
                 const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
@@ -1468,14 +1537,16 @@ gemm_2cta_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
 #pragma unroll
                 for (int j = 0; j < 8; ++j) v[j] = gelu_tanh(v[j]);
               }
-              *reinterpret_cast<uint4*>(sbuf + off) = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]),
-                                                                 pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+              sts_v4(sbuf_u32 + off, pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
+                     pack_bf16x2(v[6], v[7]));
             }
             fence_proxy_async_smem();
+            if (it == 0 && sl == 0 && o == 0 && threadIdx.x == 64) GT_STAMP(14);
             epi_group_sync(g);
             if (leader) {
               tma_store_2d(o == 0 ? &tma_out : &tma_out2, sbuf, col0, row0);
               tma_store_commit();
+              if (it == 0 && g == 0 && sl == SPG - 1 && o == n_out - 1) GT_STAMP(7);
               if (use_aux) {
                 // request the aux slab of the group's NEXT job (same tile, next slab — or the next tile of this pair)
                 int ntile = tile, nsl = sl + 1;
@@ -1496,21 +1567,31 @@ gemm_2cta_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
           }
         }
       }
-      if (leader) tma_store_wait_all();
+      // shared memory must outlive the stores' READS only; their writes are complete (and visible to the next kernel) when
+      // the grid is — waiting for the writes here kept every CTA ~0.5 us longer than necessary
+      if (leader) tma_store_wait_read();
+      if (leader && g == 0) GT_STAMP(8);
     }
   }
 
   tc_fence_before();
   __syncthreads();
-  cluster_sync_all();  // neither CTA leaves (or frees TMEM) while its peer may still touch its smem / barriers
+  if (threadIdx.x == 0) GT_STAMP(9);
+  cluster_sync_relaxed();  // neither CTA leaves (or frees TMEM) while its peer may still touch its smem / barriers
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc_2sm(tmem_base, 2 * BN);
+#ifdef DTC_GEMM_TRACE
+    if (lane == 0 && s_trace_rec) {
+      s_trace_rec[10] = clock64();
+      s_trace_rec[11] = gt_globaltimer();
+    }
+#endif
   }
 }
 
-template <bool A_MN, bool B_MN, int BN, int NSLAB>
-static int launch_gemm_2cta(const void* A, long long lda, const void* B, long long ldb, int M, int N, int K, int splits,
+template <bool A_MN, bool B_MN, int BN, int NSLAB, int MODE>
+static int launch_gemm_2cta_mode(const void* A, long long lda, const void* B, long long ldb, int M, int N, int K, int splits,
                             int stages, const GemmEpi& epi, cudaStream_t stream) {
   using S = P2Smem<BN, NSLAB>;
   CUtensorMap ta, tb, tout, tout2, taux;
@@ -1543,8 +1624,8 @@ static int launch_gemm_2cta(const void* A, long long lda, const void* B, long lo
   const int smem_cap = NSLAB == 2 ? 112 * 1024 : 227 * 1024;  // light configuration: two CTAs (+1 KB reserved each) per SM
   while (stages > 2 && S::bytes(stages) > smem_cap) --stages;
   const int smem_bytes = S::bytes(stages);
-  auto kern = gemm_2cta_kernel<A_MN, B_MN, BN, NSLAB>;
-  static dtc::SmemOptIn configured;  // per device
+  auto kern = gemm_2cta_kernel<A_MN, B_MN, BN, NSLAB, MODE>;
+  static dtc::SmemOptIn configured;  // per device (and per instantiation)
   DTC_CHECK_CUDA(dtc::ensure_dyn_smem(kern, NSLAB == 2 ? 113 * 1024 : 227 * 1024, configured));
   const int m_blocks = (M + 255) / 256, n_blocks = (N + BN - 1) / BN;
   const int total_tiles = m_blocks * n_blocks * splits;
@@ -1554,6 +1635,28 @@ static int launch_gemm_2cta(const void* A, long long lda, const void* B, long lo
                                                       kb_per_split, stages, epi));
   DTC_CHECK_LAUNCH();
   return 0;
+}
+
+// The epilogue modes the model's GEMMs use get their own instantiation (see the kernel's MODE parameter); the rest share
+// the run-time-mode one.  Transposed-A problems are weight gradients: fp32 reduce-add, or the run-time-mode kernel.
+template <bool A_MN, bool B_MN, int BN, int NSLAB>
+static int launch_gemm_2cta(const void* A, long long lda, const void* B, long long ldb, int M, int N, int K, int splits,
+                            int stages, const GemmEpi& epi, cudaStream_t stream) {
+#define DTC_2CTA_MODE(MODE) \
+  return launch_gemm_2cta_mode<A_MN, B_MN, BN, NSLAB, MODE>(A, lda, B, ldb, M, N, K, splits, stages, epi, stream)
+  if (epi.mode == EPI_ATOMIC_F32) DTC_2CTA_MODE(EPI_ATOMIC_F32);
+  if constexpr (!A_MN) {
+    switch (epi.mode) {
+      case EPI_STORE_BF16: DTC_2CTA_MODE(EPI_STORE_BF16);
+      case EPI_BIAS_GELU: DTC_2CTA_MODE(EPI_BIAS_GELU);
+      case EPI_BIAS_RESIDUAL: DTC_2CTA_MODE(EPI_BIAS_RESIDUAL);
+      case EPI_DGELU: DTC_2CTA_MODE(EPI_DGELU);
+      case EPI_STORE_STATS: DTC_2CTA_MODE(EPI_STORE_STATS);
+      default: break;
+    }
+  }
+  DTC_2CTA_MODE(-1);
+#undef DTC_2CTA_MODE
 }
 
 }  // namespace dtc
@@ -1633,14 +1736,17 @@ static int gemm_bf16_dispatch(const void* A, long long lda, int a_mn_major, cons
   // CTA-pair kernel: needs >= 256 rows; 256-wide tiles when that still leaves enough pair-tiles to fill the GPU.
   // Default policy (impl 0), from profiles/r2/gemm_microbench.txt (device time, this kernel vs the 1-CTA persistent one):
   //   * big GEMMs (lm_head, >= 1e11 FLOP): always pairs — forward 251 -> 183 us, wgrad 234 -> 188 us;
-  //   * layer GEMMs of >= 6 GFLOP with a plain / GELU / residual epilogue (qkv 16.4 -> 14.3, fc1 23.5 -> 20.4,
-  //     fc2 20.6 -> 17.7, fc1 dgrad 20.2 -> 16.6 us); smaller ones (out_proj) and the GELU-backward epilogue are faster
-  //     on the 1-CTA kernel and stay there.  DTC_GEMM_PAIR_LAYERS=0 keeps every layer GEMM on the 1-CTA kernel.
+  //   * layer GEMMs of >= 2 GFLOP with a bf16 epilogue: with the epilogue mode compiled in (gemm_2cta_kernel's MODE) the
+  //     pair kernel wins on every layer shape of the small model — qkv 16.4 -> 12.2, fc1 23.5 -> 17.9, fc2 20.6 -> 16.3,
+  //     out_proj 10.0 -> 9.2, fc2 dgrad + GELU' 23.2 -> 21.2, fc1 dgrad 20.2 -> 15.3 us.  Smaller problems (micro-batches of
+  //     the pipeline / sequence-parallel paths) stay on the 1-CTA kernel with its 64-wide tiles.
+  //     DTC_GEMM_PAIR_LAYERS=0 keeps every layer GEMM on the 1-CTA kernel.
   static const bool pair_layers = !(getenv("DTC_GEMM_PAIR_LAYERS") && getenv("DTC_GEMM_PAIR_LAYERS")[0] == '0');
   const double flops = 2.0 * M * N * (double)K;
   const bool big = flops >= 1e11 || (flops >= 2e10 && splits > 1);  // (split-K: the lm_head dgrad of a small local batch)
-  const bool mid = pair_layers && flops >= 6e9 && !a_mn_major && splits <= 1 &&
-                   (epi_mode == EPI_STORE_BF16 || epi_mode == EPI_BIAS_GELU || epi_mode == EPI_BIAS_RESIDUAL);
+  const bool mid = pair_layers && flops >= 2e9 && !a_mn_major && splits <= 1 &&
+                   (epi_mode == EPI_STORE_BF16 || epi_mode == EPI_BIAS_GELU || epi_mode == EPI_BIAS_RESIDUAL ||
+                    epi_mode == EPI_DGELU);
   const bool want_2cta = ((impl == 2 || impl == 3 || (impl == 0 && (big || mid) && !env_v1)) &&
                           M >= 256 && N >= 128) || epi_mode == EPI_STORE_STATS;  // impl 4 forces the 1-CTA persistent kernel
   if (want_2cta) {
@@ -1897,3 +2003,11 @@ extern "C" int dtc_gemm_wgrad_grouped_pair(int count, const unsigned long long* 
   DTC_CHECK_LAUNCH();
   return 0;
 }
+
+#ifdef DTC_GEMM_TRACE
+// debug builds only: trace buffer of the pair kernel (>= 16 + 16 * 4096 zeroed 64-bit words), nullptr switches it off
+extern "C" int dtc_gemm_pair_set_trace(unsigned long long* buf) {
+  DTC_CHECK_CUDA(cudaMemcpyToSymbol(dtc::g_pair_trace, &buf, sizeof(buf)));
+  return 0;
+}
+#endif

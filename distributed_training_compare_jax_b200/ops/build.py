@@ -31,6 +31,9 @@ NVCC_FLAGS = [
     "-I", str(REPO_DIR / "include"),
     "-I", str(CSRC),
 ]
+# debug facilities compiled in on request, e.g. DTC_NVCC_DEFINES=DTC_GEMM_TRACE (part of the digest: set it wherever the
+# library is loaded as well, or the loader rebuilds without it)
+NVCC_FLAGS += [f"-D{d}" for d in os.environ.get("DTC_NVCC_DEFINES", "").split(",") if d]
 
 
 def find_nvcc() -> str:
