@@ -79,7 +79,14 @@ flash_attn_fwd_pipe_kernel(const __grid_constant__ CUtensorMap tm_q, const __gri
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 11);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int qblk = gridDim.x - 1 - blockIdx.x, h = blockIdx.y, b = blockIdx.z;  // heaviest query blocks first
+  // Longest-processing-time-first over the WHOLE grid: CTAs are dispatched in linear block order, and only two fit an SM
+  // (256 TMEM columns each), so the causal work (1..T/128 key blocks) is ordered globally — every (batch, head) pair's
+  // heaviest query block first, then all second-heaviest ones, ... — instead of heavy and light blocks interleaved, which
+  // left 4-unit CTAs in the last partial wave.
+  const int lin = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+  const int n_bh = gridDim.y * gridDim.z;
+  const int qblk = gridDim.x - 1 - lin / n_bh;
+  const int h = (lin % n_bh) % H, b = (lin % n_bh) / H;
   const int row0 = b * T + qblk * ATT_BLK;
   const int nkv = 2 * (qblk + 1);  // causal: 64-key blocks 0 .. 2*qblk+1
 

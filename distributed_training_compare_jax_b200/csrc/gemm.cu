@@ -769,6 +769,7 @@ constexpr int GG_MAX = 4;
 struct GemmGroup {
   CUtensorMap a[GG_MAX];
   CUtensorMap b[GG_MAX];
+  CUtensorMap o[GG_MAX];  // fp32 outputs in boxes of [128 rows x 32 columns] (CTA-pair kernel: TMA reduce-add epilogue)
   float* out[GG_MAX];
   long long ldo[GG_MAX];
   int M[GG_MAX];
@@ -948,6 +949,15 @@ gemm_grouped_wgrad_kernel(const __grid_constant__ GemmGroup grp, int K, int spli
 // runs two CTAs per SM that share that port: 39 us per layer, profiles/r2/step_budget_ncu.md).  Both operands are
 // MN-major (X is [K, M_p], dY is [K, N_p] row-major); fp32 reduce-add epilogue straight from registers; six 32 KB stages.
 // =========================================================================================================
+// epilogue helpers of the CTA-pair kernels: bounded wait on outstanding TMA stores / reduces, 128-thread group barrier
+template <int N>
+DTC_DEVICE void tma_store_wait_read_n() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+DTC_DEVICE void epi_group_sync(int g) { asm volatile("bar.sync %0, 128;" ::"r"(g + 1) : "memory"); }
+
+constexpr int GW_SLAB_BYTES = BM * 128;  // [128 rows x 32 fp32], one TMA box
+
 template <int BN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(PG_THREADS, 1)
 gemm_grouped_wgrad_2cta_kernel(const __grid_constant__ GemmGroup grp, int K, int splits, int kb_per_split, int num_stages,
@@ -955,7 +965,8 @@ gemm_grouped_wgrad_2cta_kernel(const __grid_constant__ GemmGroup grp, int K, int
   constexpr int A_BYTES = BM * BK * 2, B_BYTES = (BN / 2) * BK * 2, STAGE_BYTES = A_BYTES + B_BYTES;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + num_stages * STAGE_BYTES);
+  uint8_t* slabs = smem + num_stages * STAGE_BYTES;  // 4 x [128 rows x 32 fp32] (two per epilogue group)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(slabs + 4 * GW_SLAB_BYTES);
   uint64_t* full_bar = bars;                       // [PG_STAGE_MAX]  (leader's copy counts both CTAs' bytes)
   uint64_t* empty_bar = bars + PG_STAGE_MAX;       // [PG_STAGE_MAX]
   uint64_t* tmem_full = bars + 2 * PG_STAGE_MAX;   // [2]
@@ -974,6 +985,7 @@ gemm_grouped_wgrad_2cta_kernel(const __grid_constant__ GemmGroup grp, int K, int
     for (int p = 0; p < grp.count; ++p) {
       tma_prefetch_desc(&grp.a[p]);
       tma_prefetch_desc(&grp.b[p]);
+      tma_prefetch_desc(&grp.o[p]);
     }
     for (int s = 0; s < num_stages; ++s) {
       mbar_init(&full_bar[s], 1);
@@ -1064,24 +1076,27 @@ gemm_grouped_wgrad_2cta_kernel(const __grid_constant__ GemmGroup grp, int K, int
     }
   } else {
     // ------------------------------ epilogue (warps 2..9 of both CTAs): fp32 reduce-add ------------------------------
+    // Two groups of four warps (one warp per TMEM lane quadrant) take the two column halves of the tile in slabs of
+    // [128 rows x 32 fp32] = one 128B-swizzled TMA box, added to the gradient in L2 by TMA reduce: one bulk request per slab
+    // where each thread used to issue eight 16-byte red.global.add into eight different 128-byte lines.
     const int q = warp & 3;
     const int g = (warp - 2) >> 2;      // column half of the tile
     const int row = q * 32 + lane;
     const int gcol = g * (BN / 2);
+    const bool leader = (int)threadIdx.x - 64 - g * 128 == 0;
+    uint8_t* gslab = slabs + g * 2 * GW_SLAB_BYTES;
+    uint32_t jc = 0;
     int it = 0;
     for (int tile = pair; tile < total_tiles; tile += num_pairs, ++it) {
       int p, m_blk, n_blk;
       group_decode(grp, tile % tiles_mn, p, m_blk, n_blk);
       const int buf = it & 1;
-      const long long gm = (long long)m_blk * 256 + (int)cta * BM + row;
-      const bool row_ok = gm < grp.M[p];
-      const int Np = grp.N[p];
-      float* obase = grp.out[p] + gm * grp.ldo[p];
+      const int row0 = m_blk * 256 + (int)cta * BM;
       mbar_wait(&tmem_full[buf], (it >> 1) & 1);
       tc_fence_after();
       const uint32_t tmem_d = tmem_base + buf * BN + ((uint32_t)(q * 32) << 16) + gcol;
 #pragma unroll 1
-      for (int c = 0; c < BN / 64; ++c) {
+      for (int c = 0; c < BN / 64; ++c, ++jc) {
         uint32_t r[32];
         tmem_ld_32x32b_x32(tmem_d + c * 32, r);
         tmem_ld_wait();
@@ -1090,16 +1105,24 @@ gemm_grouped_wgrad_2cta_kernel(const __grid_constant__ GemmGroup grp, int K, int
           __syncwarp();
           if (lane == 0) mbar_arrive_cluster(mapa_shared(smem_u32(&tmem_empty[buf]), 0));
         }
-        const int n0 = n_blk * BN + gcol + c * 32;
+        uint8_t* sbuf = gslab + (jc & 1) * GW_SLAB_BYTES;
+        const uint32_t sbuf_u32 = smem_u32(sbuf);
+        if (leader) tma_store_wait_read_n<1>();  // the reduce that last used this buffer has read it
+        epi_group_sync(g);
 #pragma unroll
-        for (int c4 = 0; c4 < 8; ++c4) {
-          const int n = n0 + c4 * 4;
-          if (row_ok && n < Np)
-            red_add_v4_f32(obase + n, __uint_as_float(r[c4 * 4]) * alpha, __uint_as_float(r[c4 * 4 + 1]) * alpha,
-                           __uint_as_float(r[c4 * 4 + 2]) * alpha, __uint_as_float(r[c4 * 4 + 3]) * alpha);
+        for (int c4 = 0; c4 < 8; ++c4)
+          sts_v4(sbuf_u32 + swizzle_offset<3>(row * 128 + c4 * 16), __float_as_uint(__uint_as_float(r[c4 * 4]) * alpha),
+                 __float_as_uint(__uint_as_float(r[c4 * 4 + 1]) * alpha), __float_as_uint(__uint_as_float(r[c4 * 4 + 2]) * alpha),
+                 __float_as_uint(__uint_as_float(r[c4 * 4 + 3]) * alpha));
+        fence_proxy_async_smem();
+        epi_group_sync(g);
+        if (leader) {
+          tma_reduce_add_2d(&grp.o[p], sbuf, n_blk * BN + gcol + c * 32, row0);  // rows / columns past M_p / N_p are clipped
+          tma_store_commit();
         }
       }
     }
+    if (leader) tma_store_wait_read();
   }
 
   tc_fence_before();
@@ -1156,11 +1179,6 @@ DTC_DEVICE unsigned long long gt_globaltimer() {
 #define GT_STAMP(i) do { } while (0)
 #endif
 
-template <int N>
-DTC_DEVICE void tma_store_wait_read_n() {
-  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
-}
-DTC_DEVICE void epi_group_sync(int g) { asm volatile("bar.sync %0, 128;" ::"r"(g + 1) : "memory"); }
 
 // MODE >= 0: the epilogue mode is a compile-time constant (the launch's epi.mode must equal it); MODE < 0: read at run time.
 // A run-time mode makes the compiler if-convert the mode branches: every slab then ISSUES the GELU / residual / statistics
@@ -1229,7 +1247,7 @@ gemm_2cta_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tma_a);
     tma_prefetch_desc(&tma_b);
-    if (bf16_out) tma_prefetch_desc(&tma_out);
+    if (bf16_out || MODE == EPI_ATOMIC_F32) tma_prefetch_desc(&tma_out);
     if (use_aux) tma_prefetch_desc(&tma_aux);
     if (mode == EPI_BIAS_GELU) tma_prefetch_desc(&tma_out2);
     for (int s = 0; s < num_stages; ++s) {
@@ -1352,8 +1370,49 @@ gemm_2cta_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
     uint64_t* gaux = aux_full + g * GB;
     int it = 0;
 
-    if (!bf16_out) {
-      // fp32 outputs (split-K reduce-add / fp32 store): straight from registers, one accumulator row per thread
+    if (MODE == EPI_ATOMIC_F32) {
+      // fp32 reduce-add (weight gradients, split-K) with the mode compiled in: the group's column half leaves in slabs of
+      // [128 rows x 32 fp32] = one 128B-swizzled TMA box each, added to global memory by TMA reduce (tma_out is an fp32 map).
+      // One bulk request per slab replaces 1024 16-byte red.global.add, each of which touched its own 128-byte line.
+      uint32_t jc = 0;
+      for (int tile = pair; tile < total_tiles; tile += num_pairs, ++it) {
+        const int mn = tile % tiles_mn;
+        const int m_blk = mn % m_blocks, n_blk = mn / m_blocks;
+        const int buf = it & 1;
+        const int row0 = m_blk * 256 + (int)cta * BM;
+        mbar_wait(&tmem_full[buf], (it >> 1) & 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + buf * BN + ((uint32_t)(q * 32) << 16) + gcol;
+#pragma unroll 1
+        for (int c = 0; c < BN / 64; ++c, ++jc) {
+          uint32_t r[32];
+          tmem_ld_32x32b_x32(tmem_d + c * 32, r);
+          tmem_ld_wait();
+          if (c == BN / 64 - 1) {  // accumulator buffer drained by this warp
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(mapa_shared(smem_u32(&tmem_empty[buf]), 0));
+          }
+          const uint32_t sbuf_u32 = smem_u32(gslab + (jc % GB) * S::SLAB_BYTES);
+          if (leader) tma_store_wait_read_n<GB - 1>();  // the reduce that last used this buffer has read it
+          epi_group_sync(g);
+#pragma unroll
+          for (int c4 = 0; c4 < 8; ++c4)
+            sts_v4(sbuf_u32 + swizzle_offset<3>(row * 128 + c4 * 16), __float_as_uint(__uint_as_float(r[c4 * 4]) * alpha),
+                   __float_as_uint(__uint_as_float(r[c4 * 4 + 1]) * alpha),
+                   __float_as_uint(__uint_as_float(r[c4 * 4 + 2]) * alpha),
+                   __float_as_uint(__uint_as_float(r[c4 * 4 + 3]) * alpha));
+          fence_proxy_async_smem();
+          epi_group_sync(g);
+          if (leader) {
+            tma_reduce_add_2d(&tma_out, gslab + (jc % GB) * S::SLAB_BYTES, n_blk * BN + gcol + c * 32, row0);
+            tma_store_commit();
+          }
+        }
+      }
+      if (leader) tma_store_wait_read();
+    } else if (!bf16_out) {
+      // fp32 outputs (fp32 store, or reduce-add into a buffer TMA cannot address): straight from registers, one row per thread
       for (int tile = pair; tile < total_tiles; tile += num_pairs, ++it) {
         const int mn = tile % tiles_mn;
         const int m_blk = mn % m_blocks, n_blk = mn / m_blocks;
@@ -1613,6 +1672,8 @@ static int launch_gemm_2cta_mode(const void* A, long long lda, const void* B, lo
     if ((epi.mode == EPI_BIAS_RESIDUAL || epi.mode == EPI_DGELU) &&
         (rc = make_tmap_2d_bf16(&taux, epi.aux, M, N, epi.ld_aux, BM, 64, CU_TENSOR_MAP_SWIZZLE_128B)))
       return rc;
+  } else if (MODE == EPI_ATOMIC_F32) {
+    if ((rc = make_tmap_2d_f32(&tout, epi.out, M, N, epi.ldo, BM, 32, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
   }
   const int total_kb = (K + BK - 1) / BK;
   if (splits < 1) splits = 1;
@@ -1644,7 +1705,8 @@ static int launch_gemm_2cta(const void* A, long long lda, const void* B, long lo
                             int stages, const GemmEpi& epi, cudaStream_t stream) {
 #define DTC_2CTA_MODE(MODE) \
   return launch_gemm_2cta_mode<A_MN, B_MN, BN, NSLAB, MODE>(A, lda, B, ldb, M, N, K, splits, stages, epi, stream)
-  if (epi.mode == EPI_ATOMIC_F32) DTC_2CTA_MODE(EPI_ATOMIC_F32);
+  // (the TMA reduce epilogue needs a 16-byte aligned fp32 output with 16-byte row pitch; anything else takes the register path)
+  if (epi.mode == EPI_ATOMIC_F32 && epi.ldo % 4 == 0 && ((uintptr_t)epi.out & 15) == 0) DTC_2CTA_MODE(EPI_ATOMIC_F32);
   if constexpr (!A_MN) {
     switch (epi.mode) {
       case EPI_STORE_BF16: DTC_2CTA_MODE(EPI_STORE_BF16);
@@ -1976,6 +2038,9 @@ extern "C" int dtc_gemm_wgrad_grouped_pair(int count, const unsigned long long* 
     if ((rc = make_tmap_2d_bf16(&grp.b[p], reinterpret_cast<const void*>(B[p]), K, Ns[p], ldb[p], BK, 64,
                                 CU_TENSOR_MAP_SWIZZLE_128B)))
       return rc;
+    if ((rc = make_tmap_2d_f32(&grp.o[p], reinterpret_cast<const void*>(out[p]), Ms[p], Ns[p], ldo[p], BM, 32,
+                               CU_TENSOR_MAP_SWIZZLE_128B)))
+      return rc;
     grp.out[p] = reinterpret_cast<float*>(out[p]);
     grp.ldo[p] = ldo[p];
     grp.M[p] = Ms[p];
@@ -1991,7 +2056,7 @@ extern "C" int dtc_gemm_wgrad_grouped_pair(int count, const unsigned long long* 
   const int kb_per_split = (total_kb + splits - 1) / splits;
   splits = (total_kb + kb_per_split - 1) / kb_per_split;
   if (stages < 2 || stages > PG_STAGE_MAX) stages = PG_STAGE_MAX;
-  auto smem_of = [](int st) { return st * (BM * BK * 2 + (BN / 2) * BK * 2) + 1024 + 512; };
+  auto smem_of = [](int st) { return st * (BM * BK * 2 + (BN / 2) * BK * 2) + 4 * GW_SLAB_BYTES + 1024 + 512; };
   while (stages > 2 && smem_of(stages) > 227 * 1024) --stages;
   auto kern = gemm_grouped_wgrad_2cta_kernel<BN>;
   static dtc::SmemOptIn configured;  // per device

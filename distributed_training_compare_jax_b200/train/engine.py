@@ -265,9 +265,17 @@ def _grouped_backward_impl(self, ws, top: torch.Tensor) -> torch.Tensor:
         cs_args, wg_args = ws.group_args[key]
         splits = getattr(ws, "group_splits", None)
         if splits is None:
-            if self.wgrad_pair:   # 256 x 256 tiles on the 74 CTA pairs: slice the token reduction until they are busy ~twice
+            if self.wgrad_pair:
+                # 256 x 256 tiles on the 74 CTA pairs: slice the token reduction so that the last wave is nearly full, at a
+                # small price per extra slice (its reduce-add traffic).  48 tiles of the small model: 1 slice = 0.65 waves
+                # (29.1 us), 3 slices = 1.95 waves (27.4 us); profiles/r2/grouped_wgrad_microbench.txt
                 kb = max(1, self.micro_batch * self.seq_len // 64)
-                splits = ws.group_splits = max(1, min(8, kb // 8, 74 // max(ws.group_tiles256, 1)))
+                t = max(ws.group_tiles256, 1)
+
+                def fill(s):
+                    waves = t * s / 74.0
+                    return waves / -(-(t * s) // 74) - 0.05 * (s - 1)
+                splits = ws.group_splits = max(range(1, max(1, min(4, kb // 8)) + 1), key=fill)
             else:                 # fill 2 CTAs per SM when the layer is small (tensor-parallel shards)
                 splits = ws.group_splits = max(1, min(8, 296 // max(tiles, 1)))
         side = self.side if self.side is not None else main
