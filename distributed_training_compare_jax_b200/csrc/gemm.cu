@@ -1796,19 +1796,17 @@ static int gemm_bf16_dispatch(const void* A, long long lda, int a_mn_major, cons
   static const bool env_v1 = getenv("DTC_GEMM_V1") != nullptr;  // A/B switch: one-tile-per-CTA kernel
   const bool use_v1 = env_v1 || impl == 1;
   // CTA-pair kernel: needs >= 256 rows; 256-wide tiles when that still leaves enough pair-tiles to fill the GPU.
-  // Default policy (impl 0), from profiles/r2/gemm_microbench.txt (device time, this kernel vs the 1-CTA persistent one):
-  //   * big GEMMs (lm_head, >= 1e11 FLOP): always pairs — forward 251 -> 183 us, wgrad 234 -> 188 us;
-  //   * layer GEMMs of >= 2 GFLOP with a bf16 epilogue: with the epilogue mode compiled in (gemm_2cta_kernel's MODE) the
-  //     pair kernel wins on every layer shape of the small model — qkv 16.4 -> 12.2, fc1 23.5 -> 17.9, fc2 20.6 -> 16.3,
-  //     out_proj 10.0 -> 9.2, fc2 dgrad + GELU' 23.2 -> 21.2, fc1 dgrad 20.2 -> 15.3 us.  Smaller problems (micro-batches of
-  //     the pipeline / sequence-parallel paths) stay on the 1-CTA kernel with its 64-wide tiles.
-  //     DTC_GEMM_PAIR_LAYERS=0 keeps every layer GEMM on the 1-CTA kernel.
+  // Default policy (impl 0): every GEMM with >= 256 rows and >= 128 columns runs on CTA pairs.  With the epilogue mode
+  // compiled in, relaxed cluster barriers and the TMA reduce-add epilogue the pair kernel beats the 1-CTA persistent kernel
+  // on every shape of the model, at 4096 tokens per GPU and at the 512 / 1024 / 2048 of the strong-scaling runs alike
+  // (profiles/r2/gemm_microbench_mode_templated.txt, gemm_microbench_small_m.txt: e.g. M = 512: qkv 7.6 -> 6.3, fc2 17.2 ->
+  // 12.2, fc1 wgrad 17.0 -> 11.1, lm_head wgrad 99 -> 54 us).  Narrower problems (tensor-parallel shards below 128 columns,
+  // fewer than 256 tokens) stay on the 1-CTA kernel with its 64-wide tiles.  DTC_GEMM_PAIR_LAYERS=0 restores the old split
+  // (pairs only for the lm_head-sized GEMMs).
   static const bool pair_layers = !(getenv("DTC_GEMM_PAIR_LAYERS") && getenv("DTC_GEMM_PAIR_LAYERS")[0] == '0');
   const double flops = 2.0 * M * N * (double)K;
   const bool big = flops >= 1e11 || (flops >= 2e10 && splits > 1);  // (split-K: the lm_head dgrad of a small local batch)
-  const bool mid = pair_layers && flops >= 2e9 && !a_mn_major && splits <= 1 &&
-                   (epi_mode == EPI_STORE_BF16 || epi_mode == EPI_BIAS_GELU || epi_mode == EPI_BIAS_RESIDUAL ||
-                    epi_mode == EPI_DGELU);
+  const bool mid = pair_layers && epi_mode <= EPI_STORE_F32;
   const bool want_2cta = ((impl == 2 || impl == 3 || (impl == 0 && (big || mid) && !env_v1)) &&
                           M >= 256 && N >= 128) || epi_mode == EPI_STORE_STATS;  // impl 4 forces the 1-CTA persistent kernel
   if (want_2cta) {

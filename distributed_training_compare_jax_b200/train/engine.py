@@ -16,6 +16,8 @@ step (train/create_train_step.py:90-168).
 from __future__ import annotations
 
 import numpy as np
+import os
+
 import torch
 
 from ..config.schema import ModelConfig
@@ -266,16 +268,13 @@ def _grouped_backward_impl(self, ws, top: torch.Tensor) -> torch.Tensor:
         splits = getattr(ws, "group_splits", None)
         if splits is None:
             if self.wgrad_pair:
-                # 256 x 256 tiles on the 74 CTA pairs: slice the token reduction so that the last wave is nearly full, at a
-                # small price per extra slice (its reduce-add traffic).  48 tiles of the small model: 1 slice = 0.65 waves
-                # (29.1 us), 3 slices = 1.95 waves (27.4 us); profiles/r2/grouped_wgrad_microbench.txt
+                # 256 x 256 tiles on the 74 CTA pairs: slice the token reduction only while ALL slices still fit one wave.
+                # (Alone, 3 slices of the small model's 48 tiles are faster — 27.4 vs 29.1 us, 1.95 waves — but in the step
+                # this launch shares the GPU with the main stream: 3.79 ms with 3 slices, 3.74 ms with 1.)
                 kb = max(1, self.micro_batch * self.seq_len // 64)
-                t = max(ws.group_tiles256, 1)
-
-                def fill(s):
-                    waves = t * s / 74.0
-                    return waves / -(-(t * s) // 74) - 0.05 * (s - 1)
-                splits = ws.group_splits = max(range(1, max(1, min(4, kb // 8)) + 1), key=fill)
+                splits = ws.group_splits = max(1, min(8, kb // 8, 74 // max(ws.group_tiles256, 1)))
+                if os.environ.get("DTC_WGRAD_GROUP_SPLITS"):   # A/B override
+                    splits = ws.group_splits = int(os.environ["DTC_WGRAD_GROUP_SPLITS"])
             else:                 # fill 2 CTAs per SM when the layer is small (tensor-parallel shards)
                 splits = ws.group_splits = max(1, min(8, 296 // max(tiles, 1)))
         side = self.side if self.side is not None else main

@@ -12,6 +12,9 @@ from distributed_training_compare_jax_b200.ops import functional as Fn  # noqa: 
 from distributed_training_compare_jax_b200.ops import native  # noqa: E402
 
 M, D, F, V = 4096, 512, 2048, 50304
+for _a in sys.argv:   # --m=512: tokens per GPU of the strong-scaling runs (global batch 8 x 512 tokens over N GPUs)
+    if _a.startswith("--m="):
+        M = int(_a.split("=")[1])
 SHAPES = [  # name, a shape, b shape, a_mn, b_mn, epi, out shape / dtype, splits
     ("qkv fwd", (M, D), (D, 3 * D), False, True, "store", 0),
     ("fc1 fwd+gelu", (M, D), (D, F), False, True, "bias_gelu", 0),
