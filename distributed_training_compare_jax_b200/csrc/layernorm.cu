@@ -325,6 +325,7 @@ extern "C" int dtc_layernorm_bwd(const void* dy, const void* x, const float* mea
                                  const void* dres, void* dx, float* dgamma, float* dbeta, int M, int D,
                                  cudaStream_t stream) {
   DTC_CHECK_ARG(M > 0 && D % 256 == 0 && D >= 256 && D <= 2048, "layernorm_bwd: D=%d must be a multiple of 256, <= 2048", D);
+  DTC_CHECK_ARG((((uintptr_t)dgamma | (uintptr_t)dbeta) & 15) == 0, "layernorm_bwd: dgamma / dbeta must be 16-byte aligned");
   static const bool v1 = getenv("DTC_LN_BWD_V1") != nullptr;  // A/B: the 8-warp kernel for every D
   if (D <= 512 && !v1) {
     int sms = 148, dev = 0;

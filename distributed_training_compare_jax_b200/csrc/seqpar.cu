@@ -186,13 +186,19 @@ DTC_DEVICE void sp_ln_bwd_body(const bf16* __restrict__ part, int n_part, long l
                                float* __restrict__ dbeta, bf16* mc_out, const SpPeers& peers, int n_out, long long out_row0,
                                int Ms) {
   constexpr int D = NCH * 256;
-  __shared__ float s_dg[D];
-  __shared__ float s_db[D];
-  for (int i = threadIdx.x; i < D; i += blockDim.x) {
-    s_dg[i] = 0.f;
-    s_db[i] = 0.f;
+  // D <= 512: one [D] row of column partials per warp, summed by column after the row loop (plain 16-byte stores; the
+  // shared-memory atomics of the general path hit the same banks 8 ways with the lane * 8 + j layout)
+  constexpr bool WARP_ROWS = NCH <= 2;
+  constexpr int S_ROWS = WARP_ROWS ? SP_WARPS : 1;
+  __shared__ __align__(16) float s_dg[S_ROWS * D];
+  __shared__ __align__(16) float s_db[S_ROWS * D];
+  if constexpr (!WARP_ROWS) {
+    for (int i = threadIdx.x; i < D; i += blockDim.x) {
+      s_dg[i] = 0.f;
+      s_db[i] = 0.f;
+    }
+    __syncthreads();
   }
-  __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float acc_dg[NCH * 8], acc_db[NCH * 8], gam[NCH * 8];
 #pragma unroll
@@ -244,18 +250,49 @@ DTC_DEVICE void sp_ln_bwd_body(const bf16* __restrict__ part, int n_part, long l
                 make_uint4(pack_bf16x2(r[0], r[1]), pack_bf16x2(r[2], r[3]), pack_bf16x2(r[4], r[5]), pack_bf16x2(r[6], r[7])));
     }
   }
+  if constexpr (WARP_ROWS) {
 #pragma unroll
-  for (int k = 0; k < NCH; ++k) {
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      atomicAdd(&s_dg[k * 256 + lane * 8 + j], acc_dg[k * 8 + j]);
-      atomicAdd(&s_db[k * 256 + lane * 8 + j], acc_db[k * 8 + j]);
+    for (int k = 0; k < NCH; ++k) {
+      float4* pg = reinterpret_cast<float4*>(s_dg + warp * D + k * 256 + lane * 8);
+      float4* pb = reinterpret_cast<float4*>(s_db + warp * D + k * 256 + lane * 8);
+      pg[0] = make_float4(acc_dg[k * 8], acc_dg[k * 8 + 1], acc_dg[k * 8 + 2], acc_dg[k * 8 + 3]);
+      pg[1] = make_float4(acc_dg[k * 8 + 4], acc_dg[k * 8 + 5], acc_dg[k * 8 + 6], acc_dg[k * 8 + 7]);
+      pb[0] = make_float4(acc_db[k * 8], acc_db[k * 8 + 1], acc_db[k * 8 + 2], acc_db[k * 8 + 3]);
+      pb[1] = make_float4(acc_db[k * 8 + 4], acc_db[k * 8 + 5], acc_db[k * 8 + 6], acc_db[k * 8 + 7]);
     }
-  }
-  __syncthreads();
-  for (int i = threadIdx.x; i < D; i += blockDim.x) {
-    atomicAdd(&dgamma[i], s_dg[i]);
-    atomicAdd(&dbeta[i], s_db[i]);
+    __syncthreads();
+    // one thread per 4 columns of dgamma (first D / 4 threads) or dbeta (next D / 4): sum over the warps, one 16-byte reduce-add
+    for (int i = threadIdx.x; i < D / 2; i += blockDim.x) {
+      const bool is_db = i >= D / 4;
+      const int c = (is_db ? i - D / 4 : i) * 4;
+      const float* src = (is_db ? s_db : s_dg) + c;
+      float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int w = 0; w < SP_WARPS; ++w) {
+        const float4 v = *reinterpret_cast<const float4*>(src + w * D);
+        a.x += v.x;
+        a.y += v.y;
+        a.z += v.z;
+        a.w += v.w;
+      }
+      asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"((is_db ? dbeta : dgamma) + c), "f"(a.x), "f"(a.y),
+                   "f"(a.z), "f"(a.w)
+                   : "memory");
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < NCH; ++k) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        atomicAdd(&s_dg[k * 256 + lane * 8 + j], acc_dg[k * 8 + j]);
+        atomicAdd(&s_db[k * 256 + lane * 8 + j], acc_db[k * 8 + j]);
+      }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < D; i += blockDim.x) {
+      atomicAdd(&dgamma[i], s_dg[i]);
+      atomicAdd(&dbeta[i], s_db[i]);
+    }
   }
 }
 
@@ -384,6 +421,7 @@ extern "C" int dtc_sp_ln_bwd(const void* part, int n_part, const void* x, const 
                              cudaStream_t stream) {
   DTC_CHECK_ARG(Ms > 0 && D % 256 == 0 && D >= 256 && D <= 2048, "sp_ln_bwd: D=%d must be a multiple of 256, <= 2048", D);
   DTC_CHECK_ARG(n_part >= 1 && n_part <= SP_MAX_RANKS && part != nullptr, "sp_ln_bwd: bad n_part %d", n_part);
+  DTC_CHECK_ARG((((uintptr_t)dgamma | (uintptr_t)dbeta) & 15) == 0, "sp_ln_bwd: dgamma / dbeta must be 16-byte aligned");
   SpPeers peers;
   if (sp_fill_peers(&peers, mc_out, peer_out, n_out, "sp_ln_bwd")) return -1;
   int blocks = (Ms + SP_WARPS - 1) / SP_WARPS;
@@ -449,6 +487,7 @@ extern "C" int dtc_sp_ln_bwd_sync(const void* part, int n_part, const void* x, c
                                   int rank, int world, int wait_in, int signal_out, cudaStream_t stream) {
   DTC_CHECK_ARG(Ms > 0 && D % 256 == 0 && D >= 256 && D <= 2048, "sp_ln_bwd_sync: D=%d must be a multiple of 256, <= 2048", D);
   DTC_CHECK_ARG(n_part >= 1 && n_part <= SP_MAX_RANKS && part != nullptr, "sp_ln_bwd_sync: bad n_part %d", n_part);
+  DTC_CHECK_ARG((((uintptr_t)dgamma | (uintptr_t)dbeta) & 15) == 0, "sp_ln_bwd_sync: dgamma / dbeta must be 16-byte aligned");
   SpPeers peers;
   SpSync sync;
   if (sp_fill_peers(&peers, mc_out, peer_out, n_out, "sp_ln_bwd_sync")) return -1;
