@@ -12,7 +12,7 @@ import subprocess
 import sys
 from collections import Counter
 
-KEY = re.compile(r"\b(UTC[A-Z]*MMA[.\w]*|LDTM[.\w]*|STTM[.\w]*|UTMALDG[.\w]*|UTMASTG[.\w]*|UBLKCP[.\w]*|UTCBAR[.\w]*|"
+KEY = re.compile(r"\b(UTC[A-Z]*MMA[.\w]*|LDTM[.\w]*|STTM[.\w]*|UTMALDG[.\w]*|UTMASTG[.\w]*|UTMAREDG[.\w]*|UBLKCP[.\w]*|UTCBAR[.\w]*|"
                  r"UTCATOMSWS[.\w]*|UCGABAR_\w+|LDGMC[.\w]*|STGMC[.\w]*|REDG[.\w]*|RED\.[.\w]*|MUFU\.\w+|HMMA[.\w]*|"
                  r"ST\.E[.\w]*SYS[.\w]*|STG\.E[.\w]*SYS[.\w]*|LDG\.E[.\w]*SYS[.\w]*|LD\.E[.\w]*SYS[.\w]*|MEMBAR[.\w]*|"
                  r"ATOMG[.\w]*|SYNCS[.\w]*)")
@@ -34,9 +34,18 @@ EXCERPTS = {
     "sp_ln_bwd_kernel": (
         "Sequence-parallel LayerNorm backward: partial-slot reduction, gradient rows pushed to every rank",
         [r"ST(G)?\.E[.\w]*SYS"], 6),
-    "gemm_2cta_kernel<false, true, 256, 4>": (
-        "CTA-pair GEMM (cta_group::2, 256 x 256 tile): 2-SM TMA loads, UMMA, slab epilogue with TMA stores",
+    "gemm_2cta_kernel<false, true, 256, 4, 0>": (
+        "CTA-pair GEMM (cta_group::2, 256 x 256 tile, store epilogue compiled in): 2-SM TMA loads, UMMA, slab epilogue with TMA stores",
         [r"UTCHMMA\.2CTA", r"UTMALDG\.2D\.2CTA", r"UTMASTG", r"LDTM"], 4),
+    "gemm_2cta_kernel<true, true, 256, 4, 4>": (
+        "CTA-pair GEMM, fp32 reduce-add epilogue (weight gradients / split-K): accumulator slabs leave through TMA reduce-add",
+        [r"UTMAREDG", r"LDTM", r"STS\.128"], 4),
+    "gemm_grouped_wgrad_2cta_kernel<256>": (
+        "Grouped weight gradients of a layer on CTA pairs: tile table in the parameter block, TMA reduce-add epilogue",
+        [r"UTCHMMA\.2CTA", r"UTMAREDG"], 4),
+    "layernorm_bwd_wide_kernel<2>": (
+        "LayerNorm backward, 16 warps per CTA: per-warp column partials in shared memory, one red.global.add.v4 per 4 columns",
+        [r"RED", r"STS\.128"], 4),
     "flash_attn_fwd_pipe_kernel<32>": (
         "Flash attention forward, pipelined: issue warp (TMA + tcgen05.mma) and softmax warps (LDTM, MUFU.EX2)",
         [r"UTCHMMA", r"MUFU\.EX2", r"LDTM"], 3),
@@ -63,8 +72,8 @@ def parse(path):
             cur = m.group(1)
             funcs[cur] = []
             continue
-        if cur and re.match(r"\s+/\*[0-9a-f]{4}\*/", line):
-            addr = re.match(r"\s+/\*([0-9a-f]{4})\*/", line).group(1)
+        if cur and re.match(r"\s+/\*[0-9a-f]{4,6}\*/", line):
+            addr = re.match(r"\s+/\*([0-9a-f]{4,6})\*/", line).group(1)
             ins = re.sub(r"/\*.*?\*/", "", line)
             funcs[cur].append((addr, " ".join(ins.split()).rstrip(";")))
     return funcs
