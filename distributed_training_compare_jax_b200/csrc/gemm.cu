@@ -2036,8 +2036,10 @@ extern "C" int dtc_gemm_wgrad_grouped_pair(int count, const unsigned long long* 
     if ((rc = make_tmap_2d_bf16(&grp.b[p], reinterpret_cast<const void*>(B[p]), K, Ns[p], ldb[p], BK, 64,
                                 CU_TENSOR_MAP_SWIZZLE_128B)))
       return rc;
-    if ((rc = make_tmap_2d_f32(&grp.o[p], reinterpret_cast<const void*>(out[p]), Ms[p], Ns[p], ldo[p], BM, 32,
-                               CU_TENSOR_MAP_SWIZZLE_128B)))
+    // (box rows clamped to the tensor: a tensor-parallel shard can have fewer than 128 rows; the slab's first rows are the
+    // valid ones, and the second CTA of the pair then addresses a box that lies entirely outside and is dropped)
+    if ((rc = make_tmap_2d_f32(&grp.o[p], reinterpret_cast<const void*>(out[p]), Ms[p], Ns[p], ldo[p],
+                               Ms[p] < BM ? Ms[p] : BM, 32, CU_TENSOR_MAP_SWIZZLE_128B)))
       return rc;
     grp.out[p] = reinterpret_cast<float*>(out[p]);
     grp.ldo[p] = ldo[p];
